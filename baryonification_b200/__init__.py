@@ -1,0 +1,6 @@
+"""baryonification_b200 -- B200-native halo displacement & painting behind the BaryonForge Runners API."""
+from . import utils  # noqa: F401
+from .utils.io import *  # noqa: F401,F403
+from .tables import DisplacementTable, ProfileTable  # noqa: F401
+
+__version__ = "0.1.0"
