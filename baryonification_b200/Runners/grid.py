@@ -1,0 +1,112 @@
+"""Periodic 2-D / 3-D grid runners on the GPU: ``BaryonifyGrid`` and ``PaintProfilesGrid``.
+
+Drop-in for ``BaryonForge/Runners/Map2DRunner.py`` (``DefaultRunnerGrid`` :171-366, ``BaryonifyGrid``
+:370-615, ``PaintProfilesGrid`` :618-814): same constructor and ``process()`` contract.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import time
+
+import numpy as np
+import torch
+
+from .. import _device as dv
+from .. import _lib, host
+from .._ccl import default_mass_def
+from ..tables import displacement_host_table, profile_host_table
+
+__all__ = ["DefaultRunnerGrid", "BaryonifyGrid", "PaintProfilesGrid"]
+
+
+class DefaultRunnerGrid:
+    def __init__(self, HaloNDCatalog, GriddedMap, epsilon_max, model, use_ellipticity=False, mass_def=None,
+                 verbose=True, *, device=None):
+        self.HaloNDCatalog = HaloNDCatalog
+        self.GriddedMap = GriddedMap
+        self.cosmo = HaloNDCatalog.cosmology
+        self.model = model
+        self.epsilon_max = epsilon_max
+        self.mass_def = mass_def if mass_def is not None else default_mass_def()
+        self.verbose = verbose
+        self.use_ellipticity = use_ellipticity
+        self.device = device
+        self.npairs = None
+        self.timings = {}
+        if use_ellipticity:  # Map2DRunner.py:266-272
+            names = HaloNDCatalog.cat.dtype.names
+            assert "q_ell" in names, "The 'q_ell' column is missing, but you set use_ellipticity = True"
+            if not GriddedMap.is2D:
+                assert "c_ell" in names, "The 'c_ell' column is missing, but you set use_ellipticity = True"
+            assert "A_ell" in names, "The 'A_ell' column is missing, but you set use_ellipticity = True"
+
+    def _prepare(self, table_host, baryonify, dev):
+        keys = vars(self.model).get("p_keys", [])
+        if len(keys) > 0:
+            raise NotImplementedError(f"property-keyed tables {keys} are not yet supported by the B200 runners")
+        if self.use_ellipticity:
+            if not self.GriddedMap.is2D:  # Map2DRunner.py:565 / :790
+                if baryonify:
+                    raise NotImplementedError("Currently not able to ellipticities with 3D maps.")
+                raise ValueError("use_ellipticity is not implemented for 3D maps")
+            raise NotImplementedError("use_ellipticity = True is not yet supported by the B200 grid runners")
+        G = self.GriddedMap
+        table = dv.DeviceTable(table_host, dev=dev)
+        s = host.grid_scalars(self.HaloNDCatalog, G, self.mass_def, self.epsilon_max, self.model, baryonify)
+        t = {k: dv.to_dev(s[k], dev=dev) for k in ("pos", "cut", "lnr_shift", "z_in", "M_in")}
+        t["Nsize"] = dv.to_dev(s["Nsize"], dtype=np.int64, dev=dev)
+        rows = table.collapse(t["z_in"], t["M_in"])
+        desc = _lib.GridHalos(t["pos"].data_ptr(), t["Nsize"].data_ptr(), t["cut"].data_ptr(),
+                              t["lnr_shift"].data_ptr(), rows.data_ptr(), s["cut"].size)
+        bins = dv.to_dev(G.bins, dev=dev)
+        return table, s, desc, bins, (t, rows)
+
+
+class BaryonifyGrid(DefaultRunnerGrid):
+    def offsets_device(self, dev):
+        G = self.GriddedMap
+        table, s, desc, bins, keep = self._prepare(displacement_host_table(self.model), True, dev)
+        off = dv.zeros((G.map.size, s["dim"]), dev=dev)
+        cnt = dv.pair_counter(dev)
+        _lib.call("bf_grid_baryonify_atomic", s["dim"], G.Npix, dv.ptr(bins), float(G.res), C.byref(desc),
+                  C.byref(table.desc), dv.ptr(off), dv.ptr(cnt), dv.stream_ptr())
+        self.npairs = int(cnt.item())
+        del keep
+        return off
+
+    def process(self):
+        dev = dv.device(self.device)
+        G = self.GriddedMap
+        with torch.cuda.device(dev):
+            t0 = time.perf_counter()
+            off = self.offsets_device(dev)
+            orig = np.ascontiguousarray(G.map, dtype=np.float64).reshape(-1)
+            orig_d = dv.to_dev(orig, dev=dev, pinned=True)
+            new_d = dv.zeros(orig.size, dev=dev)
+            _lib.call("bf_grid_regrid", 2 if G.is2D else 3, G.Npix, dv.ptr(off), dv.ptr(orig_d), dv.ptr(new_d),
+                      dv.stream_ptr())
+            new_sum = float(new_d.sum().item())
+            new_map = new_d.cpu().numpy().reshape(G.map.shape)
+            self.timings["process"] = time.perf_counter() - t0
+        old_sum = np.sum(orig)  # Map2DRunner.py:611-613
+        assert np.isclose(new_sum, old_sum), \
+            "ERROR in pixel regridding, sum(new_map) [%0.14e] != sum(oldmap) [%0.14e]" % (new_sum, old_sum)
+        return new_map
+
+
+class PaintProfilesGrid(DefaultRunnerGrid):
+    def process(self):
+        dev = dv.device(self.device)
+        G = self.GriddedMap
+        with torch.cuda.device(dev):
+            t0 = time.perf_counter()
+            table, s, desc, bins, keep = self._prepare(profile_host_table(self.model, "2D" if G.is2D else "3D"),
+                                                        False, dev)
+            out = dv.zeros(G.map.size, dev=dev)
+            cnt = dv.pair_counter(dev)
+            _lib.call("bf_grid_paint_atomic", s["dim"], G.Npix, dv.ptr(bins), float(G.res), C.byref(desc),
+                      C.byref(table.desc), dv.ptr(out), dv.ptr(cnt), dv.stream_ptr())
+            self.npairs = int(cnt.item())
+            res = out.cpu().numpy().reshape(G.map.shape)
+            self.timings["process"] = time.perf_counter() - t0
+        return res

@@ -1,0 +1,97 @@
+// bf_common.cuh -- shared host/device helpers of the sm_100a kernels.
+//
+// The whole library is compiled with -fmad=false: every a*b+c in index-determining arithmetic
+// (ring ranges, interpolation-neighbour indices, table cells) then rounds twice, exactly like the
+// reference's numpy / healpix_cxx arithmetic, so pixel lists are bit-identical.  Value arithmetic
+// that wants a fused multiply-add calls fma() explicitly.
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/baryonification_b200.h"
+
+typedef long long i64;
+typedef unsigned long long u64;
+
+void bf_set_error(const char *fmt, ...);
+
+#define BF_CUDA_OK(expr)                                                              \
+    do {                                                                              \
+        cudaError_t _e = (expr);                                                      \
+        if (_e != cudaSuccess) {                                                      \
+            bf_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+            return (int)_e;                                                           \
+        }                                                                             \
+    } while (0)
+
+#define BF_REQUIRE(cond, msg)                                        \
+    do {                                                             \
+        if (!(cond)) {                                               \
+            bf_set_error("%s:%d invalid argument: %s", __FILE__, __LINE__, msg); \
+            return BF_E_INVALID;                                     \
+        }                                                            \
+    } while (0)
+
+#define BF_LAUNCH_OK() BF_CUDA_OK(cudaGetLastError())
+
+static inline int bf_sm_count() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (n <= 0) n = 148;
+    }
+    return n;
+}
+
+// ------------------------------------------------------------------------------------------
+// r-axis descriptor of a table.  scipy's interval search (find_interval_ascending: grid[i] <= x <
+// grid[i+1], last interval closed, out of range -> NaN fill) is reproduced exactly: a uniform-grid
+// guess floor((x - g0) * inv_dx) is corrected against the stored grid, so the cell equals bisection.
+// ------------------------------------------------------------------------------------------
+struct bf_raxis {
+    const double *g; // [nr] ln r grid (global or shared)
+    int nr;
+    double g0, glast, inv_dx;
+};
+
+__device__ __forceinline__ int bf_find_cell(const bf_raxis &ax, double x) {
+    // precondition: g0 <= x <= glast
+    int k = (int)((x - ax.g0) * ax.inv_dx);
+    k = max(0, min(k, ax.nr - 2));
+    while (k > 0 && x < ax.g[k]) --k;
+    while (k < ax.nr - 2 && x >= ax.g[k + 1]) ++k;
+    return k;
+}
+
+// value of one collapsed row at ln r = x; NaN outside the table (fill_value).  The two-product form
+// keeps scipy's inf/NaN propagation: a zero weight still multiplies (0 * -inf = NaN).
+__device__ __forceinline__ double bf_row_lerp(const bf_raxis &ax, const double *__restrict__ row, double x) {
+    if (!(x >= ax.g0 && x <= ax.glast)) return nan("");
+    int k = bf_find_cell(ax, x);
+    double gk = ax.g[k];
+    double t = (x - gk) / (ax.g[k + 1] - gk);
+    return row[k] * (1.0 - t) + row[k + 1] * t;
+}
+
+static inline bf_raxis bf_make_raxis(const bf_table *t) {
+    bf_raxis ax;
+    ax.g = t->gr;
+    ax.nr = (int)t->nr;
+    ax.g0 = t->lnr_first;
+    ax.glast = t->lnr_last;
+    ax.inv_dx = (double)(t->nr - 1) / (ax.glast - ax.g0);
+    return ax;
+}
+
+static inline int bf_check_table(const bf_table *t) {
+    if (!t || !t->gz || !t->gM || !t->gr || !t->values) return 0;
+    if (t->nz < 2 || t->nM < 2 || t->nr < 2 || t->nr > (1 << 30)) return 0;
+    if (!(t->lnr_last > t->lnr_first)) return 0;
+    return 1;
+}
+
+__device__ __forceinline__ bool bf_finite(double v) { return isfinite(v); }

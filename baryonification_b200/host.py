@@ -1,0 +1,128 @@
+"""Vectorised host-side set-up of the per-halo scalars the kernels consume.
+
+The reference computes these inside its Python loop, one halo at a time, through pyccl
+(``Runners/HealpixRunner.py:293-305``, ``Runners/Map2DRunner.py:478-497,716-733``,
+``Runners/SnapshotRunner.py:207-215``, ``Profiles/BaryonCorrection.py:364-381``).  Here they are
+numpy array expressions with the same operation order and the same dtypes (``HaloNDCatalog`` stores
+float32, and the reference takes ``np.log`` / ``get_radius`` of those float32 scalars), handed to the
+device as float64 arrays.  Table construction and cosmology stay on the host, as in the reference.
+"""
+from __future__ import annotations
+
+import numpy as np
+from scipy import interpolate
+
+from ._ccl import get_ccl
+
+
+def runner_cosmology(cosmo: dict, with_w0: bool):
+    """ccl.Cosmology as built at HealpixRunner.py:268-272 (with w0) / Map2DRunner.py:456-459 (without)."""
+    ccl = get_ccl()
+    kw = dict(Omega_c=cosmo["Omega_m"] - cosmo["Omega_b"], Omega_b=cosmo["Omega_b"], h=cosmo["h"],
+              sigma8=cosmo["sigma8"], n_s=cosmo["n_s"], matter_power_spectrum="linear")
+    if with_w0:
+        kw["w0"] = cosmo["w0"]
+    return ccl.Cosmology(**kw)
+
+
+def radius_of(mass_def, cosmo, M, a):
+    """``mass_def.get_radius(cosmo, M_j, a_j)`` for all halos.  M keeps its catalogue dtype so numpy's
+    promotion is the one the reference's per-halo call sees.  Falls back to a per-halo loop when the
+    mass definition does not broadcast over ``a``."""
+    M = np.asarray(M)
+    a_arr = np.broadcast_to(np.asarray(a, dtype=np.float64), M.shape)
+    try:
+        R = np.asarray(mass_def.get_radius(cosmo, M, a if np.ndim(a) == 0 else a_arr))
+        if R.shape == M.shape:
+            return R.astype(np.float64)
+    except Exception:
+        pass
+    return np.array([mass_def.get_radius(cosmo, M[j], a_arr[j]) for j in range(M.size)], dtype=np.float64)
+
+
+def model_cut(model, M, a, need_cut=True):
+    """(eps_model * R_model, ln R_model if Rdelta_sampling else 0) -- BaryonCorrection.py:370-381."""
+    n = np.asarray(M).size
+    if not need_cut:
+        return np.zeros(n), np.zeros(n)
+    R = radius_of(model.mass_def, model.cosmo, M, a) / a
+    cut = model.epsilon_max * R
+    shift = np.log(R) if getattr(model, "Rdelta_sampling", False) else np.zeros(n)
+    return np.asarray(cut, dtype=np.float64), np.asarray(shift, dtype=np.float64)
+
+
+def log_native(M):
+    """np.log(M_j) in the catalogue's dtype (BaryonCorrection.py:369, Tabulate.py:283), widened."""
+    M = np.asarray(M)
+    if M.dtype.byteorder == ">":
+        M = M.astype(M.dtype.newbyteorder("="))
+    return np.log(M).astype(np.float64)
+
+
+def ang2vec_lonlat(lon, lat):
+    """healpy.ang2vec(lon, lat, lonlat=True)."""
+    theta = np.pi / 2.0 - np.radians(lat)
+    phi = np.radians(lon)
+    st = np.sin(theta)
+    return np.ascontiguousarray(np.stack([st * np.cos(phi), st * np.sin(phi), np.cos(theta)], axis=1))
+
+
+def shell_scalars(catalog, cosmo_dict, mass_def, epsilon_max, model, baryonify: bool):
+    ccl = get_ccl()
+    cosmo = runner_cosmology(cosmo_dict, with_w0=True)
+    z_t = np.linspace(0, 30, 1000)  # HealpixRunner.py:279-280
+    D_a = interpolate.CubicSpline(z_t, ccl.angular_diameter_distance(cosmo, 1 / (1 + z_t)))
+    cat = catalog.cat
+    M, z = cat["M"], cat["z"]
+    a = 1 / (1 + z)
+    R = radius_of(mass_def, cosmo, M, a)
+    D = D_a(z)
+    out = dict(a=a, D=D, radius=R * epsilon_max / D, z_in=np.log(1 / a), M_in=log_native(M),
+               lon=np.asarray(cat["ra"], dtype=np.float64), lat=np.asarray(cat["dec"], dtype=np.float64))
+    out["vec"] = ang2vec_lonlat(out["lon"], out["lat"])
+    out["cut"], out["lnr_shift"] = model_cut(model, M, a, need_cut=baryonify)
+    return out
+
+
+def nd_positions(cat, dim):
+    return np.ascontiguousarray(np.stack([np.asarray(cat[k], dtype=np.float64) for k in ("x", "y", "z")[:dim]], axis=1))
+
+
+def grid_scalars(catalog, gmap, mass_def, epsilon_max, model, baryonify: bool):
+    cosmo = runner_cosmology(catalog.cosmology, with_w0=False)
+    cat = catalog.cat
+    M = cat["M"]
+    n = M.size
+    a_j = 1 / (1 + catalog.redshift)
+    a = np.full(n, a_j)
+    R = radius_of(mass_def, cosmo, M, a_j)
+    res = gmap.res
+    if baryonify:  # Map2DRunner.py:485-497
+        R_q = np.clip(epsilon_max * R / a_j, 0, np.max(gmap.bins) / 2)
+        Ns = 2 * R_q / res
+        Nsize = (Ns // 2).astype(np.int64) * 2
+        cut, shift = model_cut(model, M, a_j)
+    else:  # Map2DRunner.py:723-733, :804
+        Rc = R / a_j
+        Ns = 2 * epsilon_max * Rc / res
+        Nsize = np.clip((Ns // 2).astype(np.int64) * 2, 2, gmap.bins.size // 2)
+        if np.any(Nsize % 2):
+            raise ValueError("PaintProfilesGrid: bins.size//2 is odd, the reference's cut-out shapes do not match")
+        cut, shift = Rc * epsilon_max, np.zeros(n)
+    dim = 2 if gmap.is2D else 3
+    return dict(pos=nd_positions(cat, dim), Nsize=Nsize, cut=np.asarray(cut, dtype=np.float64), lnr_shift=shift,
+                z_in=np.log(1 / a), M_in=log_native(M), dim=dim, a=a_j)
+
+
+def snapshot_scalars(catalog, snap, mass_def, epsilon_max, model):
+    cosmo = runner_cosmology(catalog.cosmology, with_w0=False)
+    cat = catalog.cat
+    M = cat["M"]
+    n = M.size
+    a_j = 1 / (1 + catalog.redshift)
+    R = radius_of(mass_def, cosmo, M, a_j)
+    Rq = np.clip(epsilon_max * R / a_j, 0, snap.L / 2)  # SnapshotRunner.py:213-215
+    cut, shift = model_cut(model, M, a_j)
+    dim = 2 if snap.is2D else 3
+    return dict(pos=nd_positions(cat, dim), Rq=np.asarray(Rq, dtype=np.float64), cut=cut, lnr_shift=shift,
+                z_in=np.log(1 / np.full(n, a_j)), M_in=log_native(M), dim=dim, a=a_j)

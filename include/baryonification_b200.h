@@ -1,0 +1,125 @@
+/*
+ * baryonification_b200.h -- C ABI of the B200-native halo displacement-and-painting path.
+ *
+ * Drop-in boundary for the per-halo loops of BaryonForge's Runners.  The reference has no FFI
+ * (it is pure Python); each entry point cites the reference lines whose work it replaces
+ * (paths relative to BaryonForge/).  INTEGRATION.md shows the ctypes binding a maintainer adds.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer unless the name ends in _host; sizes are element counts;
+ *  - `stream` is a cudaStream_t passed as void*; all work is stream-ordered, nothing synchronises
+ *    unless documented; the library never allocates or frees caller memory: scratch comes from a
+ *    caller workspace whose size the matching *_ws_bytes() function returns;
+ *  - return value: 0 = ok, >0 = cudaError_t, <0 = BF_E_* ; bf_last_error() gives a thread-local
+ *    message; nothing throws across the boundary;
+ *  - all floating point is IEEE double, all pixel / cell / particle indices are int64.
+ */
+#ifndef BARYONIFICATION_B200_H
+#define BARYONIFICATION_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BF_OK 0
+#define BF_E_INVALID (-1)   /* bad argument */
+#define BF_E_WORKSPACE (-2) /* workspace too small */
+
+const char *bf_last_error(void);
+int bf_version(void);
+int bf_device_sm_count(int *sm_count_host);
+
+/* A (ln(1+z), ln M, ln r) table resident on the device.  `values` holds d (displacement,
+ * Profiles/BaryonCorrection.py:315) or ln(profile) (utils/Tabulate.py:237-238). */
+typedef struct {
+    const double *gz, *gM, *gr; /* ascending axes */
+    const double *values;       /* [nz][nM][nr], C order */
+    int64_t nz, nM, nr;
+    double lnr_first, lnr_last; /* gr[0], gr[nr-1] (host copies, so no launch needs a read-back) */
+} bf_table;
+
+/* ---- table readout (BaryonCorrection.py:356-390, Tabulate.py:272-294, scipy RGI 'linear') ---- */
+/* rows[j][:] = blend of the 4 (z,M) corners for halo j; rows of out-of-table halos are NaN. */
+int bf_table_collapse_zM(const bf_table *tab_host, int64_t nh, const double *z_in, const double *M_in,
+                         double *rows /* [nh][nr] */, void *stream);
+/* out[i] = readout of halo `row` at radius r[i]; mode 0: linear table with cut (r < cut else 0),
+ * mode 1: exp(log table).  lnr_shift is subtracted from ln r (Rdelta_sampling). */
+int bf_table_readout(const bf_table *tab_host, const double *row, int64_t n, const double *r,
+                     double lnr_shift, double cut, int mode, double *out, void *stream);
+
+/* ---- HEALPix RING geometry (healpy call sites HealpixRunner.py:303-337,429-433) ---- */
+int bf_healpix_ang2pix(int64_t nside, int64_t n, const double *theta, const double *phi, int64_t *pix, void *stream);
+int bf_healpix_pix2ang(int64_t nside, int64_t n, const int64_t *pix, double *theta, double *phi, void *stream);
+int bf_healpix_pix2vec(int64_t nside, int64_t n, const int64_t *pix, double *vec /* [n][3] */, void *stream);
+int bf_healpix_ang2vec_lonlat(int64_t n, const double *lon, const double *lat, double *vec, void *stream);
+int bf_healpix_interp_weights_lonlat(int64_t nside, int64_t n, const double *lon, const double *lat,
+                                     int64_t *pix /* [n][4] */, double *wgt /* [n][4] */, void *stream);
+/* query_disc(inclusive=False, nest=False) for n discs at once: counts[j] = #pixels of disc j.
+ * If pix != NULL, disc j's ascending pixel list is written at pix[offsets[j] ...]. */
+int bf_healpix_query_disc(int64_t nside, int64_t n, const double *vec /* [n][3] */, const double *radius,
+                          int64_t *counts, const int64_t *offsets, int64_t *pix, void *stream);
+
+/* ---- per-halo record of the Shell runners (HealpixRunner.py:293-305, 420-431) ---- */
+typedef struct {
+    const double *vec;       /* [nh][3] hp.ang2vec(ra, dec, lonlat=True) */
+    const double *lon, *lat; /* ra, dec in degrees (for the <4-pixel fallback, :309-310) */
+    const double *radius;    /* R_j * epsilon_max / D_j  [rad] */
+    const double *D, *a;     /* D_A(z_j) [physical Mpc], scale factor */
+    const double *cut;       /* model.epsilon_max * R_model_j (comoving); unused for paint */
+    const double *lnr_shift; /* ln R_model_j if Rdelta_sampling else 0; unused for paint */
+    const double *rows;      /* [nh][nr] from bf_table_collapse_zM */
+    const int64_t *order;    /* optional processing order for the halo-centric kernels (e.g. radius-
+                                descending for load balance), or NULL for catalogue order */
+    int64_t nh;
+} bf_shell_halos;
+
+/* PaintProfilesShell per-halo loop (HealpixRunner.py:418-445): map[pix] += P(r).  Atomic variant. */
+int bf_shell_paint_atomic(int64_t nside, const bf_shell_halos *h_host, const bf_table *tab_host,
+                          double *map, unsigned long long *npairs, void *stream);
+/* BaryonifyShell per-halo loop (HealpixRunner.py:291-331): pix_offsets[pix][3] += unit-vector shift. */
+int bf_shell_baryonify_atomic(int64_t nside, const bf_shell_halos *h_host, const bf_table *tab_host,
+                              double *pix_offsets, unsigned long long *npairs, void *stream);
+/* BaryonifyShell re-binning (HealpixRunner.py:333-341 + regrid_pixels_hpix :13-67). */
+int bf_shell_regrid(int64_t nside, const double *orig_map, const double *pix_offsets, double *new_map,
+                    void *stream);
+
+/* ---- Grid runners (Map2DRunner.py) ---- */
+typedef struct {
+    const double *pos;       /* [nh][dim] halo x,y[,z] (float32 catalogue values widened) */
+    const int64_t *Nsize;    /* cut-out width in cells (:494-497 / :731-733); < 2 = skip */
+    const double *cut;       /* baryonify: model cut; paint: R_j*epsilon_max (:804) */
+    const double *lnr_shift;
+    const double *rows;      /* [nh][nr] */
+    int64_t nh;
+} bf_grid_halos;
+
+/* BaryonifyGrid per-halo loop (:476-580): offsets[cell][dim] += d/res * hat   (atomic variant) */
+int bf_grid_baryonify_atomic(int dim, int64_t npix, const double *bins, double res, const bf_grid_halos *h_host,
+                             const bf_table *tab_host, double *offsets, unsigned long long *npairs, void *stream);
+/* PaintProfilesGrid per-halo loop (:714-810): out[cell] += P masked by finite & r < cut */
+int bf_grid_paint_atomic(int dim, int64_t npix, const double *bins, double res, const bf_grid_halos *h_host,
+                         const bf_table *tab_host, double *out, unsigned long long *npairs, void *stream);
+/* BaryonifyGrid tail (:583-607 + regrid_pixels_2D/3D :14-163): CIC-equivalent periodic deposit. */
+int bf_grid_regrid(int dim, int64_t npix, const double *offsets, const double *orig, double *new_map, void *stream);
+
+/* ---- Snapshot runner (SnapshotRunner.py) ---- */
+typedef struct {
+    const double *pos; /* [nh][dim] */
+    const double *Rq;  /* clip(eps*R_j/a, 0, L/2) (:213-215) */
+    const double *cut, *lnr_shift, *rows;
+    int64_t nh;
+} bf_snap_halos;
+
+size_t bf_snap_ws_bytes(int dim, int64_t nh, double L, double Rq_max);
+/* Periodic ball query + displacement (SnapshotRunner.py:205-247) as a particle-centric gather over a
+ * halo cell list, then add + single wrap (:250-260).  x,y,z in / out are separate arrays (z NULL in 2-D). */
+int bf_snap_displace(int dim, int64_t np, const double *x, const double *y, const double *z, double L, double a,
+                     const bf_snap_halos *h_host, const bf_table *tab_host, double Rq_max, double *xo, double *yo,
+                     double *zo, unsigned long long *npairs, void *ws, size_t ws_bytes, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,204 @@
+"""GPU parity tests proper: CUDA path (through the C ABI) vs the CPU oracle on the same seeded inputs.
+
+Tolerances (BASELINE.json north_star): pixel / cell indices and pair counts bit-exact; per-pixel values
+within 1e-5 relative (we assert far tighter where the arithmetic allows); total mass within 1e-10.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+VAL_RTOL = 1e-5
+MASS_RTOL = 1e-10
+
+
+def relmax(a, b):
+    return np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300)
+
+
+# ------------------------------------------------------------------ HEALPix geometry
+@pytest.mark.parametrize("nside", [1, 2, 8, 64, 1024, 4096])
+def test_healpix_pix_roundtrip_and_vectors(gpu, nside):
+    import torch
+    from baryonification_b200 import _device as dv, _lib
+    from oracle import healpix as ohp
+    rng = np.random.default_rng(nside)
+    npix = 12 * nside * nside
+    pix = np.arange(npix) if npix <= 50000 else np.unique(np.concatenate(
+        [rng.integers(0, npix, 40000), np.arange(2000), npix - 1 - np.arange(2000)]))
+    p = dv.to_dev(pix, dtype=np.int64)
+    th, ph, vec = dv.empty(pix.size), dv.empty(pix.size), dv.empty((pix.size, 3))
+    _lib.call("bf_healpix_pix2ang", nside, pix.size, dv.ptr(p), dv.ptr(th), dv.ptr(ph), dv.stream_ptr())
+    _lib.call("bf_healpix_pix2vec", nside, pix.size, dv.ptr(p), dv.ptr(vec), dv.stream_ptr())
+    back = torch.empty_like(p)
+    _lib.call("bf_healpix_ang2pix", nside, pix.size, dv.ptr(th), dv.ptr(ph), dv.ptr(back), dv.stream_ptr())
+    assert np.array_equal(back.cpu().numpy(), pix)
+    oth, oph = ohp.pix2ang(nside, pix)
+    assert np.allclose(th.cpu().numpy(), oth, rtol=0, atol=4e-16 * np.pi)
+    assert np.allclose(ph.cpu().numpy(), oph, rtol=0, atol=1e-15 * 2 * np.pi)
+    ov = np.stack(ohp.pix2vec(nside, pix), axis=1)
+    assert np.max(np.abs(vec.cpu().numpy() - ov)) < 1e-15
+
+
+@pytest.mark.parametrize("nside", [4, 64, 1024])
+def test_healpix_ang2pix_and_interp_weights(gpu, nside):
+    from baryonification_b200 import _device as dv, _lib
+    from oracle import healpix as ohp
+    rng = np.random.default_rng(100 + nside)
+    n = 20000
+    lon = rng.uniform(0, 360, n)
+    lat = np.degrees(np.arcsin(rng.uniform(-1, 1, n)))
+    lat[:50] = np.linspace(-89.9999, 89.9999, 50)
+    theta, phi = np.pi / 2 - np.radians(lat), np.radians(lon)
+    t, p = dv.to_dev(theta), dv.to_dev(phi)
+    pix = dv.empty(n, dtype=__import__("torch").int64)
+    _lib.call("bf_healpix_ang2pix", nside, n, dv.ptr(t), dv.ptr(p), dv.ptr(pix), dv.stream_ptr())
+    assert np.array_equal(pix.cpu().numpy(), ohp.ang2pix(nside, theta, phi))
+    lo, la = dv.to_dev(lon), dv.to_dev(lat)
+    ip, iw = dv.empty((n, 4), dtype=__import__("torch").int64), dv.empty((n, 4))
+    _lib.call("bf_healpix_interp_weights_lonlat", nside, n, dv.ptr(lo), dv.ptr(la), dv.ptr(ip), dv.ptr(iw),
+              dv.stream_ptr())
+    op, ow = ohp.get_interp_weights(nside, lon, lat, lonlat=True)
+    assert np.array_equal(ip.cpu().numpy(), op.T)
+    assert np.max(np.abs(iw.cpu().numpy() - ow.T)) < 1e-9  # weights ~ 1e-16 * nside sensitivity
+    assert np.allclose(iw.cpu().numpy().sum(1), 1.0, atol=1e-12)
+
+
+@pytest.mark.parametrize("nside", [1, 4, 64, 512])
+def test_healpix_query_disc_bit_exact(gpu, nside):
+    import torch
+    from baryonification_b200 import _device as dv, _lib
+    from oracle import healpix as ohp
+    rng = np.random.default_rng(200 + nside)
+    n = 300
+    vec = rng.normal(size=(n, 3))
+    vec /= np.linalg.norm(vec, axis=1)[:, None]
+    vec[0], vec[1] = [0, 0, 1], [0, 0, -1]
+    vec[2] = [1e-9, 0, 1]; vec[2] /= np.linalg.norm(vec[2])
+    radius = np.where(rng.random(n) < 0.8, rng.uniform(0, 0.2, n), rng.uniform(0, 3.3, n))
+    radius[:3] = [0.3, 0.05, 0.1]
+    v, r = dv.to_dev(vec), dv.to_dev(radius)
+    counts = dv.empty(n, dtype=torch.int64)
+    _lib.call("bf_healpix_query_disc", nside, n, dv.ptr(v), dv.ptr(r), dv.ptr(counts), None, None, dv.stream_ptr())
+    cnt = counts.cpu().numpy()
+    offs = np.concatenate([[0], np.cumsum(cnt)])
+    o = dv.to_dev(offs[:-1], dtype=np.int64)
+    pix = dv.empty(int(offs[-1]) + 1, dtype=torch.int64)
+    _lib.call("bf_healpix_query_disc", nside, n, dv.ptr(v), dv.ptr(r), dv.ptr(counts), dv.ptr(o), dv.ptr(pix),
+              dv.stream_ptr())
+    pix = pix.cpu().numpy()
+    for j in range(n):
+        ref = ohp.query_disc(nside, vec[j], radius[j])
+        assert cnt[j] == ref.size, (j, cnt[j], ref.size)
+        assert np.array_equal(pix[offs[j]:offs[j + 1]], ref), j
+
+
+# ------------------------------------------------------------------ table readout
+def test_table_readout_matches_oracle(gpu):
+    from baryonification_b200 import _device as dv, synthetic as syn
+    from baryonification_b200.tables import displacement_host_table, profile_host_table
+    from oracle import runners as orc
+    dm = syn.displacement_model(0.05, 1.2, 20.0)
+    pm = syn.profile_model(0.05, 1.2, zero_beyond=50.0)
+    rng = np.random.default_rng(7)
+    r = np.concatenate([np.geomspace(5e-4, 5e2, 3000), np.exp(dm.raw_input_r_range[[0, 1, -2, -1]]), [0.0]])
+    for M, z in [(3e13, 0.3), (1e15, 0.9), (2e12, 0.3), (1e14, 1.5), (float(np.exp(dm.raw_input_M_range[3])), 0.2)]:
+        a = 1 / (1 + z)
+        for model, mode, htab in ((dm, 0, displacement_host_table(dm)), (pm, 1, profile_host_table(pm, "2D"))):
+            T = dv.DeviceTable(htab)
+            rows = T.collapse(dv.to_dev([np.log(1 / a)]), dv.to_dev([np.log(M)]))
+            R = model.mass_def.get_radius(model.cosmo, M, a) / a
+            cut = 20.0 * R
+            got = T.readout(rows[0], dv.to_dev(r), 0.0, cut, mode).cpu().numpy()
+            want = orc.readout_displacement(dm, r, M, a) if mode == 0 else orc.readout_profile(pm, r, M, a)
+            assert np.array_equal(np.isnan(got), np.isnan(want))
+            ok = ~np.isnan(want)
+            assert np.allclose(got[ok], want[ok], rtol=1e-12, atol=1e-300)
+
+
+# ------------------------------------------------------------------ runners
+def test_paint_shell_parity(gpu):
+    import baryonification_b200 as bf
+    from baryonification_b200 import synthetic as syn
+    from oracle import runners as orc
+    cfg = syn.config_shell(nside=128, nhalo=1500, zero_map=True, zero_beyond=50.0)
+    got_r = bf.PaintProfilesShell(cfg["catalog"], cfg["field"], cfg["epsilon_max"], cfg["paint_model"], verbose=False)
+    got = got_r.process()
+    ref_r = orc.PaintProfilesShell(cfg["catalog"], cfg["field"], cfg["epsilon_max"], cfg["paint_model"])
+    ref = ref_r.process()
+    assert got_r.npairs == ref_r.npairs  # pair lists: same count ...
+    assert np.array_equal(got != 0, ref != 0)  # ... and same footprint
+    assert relmax(got, ref) < 1e-11
+    assert np.allclose(got, ref, rtol=VAL_RTOL, atol=1e-30)
+
+
+@pytest.mark.parametrize("nside,nhalo,eps", [(64, 600, 20.0), (256, 2500, 10.0)])
+def test_baryonify_shell_parity(gpu, nside, nhalo, eps):
+    import baryonification_b200 as bf
+    from baryonification_b200 import _device as dv, synthetic as syn
+    from oracle import runners as orc
+    cfg = syn.config_shell(nside=nside, nhalo=nhalo, epsilon_max=eps)
+    got_r = bf.BaryonifyShell(cfg["catalog"], cfg["field"], eps, cfg["model"], verbose=False)
+    ref_r = orc.BaryonifyShell(cfg["catalog"], cfg["field"], eps, cfg["model"])
+    off_ref = ref_r.offsets()
+    off_got = got_r.offsets_device(dv.device()).cpu().numpy()
+    assert got_r.npairs == ref_r.npairs
+    assert np.array_equal(np.any(off_got != 0, axis=1), np.any(off_ref != 0, axis=1))
+    assert np.max(np.abs(off_got - off_ref)) < 1e-13 * max(1.0, np.max(np.abs(off_ref)) / 1e-3)
+    got, ref = got_r.process(), ref_r.process()
+    assert np.allclose(got, ref, rtol=VAL_RTOL, atol=1e-5 * ref.mean())
+    assert relmax(got, ref) < 1e-9
+    assert abs(got.sum() - cfg["field"].map.sum()) / cfg["field"].map.sum() < MASS_RTOL
+
+
+def test_baryonify_shell_tiny_halo_fallback(gpu):
+    """Discs holding < 4 pixel centres use the 4 interpolation neighbours (HealpixRunner.py:309-310)."""
+    import baryonification_b200 as bf
+    from baryonification_b200 import _device as dv, synthetic as syn
+    from oracle import runners as orc
+    cfg = syn.config_shell(nside=16, nhalo=400, epsilon_max=1.0)
+    got_r = bf.BaryonifyShell(cfg["catalog"], cfg["field"], 1.0, cfg["model"], verbose=False)
+    ref_r = orc.BaryonifyShell(cfg["catalog"], cfg["field"], 1.0, cfg["model"])
+    off_ref = ref_r.offsets()
+    off_got = got_r.offsets_device(dv.device()).cpu().numpy()
+    assert got_r.npairs == ref_r.npairs
+    assert np.max(np.abs(off_got - off_ref)) < 1e-13
+
+
+@pytest.mark.parametrize("dim,npix,nhalo,eps", [(2, 256, 500, 20.0), (3, 64, 150, 8.0)])
+def test_grid_parity(gpu, dim, npix, nhalo, eps):
+    import baryonification_b200 as bf
+    from baryonification_b200 import synthetic as syn
+    from oracle import runners as orc
+    cfg = syn.config_grid(npix=npix, nhalo=nhalo, dim=dim, epsilon_max=eps, L=(500.0 / 0.7 if dim == 2 else 100.0))
+    got_r = bf.BaryonifyGrid(cfg["catalog"], cfg["field"], eps, cfg["model"], verbose=False)
+    ref_r = orc.BaryonifyGrid(cfg["catalog"], cfg["field"], eps, cfg["model"])
+    got, ref = got_r.process(), ref_r.process()
+    assert got_r.npairs == ref_r.npairs and ref_r.npairs > 1000
+    assert got.shape == ref.shape
+    assert relmax(got, ref) < 1e-9
+    assert abs(got.sum() - cfg["field"].map.sum()) / cfg["field"].map.sum() < MASS_RTOL
+    gp = bf.PaintProfilesGrid(cfg["catalog"], cfg["field"], eps, cfg["paint_model"], verbose=False)
+    rp = orc.PaintProfilesGrid(cfg["catalog"], cfg["field"], eps, cfg["paint_model"])
+    g, r = gp.process(), rp.process()
+    assert gp.npairs == rp.npairs
+    assert np.array_equal(g != 0, r != 0)
+    assert relmax(g, r) < 1e-11
+
+
+@pytest.mark.parametrize("dim,side,nhalo", [(3, 64, 400), (2, 400, 300)])
+def test_snapshot_parity(gpu, dim, side, nhalo):
+    import baryonification_b200 as bf
+    from baryonification_b200 import synthetic as syn
+    from oracle import runners as orc
+    cfg = syn.config_snapshot(npart_side=side, nhalo=nhalo, dim=dim, epsilon_max=5.0, L=(100.0 if dim == 3 else 300.0))
+    got_r = bf.BaryonifySnapshot(cfg["catalog"], cfg["field"], 5.0, cfg["model"], verbose=False)
+    ref_r = orc.BaryonifySnapshot(cfg["catalog"], cfg["field"], 5.0, cfg["model"])
+    got, ref = got_r.process(), ref_r.process()
+    assert got_r.npairs == ref_r.npairs and ref_r.npairs > 100
+    assert got.dtype == ref.dtype
+    for k in "xyz"[:dim]:
+        assert np.max(np.abs(got[k] - ref[k])) < 1e-11
+    assert np.array_equal(got["M"], ref["M"])
