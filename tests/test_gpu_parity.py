@@ -145,7 +145,7 @@ def test_baryonify_shell_parity(gpu, nside, nhalo, eps):
     off_ref = ref_r.offsets()
     off_got = got_r.offsets_device(dv.device()).cpu().numpy()
     assert got_r.npairs == ref_r.npairs
-    assert np.array_equal(np.any(off_got != 0, axis=1), np.any(off_ref != 0, axis=1))
+    # (no exact-footprint check here: a zero displacement leaves normalise(pos) - vec = O(1e-17) rounding noise)
     assert np.max(np.abs(off_got - off_ref)) < 1e-13 * max(1.0, np.max(np.abs(off_ref)) / 1e-3)
     got, ref = got_r.process(), ref_r.process()
     assert np.allclose(got, ref, rtol=VAL_RTOL, atol=1e-5 * ref.mean())
