@@ -14,7 +14,7 @@ import numpy as np
 import torch
 
 from .. import _device as dv
-from .. import _lib, host
+from .. import _lib, engine, host
 from .._ccl import default_mass_def
 from ..tables import displacement_host_table, profile_host_table
 
@@ -23,7 +23,7 @@ __all__ = ["DefaultRunner", "BaryonifyShell", "PaintProfilesShell"]
 
 class DefaultRunner:
     def __init__(self, HaloLightConeCatalog, LightconeShell, epsilon_max, model, use_ellipticity=False,
-                 mass_def=None, verbose=True, *, device=None, variant="atomic"):
+                 mass_def=None, verbose=True, *, device=None, variant="gather"):
         self.HaloLightConeCatalog = HaloLightConeCatalog
         self.LightconeShell = LightconeShell
         self.cosmo = HaloLightConeCatalog.cosmology
@@ -46,16 +46,20 @@ class DefaultRunner:
             raise NotImplementedError(f"You asked to use {keys} properties in Baryonification; "
                                       "ParamTabulatedProfile tables are not yet supported by the B200 runners")
 
-    def _upload_halos(self, s, table, dev, baryonify):
-        """H2D of the per-halo arrays + the (z, M) collapse; returns (ShellHalos descriptor, keep-alive list)."""
-        t = {k: dv.to_dev(s[k], dev=dev) for k in ("vec", "lon", "lat", "radius", "D", "a", "cut", "lnr_shift",
-                                                     "z_in", "M_in")}
-        order = torch.argsort(t["radius"], descending=True)  # largest discs first (load balance)
-        rows = table.collapse(t["z_in"], t["M_in"])
-        desc = _lib.ShellHalos(t["vec"].data_ptr(), t["lon"].data_ptr(), t["lat"].data_ptr(), t["radius"].data_ptr(),
-                               t["D"].data_ptr(), t["a"].data_ptr(), t["cut"].data_ptr(), t["lnr_shift"].data_ptr(),
-                               rows.data_ptr(), order.data_ptr(), s["a"].size)
-        return desc, (t, order, rows)
+    def _engine(self, dev, mode, bands=None):
+        """Host set-up (vectorised) + H2D + (z, M) collapse + halo binning."""
+        self._check_keys()
+        t0 = time.perf_counter()
+        baryonify = mode == engine.BARYONIFY
+        htab = displacement_host_table(self.model) if baryonify else profile_host_table(self.model, "2D")
+        s = host.shell_scalars(self.HaloLightConeCatalog, self.cosmo, self.mass_def, self.epsilon_max, self.model,
+                               baryonify)
+        self.timings["host_setup"] = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        eng = engine.ShellEngine(self.LightconeShell.NSIDE, mode, htab, s, dev, variant=self.variant, bands=bands)
+        eng.upload().bin()
+        self._tick("upload_bin", t0, dev)
+        return eng
 
     def _tick(self, name, t0, dev):
         torch.cuda.synchronize(dev)
@@ -67,20 +71,12 @@ class BaryonifyShell(DefaultRunner):
     """Baryonify a HEALPix *mass* map (RING) with a tabulated displacement model."""
 
     def offsets_device(self, dev):
-        self._check_keys()
+        eng = self._engine(dev, engine.BARYONIFY)
         t0 = time.perf_counter()
-        table = dv.DeviceTable(displacement_host_table(self.model), dev=dev)
-        s = host.shell_scalars(self.HaloLightConeCatalog, self.cosmo, self.mass_def, self.epsilon_max, self.model, True)
-        t0 = self._tick("host_setup", t0, dev)
-        NSIDE = self.LightconeShell.NSIDE
-        desc, keep = self._upload_halos(s, table, dev, True)
-        off = dv.zeros((12 * NSIDE * NSIDE, 3), dev=dev)
-        cnt = dv.pair_counter(dev)
-        _lib.call("bf_shell_baryonify_atomic", NSIDE, C.byref(desc), C.byref(table.desc), dv.ptr(off), dv.ptr(cnt),
-                  dv.stream_ptr())
+        off = eng.accumulate()
+        self.npairs = eng.pair_count()
         self._tick("accumulate", t0, dev)
-        self.npairs = int(cnt.item())
-        del keep
+        self._eng = eng
         return off
 
     def process(self):
@@ -91,8 +87,8 @@ class BaryonifyShell(DefaultRunner):
             off = self.offsets_device(dev)
             t0 = time.perf_counter()
             orig_d = dv.to_dev(orig, dev=dev, pinned=True)
-            new_d = dv.zeros(orig.size, dev=dev)
-            _lib.call("bf_shell_regrid", NSIDE, dv.ptr(orig_d), dv.ptr(off), dv.ptr(new_d), dv.stream_ptr())
+            new_d = self._eng.regrid(orig_d, off)
+            self._eng = None
             new_sum = float(new_d.sum().item())
             new_map = new_d.cpu().numpy()
             self._tick("regrid", t0, dev)
@@ -106,21 +102,12 @@ class PaintProfilesShell(DefaultRunner):
     """Paint a tabulated projected profile (e.g. tSZ) around every halo onto a HEALPix map (RING)."""
 
     def process_device(self, dev):
-        self._check_keys()
         assert self.model is not None, "You must provide a model"
+        eng = self._engine(dev, engine.PAINT)
         t0 = time.perf_counter()
-        table = dv.DeviceTable(profile_host_table(self.model, "2D"), dev=dev)
-        s = host.shell_scalars(self.HaloLightConeCatalog, self.cosmo, self.mass_def, self.epsilon_max, self.model, False)
-        t0 = self._tick("host_setup", t0, dev)
-        NSIDE = self.LightconeShell.NSIDE
-        desc, keep = self._upload_halos(s, table, dev, False)
-        out = dv.zeros(12 * NSIDE * NSIDE, dev=dev)
-        cnt = dv.pair_counter(dev)
-        _lib.call("bf_shell_paint_atomic", NSIDE, C.byref(desc), C.byref(table.desc), dv.ptr(out), dv.ptr(cnt),
-                  dv.stream_ptr())
+        out = eng.accumulate()
+        self.npairs = eng.pair_count()
         self._tick("accumulate", t0, dev)
-        self.npairs = int(cnt.item())
-        del keep
         return out
 
     def process(self):

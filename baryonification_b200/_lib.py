@@ -58,6 +58,13 @@ _SIGS = {
     "bf_healpix_query_disc": (C.c_int, [_i64, _i64, _dbl_p, _dbl_p, _dbl_p, _dbl_p, _dbl_p, C.c_void_p]),
     "bf_shell_paint_atomic": (C.c_int, [_i64, _P(ShellHalos), _P(Table), _dbl_p, _dbl_p, C.c_void_p]),
     "bf_shell_baryonify_atomic": (C.c_int, [_i64, _P(ShellHalos), _P(Table), _dbl_p, _dbl_p, C.c_void_p]),
+    "bf_shell_num_bands": (_i64, [_i64]),
+    "bf_shell_band_pixel_range": (C.c_int, [_i64, _i64, _i64, _P(_i64), _P(_i64)]),
+    "bf_shell_bin_ws_bytes": (C.c_size_t, [_i64, _i64, _i64]),
+    "bf_shell_bin_halos": (C.c_int, [_i64, C.c_int, _P(ShellHalos), _i64, _i64, _i64, C.c_void_p, C.c_size_t,
+                                     _P(_i64), C.c_void_p]),
+    "bf_shell_gather": (C.c_int, [_i64, C.c_int, _P(ShellHalos), _P(Table), _i64, _i64, C.c_void_p, _dbl_p, _i64,
+                                  C.c_int, _dbl_p, C.c_void_p]),
     "bf_shell_regrid": (C.c_int, [_i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p]),
     "bf_grid_baryonify_atomic": (C.c_int, [C.c_int, _i64, _dbl_p, C.c_double, _P(GridHalos), _P(Table), _dbl_p,
                                            _dbl_p, C.c_void_p]),

@@ -1,0 +1,266 @@
+// bf_shell_gather.cu -- pixel-owner ("gather") evaluation of the Shell runners: the deterministic hot path.
+//
+// Replaces the per-halo bodies of PaintProfilesShell.process (Runners/HealpixRunner.py:418-445) and
+// BaryonifyShell.process (:291-331).  One CTA owns one sky cell (8 rings x Wc pixels, bf_shell_cells.cuh),
+// one warp owns one ring of it, one lane owns one pixel of the current 32-pixel strip.  The cell's halo list
+// (catalogue order, from bf_shell_bin.cu) is staged in shared memory in chunks; per chunk
+//   1. thread c sets up candidate c's disc constants once (query_disc prologue);
+//   2. warp w turns them into ring-relative pixel ranges for ITS ring, 32 candidates at a time -- this is
+//      hp.query_disc's ring walk, bit for bit, so the (halo, pixel) pair set equals the reference's;
+//   3. every lane walks the candidate list with its own cursor, skipping (integer compares) to the next
+//      halo whose range holds its pixel, and evaluates that pair; lanes of a warp work on DIFFERENT halos at
+//      the same time, so the fp64 pipe stays full even when discs are narrower than the strip.
+// Each pixel's contributions are summed in registers in catalogue order and written once: no atomics, no
+// read-modify-write traffic, bit-reproducible.
+//
+// Pair arithmetic (fp64).  With delta = v - c (unit vectors), |delta|^2 = d2:
+//   r_tab = |delta| D / a  ->  ln r_tab = 0.5 ln d2 + ln(D/a)          (no sqrt for the table coordinate)
+//   paint:      P = exp(lerp(row, ln r_tab))
+//   baryonify:  the reference moves pos = D v by (d a) along delta/|delta| and renormalises.  With
+//               e = d (a/D) / |delta| the new unit vector is (v + e delta) / sqrt(1 + q), q = e d2 (1 + e)
+//               (v.delta = d2/2 for unit vectors), so  shift = v g + e (1 + g) delta,  g = (1+q)^(-1/2) - 1
+//               evaluated by its series (|q| < 1e-3): algebraically identical to HealpixRunner.py:321-328 and
+//               free of the reference's 1e-16 cancellation noise.
+#include "bf_shell_cells.cuh"
+
+#define GT_WARPS BF_BAND_RINGS
+#define GT_THREADS (32 * GT_WARPS)
+#define GT_CMAX 256
+
+struct gather_args {
+    bf_hpx h;
+    bf_cells cg;
+    bf_shell_halos S;
+    bf_raxis ax;
+    const u64 *keys;
+    const int *cell_begin, *cell_end;
+    i64 band_lo;
+    double *out;
+    i64 pix_base;
+    int accumulate;
+    u64 *npairs;
+};
+
+struct gather_smem {
+    double c0[GT_CMAX], c1[GT_CMAX], c2[GT_CMAX], lnDa[GT_CMAX], cut2[GT_CMAX], aD[GT_CMAX];
+    const double *row[GT_CMAX];
+    double phi[GT_CMAX], z0[GT_CMAX], xa[GT_CMAX], cosr[GT_CMAX];
+    int irmin[GT_CMAX], irmax[GT_CMAX], wn[GT_CMAX], ws[GT_CMAX];
+    int2 rng[GT_WARPS][GT_CMAX];
+};
+
+__device__ __forceinline__ bool in_range(int2 r, int ip) {
+    return (r.x <= r.y) ? (ip >= r.x && ip <= r.y) : (ip <= r.y || ip >= r.x);
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(GT_THREADS, 2) gather_kernel(gather_args A) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    gather_smem &sm = *reinterpret_cast<gather_smem *>(smem_raw);
+    double *g_s = reinterpret_cast<double *>(smem_raw + sizeof(gather_smem));
+    double *ig_s = g_s + A.ax.nr;
+
+    const bf_hpx &h = A.h;
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const i64 band = A.band_lo + blockIdx.x / BF_MAX_COLS;
+    const int col = blockIdx.x % BF_MAX_COLS;
+    if (col >= A.cg.ncol) return;
+    const i64 cellid = band * BF_MAX_COLS + col;
+    const int beg = A.cell_begin[cellid], end = A.cell_end[cellid];
+
+    // this warp's ring
+    const i64 iz = band * BF_BAND_RINGS + 1 + w;
+    i64 sp = 0, nr = 0; bool shifted = false;
+    const bool ring_ok = iz <= 4 * h.nside - 1;
+    if (ring_ok) bfh_ring_info_small(h, iz, sp, nr, shifted);
+    const int ip0 = col * A.cg.wc;
+    const int nstrip = (ring_ok && ip0 < nr) ? (int)min((i64)A.cg.cw, (nr - ip0 + 31) / 32) : 0;
+    const int ncomp = (MODE == 0) ? 1 : 3;
+
+    if (end <= beg) {  // empty cell: the pixels are still owned by this call
+        if (!A.accumulate)
+            for (int s = 0; s < nstrip; ++s) {
+                int ip = ip0 + s * 32 + lane;
+                if (ip < nr)
+                    for (int m = 0; m < ncomp; ++m) A.out[(sp + ip - A.pix_base) * ncomp + m] = 0.0;
+            }
+        return;
+    }
+
+    for (int k = t; k < A.ax.nr; k += GT_THREADS) g_s[k] = A.ax.g[k];
+    __syncthreads();
+    for (int k = t; k < A.ax.nr - 1; k += GT_THREADS) ig_s[k] = 1.0 / (g_s[k + 1] - g_s[k]);
+    bf_raxis ax = A.ax;
+    ax.g = g_s;
+
+    u64 my_pairs = 0;
+    for (int cb = beg; cb < end; cb += GT_CMAX) {
+        const int nc = min(GT_CMAX, end - cb);
+        __syncthreads();
+        if (t < nc) {  // stage candidate t: pair constants + query_disc prologue
+            i64 j = (i64)(A.keys[cb + t] & 0xffffffffull);
+            double c[3] = {A.S.vec[3 * j], A.S.vec[3 * j + 1], A.S.vec[3 * j + 2]};
+            double D = A.S.D[j], a = A.S.a[j];
+            sm.c0[t] = c[0]; sm.c1[t] = c[1]; sm.c2[t] = c[2];
+            sm.aD[t] = a / D;
+            sm.lnDa[t] = log(D / a) - ((MODE == 1) ? A.S.lnr_shift[j] : 0.0);
+            double ct = (MODE == 1) ? A.S.cut[j] * (a / D) : 0.0;
+            sm.cut2[t] = ct * ct;
+            sm.row[t] = A.S.rows + j * (i64)A.ax.nr;
+            bf_disc d = bfh_disc_setup(h, c, A.S.radius[j]);
+            sm.phi[t] = d.phi; sm.z0[t] = d.z0; sm.xa[t] = d.xa; sm.cosr[t] = d.cosr;
+            sm.irmin[t] = (int)d.irmin; sm.irmax[t] = (int)d.irmax;
+            sm.wn[t] = (d.north_end > 0) ? (d.all ? (int)(4 * h.nside) : (int)d.irmin - 1) : 0;  // rings <= wn whole
+            sm.ws[t] = (d.south_begin < h.npix) ? (int)d.irmax + 1 : 0x7fffffff;              // rings >= ws whole
+        }
+        __syncthreads();
+        if (nstrip > 0) {
+            // ring-relative ranges of every candidate for this warp's ring
+            for (int c = lane; c < nc; c += 32) {
+                int2 r = make_int2(0x7fffffff, -1);
+                if ((int)iz <= sm.wn[c] || (int)iz >= sm.ws[c]) r = make_int2(0, (int)nr - 1);
+                else if ((int)iz >= sm.irmin[c] && (int)iz <= sm.irmax[c]) {
+                    bf_disc d;
+                    d.phi = sm.phi[c]; d.z0 = sm.z0[c]; d.xa = sm.xa[c]; d.cosr = sm.cosr[c];
+                    i64 a0, a1, b0, b1;
+                    bfh_disc_ring(h, d, iz, a0, a1, b0, b1);
+                    bool ha = a1 > a0, hb = b1 > b0;
+                    if (ha && hb) r = make_int2((int)(b0 - sp), (int)(a1 - sp) - 1);  // wrapped: [0,hi] U [lo,nr)
+                    else if (ha) r = make_int2((int)(a0 - sp), (int)(a1 - sp) - 1);
+                    else if (hb) r = make_int2((int)(b0 - sp), (int)(b1 - sp) - 1);
+                }
+                sm.rng[w][c] = r;
+            }
+            __syncwarp();
+            for (int s = 0; s < nstrip; ++s) {
+                const int ip = ip0 + s * 32 + lane;
+                const bool valid = ip < nr;
+                double v[3] = {0, 0, 1};
+                if (valid) {
+                    double z, phi, sth; bool have;
+                    bfh_ringpix2loc(h, iz, (i64)ip + 1, z, phi, sth, have);
+                    bfh_loc2vec(z, phi, sth, have, v);
+                }
+                double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0;
+                int cur = valid ? 0 : nc;
+                for (;;) {
+                    while (cur < nc && !in_range(sm.rng[w][cur], ip)) ++cur;
+                    const bool act = cur < nc;
+                    if (!__any_sync(0xffffffffu, act)) break;
+                    if (act) {
+                        const int c = cur++;
+                        double dx = v[0] - sm.c0[c], dy = v[1] - sm.c1[c], dz = v[2] - sm.c2[c];
+                        double d2 = fma(dz, dz, fma(dy, dy, dx * dx));
+                        double x = fma(0.5, log(d2), sm.lnDa[c]);
+                        double val = nan("");
+                        if (x >= ax.g0 && x <= ax.glast) {
+                            int k = bf_find_cell(ax, x);
+                            double tt = (x - g_s[k]) * ig_s[k];
+                            const double *row = sm.row[c];
+                            val = fma(__ldg(row + k + 1), tt, __ldg(row + k) * (1.0 - tt));
+                        }
+                        if (MODE == 0) {
+                            double P = exp(val);
+                            acc0 += bf_finite(P) ? P : 0.0;
+                        } else {
+                            double dsp = (d2 < sm.cut2[c]) ? val : 0.0;  // BaryonCorrection.py:381-382
+                            double e = dsp * sm.aD[c] * rsqrt(d2);
+                            if (!bf_finite(e)) e = 0.0;                   // HealpixRunner.py:323
+                            double q = e * d2 * (1.0 + e);
+                            double gg = q * fma(q, fma(q, fma(q, 0.2734375, -0.3125), 0.375), -0.5);  // (1+q)^-1/2 - 1
+                            if (fabs(q) > 1e-3) gg = rsqrt(1.0 + q) - 1.0;  // pixel (almost) on the halo centre
+                            double ef = fma(e, gg, e);
+                            acc0 += fma(v[0], gg, ef * dx);
+                            acc1 += fma(v[1], gg, ef * dy);
+                            acc2 += fma(v[2], gg, ef * dz);
+                        }
+                        ++my_pairs;
+                    }
+                }
+                if (valid) {
+                    double *o = A.out + (sp + ip - A.pix_base) * ncomp;
+                    const bool add = A.accumulate || cb > beg;
+                    if (MODE == 0) o[0] = add ? o[0] + acc0 : acc0;
+                    else {
+                        o[0] = add ? o[0] + acc0 : acc0;
+                        o[1] = add ? o[1] + acc1 : acc1;
+                        o[2] = add ? o[2] + acc2 : acc2;
+                    }
+                }
+            }
+        }
+    }
+    for (int s = 16; s > 0; s >>= 1) my_pairs += __shfl_down_sync(0xffffffffu, my_pairs, s);
+    if (lane == 0 && A.npairs && my_pairs) atomicAdd(A.npairs, my_pairs);
+}
+
+// Baryonify only: discs with < 4 pixels use the 4 interpolation neighbours (HealpixRunner.py:309-310).  These
+// halos were diverted by the binning stage; they are applied on top of the gathered offsets with fp64
+// atomics (4 pixels each; order only matters if >= 3 of them share a pixel).
+#include "bf_pair.cuh"
+__global__ void tiny_kernel(bf_hpx h, bf_shell_halos S, bf_raxis ax, const int *__restrict__ tiny_list,
+                            const int *__restrict__ tiny_count, i64 pix_first, i64 pix_last, double *out, i64 pix_base,
+                            u64 *npairs) {
+    int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 2, k = threadIdx.x & 3;
+    if (i >= *tiny_count) return;
+    i64 j = tiny_list[i];
+    bf_halo_rec H;
+    H.c[0] = S.vec[3 * j]; H.c[1] = S.vec[3 * j + 1]; H.c[2] = S.vec[3 * j + 2];
+    H.D = S.D[j]; H.a = S.a[j]; H.cut = S.cut[j]; H.lnr_shift = S.lnr_shift[j];
+    H.row = S.rows + j * (i64)ax.nr;
+    i64 p[4]; double wgt[4], v[3], off[3];
+    bfh_interp_lonlat(h, S.lon[j], S.lat[j], p, wgt);
+    if (p[k] < pix_first || p[k] >= pix_last) return;  // another shard owns this pixel
+    bfh_pix2vec(h, p[k], v);
+    bf_pair_baryonify_shell(H, ax, v, off);
+    for (int m = 0; m < 3; ++m) atomicAdd(out + 3 * (p[k] - pix_base) + m, off[m]);
+    if (npairs) atomicAdd(npairs, 1ull);
+}
+
+extern "C" int bf_shell_gather(int64_t nside, int mode, const bf_shell_halos *S, const bf_table *T, int64_t band_lo,
+                               int64_t band_hi, const void *ws, double *out, int64_t pix_base, int accumulate,
+                               unsigned long long *npairs, void *stream) {
+    BF_REQUIRE(nside > 0 && (mode == 0 || mode == 1), "nside / mode");
+    BF_REQUIRE(bf_check_table(T), "bad table");
+    BF_REQUIRE(S && S->nh >= 0 && ws && out, "null argument");
+    bf_cells cg = bf_cells_make(nside);
+    BF_REQUIRE(band_lo >= 0 && band_lo <= band_hi && band_hi <= cg.nbands, "band range");
+    if (band_hi == band_lo) return BF_OK;
+    BF_REQUIRE(S->nh == 0 || (S->vec && S->radius && S->D && S->a && S->rows), "null per-halo array");
+    BF_REQUIRE(mode == 0 || S->nh == 0 || (S->cut && S->lnr_shift && S->lon && S->lat), "null per-halo array");
+    cudaStream_t s = (cudaStream_t)stream;
+    bf_bin_ws w = bf_bin_ws_layout(const_cast<void *>(ws), nside, S->nh, 0);  // fixed part only
+    gather_args A;
+    A.h = bf_hpx_make(nside);
+    A.cg = cg;
+    A.S = *S;
+    A.ax = bf_make_raxis(T);
+    A.keys = w.keys;
+    A.cell_begin = w.cell_begin;
+    A.cell_end = w.cell_end;
+    A.band_lo = band_lo;
+    A.out = out;
+    A.pix_base = pix_base;
+    A.accumulate = accumulate;
+    A.npairs = npairs;
+    size_t smem = sizeof(gather_smem) + 2 * sizeof(double) * (size_t)T->nr;
+    BF_REQUIRE(smem <= 200 * 1024, "table r-axis too long for the shared-memory stage");
+    unsigned grid = (unsigned)((band_hi - band_lo) * BF_MAX_COLS);
+    if (mode == 0) {
+        BF_CUDA_OK(cudaFuncSetAttribute(gather_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        gather_kernel<0><<<grid, GT_THREADS, smem, s>>>(A);
+    } else {
+        BF_CUDA_OK(cudaFuncSetAttribute(gather_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        gather_kernel<1><<<grid, GT_THREADS, smem, s>>>(A);
+    }
+    BF_LAUNCH_OK();
+    if (mode == 1 && S->nh > 0) {
+        int64_t first = 0, last = 0;
+        int rc = bf_shell_band_pixel_range(nside, band_lo, band_hi, &first, &last);
+        if (rc) return rc;
+        tiny_kernel<<<(unsigned)((S->nh * 4 + 127) / 128), 128, 0, s>>>(A.h, *S, A.ax, w.tiny_list, w.tiny_count, first,
+                                                                         last, out, pix_base, npairs);
+        BF_LAUNCH_OK();
+    }
+    return BF_OK;
+}

@@ -1,0 +1,138 @@
+"""Device-resident execution plans ("engines") behind the Runner classes and the benchmark.
+
+An engine owns the HBM-resident inputs of one runner call (per-halo arrays, table, collapsed rows, binning
+workspace) and exposes the kernel stages as methods, so that ``Runner.process()`` (host buffers in, host
+buffers out) and ``bench.py`` (inputs already resident) drive exactly the same code.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _device as dv
+from . import _lib
+from .tables import HostTable
+
+PAINT, BARYONIFY = 0, 1
+
+
+def estimate_entries(nside, radius, vec_z, band_frac=1.0):
+    """Conservative host estimate of the number of (cell, halo) entries the binning stage will emit."""
+    lib = _lib.load()
+    nb = lib.bf_shell_num_bands(nside)
+    nrmax = 4 * nside
+    cw = max(1, -(-nrmax // (64 * 32)))
+    wc = 32 * cw
+    ncol = -(-nrmax // wc)
+    r = np.minimum(np.asarray(radius, dtype=np.float64), np.pi)
+    theta = np.arccos(np.clip(vec_z, -1, 1))
+    nbands = np.minimum(np.ceil(2 * r * nside / 0.66 / 8) + 2, nb)
+    st = np.maximum(np.minimum(np.sin(np.clip(theta - r, 0, np.pi)), np.sin(np.clip(theta + r, 0, np.pi))), 0.0)
+    polar = (theta - r <= 0) | (theta + r >= np.pi)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        half = np.where(polar | (st <= np.sin(r)), np.pi, np.arcsin(np.clip(np.sin(r) / np.maximum(st, 1e-300), 0, 1)))
+    ncols = np.minimum(np.ceil(2 * half * nrmax / (2 * np.pi) / wc) + 2, ncol)
+    return int(np.sum(nbands * ncols) * 1.05 * band_frac) + 1024
+
+
+class ShellEngine:
+    def __init__(self, nside, mode, table: HostTable, scalars: dict, dev, variant="gather", bands=None):
+        self.nside, self.mode, self.dev, self.variant = int(nside), int(mode), dev, variant
+        self.lib = _lib.load(require_cuda=True)
+        self.npix = 12 * self.nside ** 2
+        self.ncomp = 1 if mode == PAINT else 3
+        nb = self.lib.bf_shell_num_bands(self.nside)
+        self.bands = (0, nb) if bands is None else (int(bands[0]), int(bands[1]))
+        f, l = C.c_int64(), C.c_int64()
+        _lib.check(self.lib.bf_shell_band_pixel_range(self.nside, self.bands[0], self.bands[1], C.byref(f), C.byref(l)))
+        self.pix_first, self.pix_last = f.value, l.value
+        self.host_table = table
+        self.s = scalars
+        self.nh = int(np.asarray(scalars["a"]).size)
+        self.table = None
+        self.ws = None
+        self.nentries = None
+        self.npairs = None
+
+    # ---- stage 0: H2D + (z, M) collapse -----------------------------------------------------
+    def upload(self, pinned=False):
+        dev, s = self.dev, self.s
+        self.table = dv.DeviceTable(self.host_table, dev=dev)
+        keys = ("vec", "lon", "lat", "radius", "D", "a", "cut", "lnr_shift", "z_in", "M_in")
+        self.t = {k: dv.to_dev(s[k], dev=dev, pinned=pinned) for k in keys}
+        self.rows = self.table.collapse(self.t["z_in"], self.t["M_in"])
+        self.order = torch.argsort(self.t["radius"], descending=True) if self.variant == "atomic" else None
+        t = self.t
+        self.desc = _lib.ShellHalos(t["vec"].data_ptr(), t["lon"].data_ptr(), t["lat"].data_ptr(),
+                                    t["radius"].data_ptr(), t["D"].data_ptr(), t["a"].data_ptr(),
+                                    t["cut"].data_ptr(), t["lnr_shift"].data_ptr(), self.rows.data_ptr(),
+                                    self.order.data_ptr() if self.order is not None else None, self.nh)
+        self.cnt = dv.pair_counter(dev)
+        return self
+
+    def recollapse(self):
+        self.rows = self.table.collapse(self.t["z_in"], self.t["M_in"])
+        self.desc.rows = self.rows.data_ptr()
+
+    # ---- stage 1: halo binning into sky cells (gather variant) ----------------------------------
+    def bin(self):
+        if self.variant != "gather":
+            return self
+        nb = self.lib.bf_shell_num_bands(self.nside)
+        if self.ws is None:
+            frac = min(1.0, (self.bands[1] - self.bands[0]) / nb * 1.5 + 0.05) if nb else 1.0
+            self.max_entries = min(estimate_entries(self.nside, self.s["radius"], self.s["vec"][:, 2], frac), 2 ** 31 - 2)
+        for _ in range(2):
+            need = self.lib.bf_shell_bin_ws_bytes(self.nside, self.nh, self.max_entries)
+            if self.ws is None or self.ws.numel() < need:
+                self.ws = torch.empty(need, dtype=torch.uint8, device=self.dev)
+            n = C.c_int64()
+            rc = self.lib.bf_shell_bin_halos(self.nside, self.mode, C.byref(self.desc), self.bands[0], self.bands[1],
+                                             self.max_entries, dv.ptr(self.ws), self.ws.numel(), C.byref(n),
+                                             dv.stream_ptr())
+            if rc == -2 and n.value > self.max_entries:  # BF_E_WORKSPACE: grow once to the exact count
+                self.max_entries, self.ws = n.value + 1024, None
+                continue
+            _lib.check(rc, "bf_shell_bin_halos")
+            self.nentries = n.value
+            return self
+        raise _lib.BFError("bf_shell_bin_halos: workspace retry failed")
+
+    # ---- stage 2: pair evaluation ----------------------------------------------------------------
+    def accumulate(self, out=None):
+        """Returns the device accumulator of the engine's pixel range: map [n] or pix_offsets [n, 3]."""
+        n = self.pix_last - self.pix_first
+        shape = (n,) if self.mode == PAINT else (n, 3)
+        self.cnt.zero_()
+        if self.variant == "gather":
+            if out is None:
+                out = dv.empty(shape, dev=self.dev)
+            _lib.call("bf_shell_gather", self.nside, self.mode, C.byref(self.desc), C.byref(self.table.desc),
+                      self.bands[0], self.bands[1], dv.ptr(self.ws), dv.ptr(out), self.pix_first, 0, dv.ptr(self.cnt),
+                      dv.stream_ptr())
+        else:
+            if self.bands != (0, self.lib.bf_shell_num_bands(self.nside)):
+                raise _lib.BFError("the atomic variant does not shard by ring band")
+            if out is None:
+                out = dv.zeros(shape, dev=self.dev)
+            else:
+                out.zero_()
+            fn = "bf_shell_paint_atomic" if self.mode == PAINT else "bf_shell_baryonify_atomic"
+            _lib.call(fn, self.nside, C.byref(self.desc), C.byref(self.table.desc), dv.ptr(out), dv.ptr(self.cnt),
+                      dv.stream_ptr())
+        return out
+
+    def pair_count(self):
+        self.npairs = int(self.cnt.item())
+        return self.npairs
+
+    # ---- stage 3 (baryonify): re-binning ------------------------------------------------------------
+    def regrid(self, orig_d, off, new_d=None):
+        if new_d is None:
+            new_d = dv.zeros(self.npix, dev=self.dev)
+        else:
+            new_d.zero_()
+        _lib.call("bf_shell_regrid", self.nside, dv.ptr(orig_d), dv.ptr(off), dv.ptr(new_d), dv.stream_ptr())
+        return new_d

@@ -81,6 +81,31 @@ int bf_shell_paint_atomic(int64_t nside, const bf_shell_halos *h_host, const bf_
 /* BaryonifyShell per-halo loop (HealpixRunner.py:291-331): pix_offsets[pix][3] += unit-vector shift. */
 int bf_shell_baryonify_atomic(int64_t nside, const bf_shell_halos *h_host, const bf_table *tab_host,
                               double *pix_offsets, unsigned long long *npairs, void *stream);
+/* ---- deterministic gather variant: halo binning into sky cells + pixel-owner evaluation ----
+ * The sphere is cut into cells of 8 consecutive rings x one column of `Wc` consecutive in-ring pixel
+ * indices (Wc = 32*CW, at most 64 columns per ring).  bf_shell_bin_halos lists, for every cell, the halos
+ * whose query_disc footprint touches it, in catalogue order (this replaces hp.query_disc's role of
+ * deciding WHICH pixels a halo updates, HealpixRunner.py:306/:432).  bf_shell_gather then gives every
+ * pixel to one lane, which walks its cell's list in catalogue order and sums in registers: no atomics,
+ * bit-reproducible, and the same per-pixel summation order as the reference's serial halo loop.
+ * Only cells of ring bands [band_lo, band_hi) are binned / evaluated (multi-GPU ring sharding);
+ * pass 0 and bf_shell_num_bands(nside) for the whole sphere. */
+int64_t bf_shell_num_bands(int64_t nside);
+/* pixel range [first, last) covered by ring bands [band_lo, band_hi) */
+int bf_shell_band_pixel_range(int64_t nside, int64_t band_lo, int64_t band_hi, int64_t *first_host, int64_t *last_host);
+size_t bf_shell_bin_ws_bytes(int64_t nside, int64_t nh, int64_t max_entries);
+/* mode 0 = paint, 1 = baryonify (baryonify diverts discs with < 4 pixels to the tiny-halo list).
+ * On return *nentries_host = number of (cell, halo) entries; BF_E_WORKSPACE if it exceeds max_entries
+ * (call again with a workspace sized for *nentries_host).  Synchronises `stream` once. */
+int bf_shell_bin_halos(int64_t nside, int mode, const bf_shell_halos *h_host, int64_t band_lo, int64_t band_hi,
+                       int64_t max_entries, void *ws, size_t ws_bytes, int64_t *nentries_host, void *stream);
+/* out: paint -> map[npix]; baryonify -> pix_offsets[npix][3]; both indexed by GLOBAL pixel number minus
+ * `pix_base` (the first pixel of band_lo when sharded, else 0).  Pixels of the evaluated bands are
+ * OVERWRITTEN (+= when accumulate != 0). */
+int bf_shell_gather(int64_t nside, int mode, const bf_shell_halos *h_host, const bf_table *tab_host,
+                    int64_t band_lo, int64_t band_hi, const void *ws, double *out, int64_t pix_base, int accumulate,
+                    unsigned long long *npairs, void *stream);
+
 /* BaryonifyShell re-binning (HealpixRunner.py:333-341 + regrid_pixels_hpix :13-67). */
 int bf_shell_regrid(int64_t nside, const double *orig_map, const double *pix_offsets, double *new_map,
                     void *stream);

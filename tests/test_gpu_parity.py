@@ -119,12 +119,14 @@ def test_table_readout_matches_oracle(gpu):
 
 
 # ------------------------------------------------------------------ runners
-def test_paint_shell_parity(gpu):
+@pytest.mark.parametrize("variant", ["gather", "atomic"])
+def test_paint_shell_parity(gpu, variant):
     import baryonification_b200 as bf
     from baryonification_b200 import synthetic as syn
     from oracle import runners as orc
     cfg = syn.config_shell(nside=128, nhalo=1500, zero_map=True, zero_beyond=50.0)
-    got_r = bf.PaintProfilesShell(cfg["catalog"], cfg["field"], cfg["epsilon_max"], cfg["paint_model"], verbose=False)
+    got_r = bf.PaintProfilesShell(cfg["catalog"], cfg["field"], cfg["epsilon_max"], cfg["paint_model"], verbose=False,
+                                  variant=variant)
     got = got_r.process()
     ref_r = orc.PaintProfilesShell(cfg["catalog"], cfg["field"], cfg["epsilon_max"], cfg["paint_model"])
     ref = ref_r.process()
@@ -134,13 +136,14 @@ def test_paint_shell_parity(gpu):
     assert np.allclose(got, ref, rtol=VAL_RTOL, atol=1e-30)
 
 
-@pytest.mark.parametrize("nside,nhalo,eps", [(64, 600, 20.0), (256, 2500, 10.0)])
-def test_baryonify_shell_parity(gpu, nside, nhalo, eps):
+@pytest.mark.parametrize("variant", ["gather", "atomic"])
+@pytest.mark.parametrize("nside,nhalo,eps", [(64, 600, 20.0), (256, 2500, 10.0), (8, 300, 30.0)])
+def test_baryonify_shell_parity(gpu, nside, nhalo, eps, variant):
     import baryonification_b200 as bf
     from baryonification_b200 import _device as dv, synthetic as syn
     from oracle import runners as orc
     cfg = syn.config_shell(nside=nside, nhalo=nhalo, epsilon_max=eps)
-    got_r = bf.BaryonifyShell(cfg["catalog"], cfg["field"], eps, cfg["model"], verbose=False)
+    got_r = bf.BaryonifyShell(cfg["catalog"], cfg["field"], eps, cfg["model"], verbose=False, variant=variant)
     ref_r = orc.BaryonifyShell(cfg["catalog"], cfg["field"], eps, cfg["model"])
     off_ref = ref_r.offsets()
     off_got = got_r.offsets_device(dv.device()).cpu().numpy()
@@ -153,13 +156,14 @@ def test_baryonify_shell_parity(gpu, nside, nhalo, eps):
     assert abs(got.sum() - cfg["field"].map.sum()) / cfg["field"].map.sum() < MASS_RTOL
 
 
-def test_baryonify_shell_tiny_halo_fallback(gpu):
+@pytest.mark.parametrize("variant", ["gather", "atomic"])
+def test_baryonify_shell_tiny_halo_fallback(gpu, variant):
     """Discs holding < 4 pixel centres use the 4 interpolation neighbours (HealpixRunner.py:309-310)."""
     import baryonification_b200 as bf
     from baryonification_b200 import _device as dv, synthetic as syn
     from oracle import runners as orc
     cfg = syn.config_shell(nside=16, nhalo=400, epsilon_max=1.0)
-    got_r = bf.BaryonifyShell(cfg["catalog"], cfg["field"], 1.0, cfg["model"], verbose=False)
+    got_r = bf.BaryonifyShell(cfg["catalog"], cfg["field"], 1.0, cfg["model"], verbose=False, variant=variant)
     ref_r = orc.BaryonifyShell(cfg["catalog"], cfg["field"], 1.0, cfg["model"])
     off_ref = ref_r.offsets()
     off_got = got_r.offsets_device(dv.device()).cpu().numpy()
