@@ -66,6 +66,7 @@ _SIGS = {
     "bf_shell_gather": (C.c_int, [_i64, C.c_int, _P(ShellHalos), _P(Table), _i64, _i64, C.c_void_p, _dbl_p, _i64,
                                   C.c_int, _dbl_p, C.c_void_p]),
     "bf_shell_regrid": (C.c_int, [_i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p]),
+    "bf_shell_regrid_range": (C.c_int, [_i64, _i64, _i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p]),
     "bf_grid_baryonify_atomic": (C.c_int, [C.c_int, _i64, _dbl_p, C.c_double, _P(GridHalos), _P(Table), _dbl_p,
                                            _dbl_p, C.c_void_p]),
     "bf_grid_paint_atomic": (C.c_int, [C.c_int, _i64, _dbl_p, C.c_double, _P(GridHalos), _P(Table), _dbl_p,

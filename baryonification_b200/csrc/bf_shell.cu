@@ -197,15 +197,17 @@ extern "C" int bf_shell_baryonify_atomic(int64_t nside, const bf_shell_halos *S,
 // Re-binning: new_vec = pix2vec(p) + offsets[p]; vec2ang(lonlat) -> degrees; get_interp_weights
 // (lonlat) -> 4 neighbours; new_map[nbr] += w * orig[p] for pixels with orig > 0.
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) shell_regrid_kernel(bf_hpx h, const double *__restrict__ orig,
+__global__ void __launch_bounds__(256) shell_regrid_kernel(bf_hpx h, i64 pix_first, i64 pix_last,
+                                                           const double *__restrict__ orig,
                                                            const double *__restrict__ off, double *__restrict__ out) {
-    i64 p = (i64)blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= h.npix) return;
-    double m = orig[p];
+    i64 q = (i64)blockIdx.x * blockDim.x + threadIdx.x;  // local index into orig / off
+    i64 p = pix_first + q;
+    if (p >= pix_last) return;
+    double m = orig[q];
     if (!(m > 0)) return;  // :335
     double v[3];
     bfh_pix2vec(h, p, v);
-    double x = v[0] + off[3 * p], y = v[1] + off[3 * p + 1], z = v[2] + off[3 * p + 2];
+    double x = v[0] + off[3 * q], y = v[1] + off[3 * q + 1], z = v[2] + off[3 * q + 2];
     // healpy.vec2ang(lonlat=True): theta = arccos(z/|v|), phi = arctan2(y, x) (+2pi if < 0), in degrees
     double dnorm = sqrt(x * x + y * y + z * z);
     double theta = acos(z / dnorm);
@@ -220,10 +222,18 @@ __global__ void __launch_bounds__(256) shell_regrid_kernel(bf_hpx h, const doubl
 
 extern "C" int bf_shell_regrid(int64_t nside, const double *orig_map, const double *pix_offsets, double *new_map,
                                void *stream) {
+    return bf_shell_regrid_range(nside, 0, 12 * nside * nside, orig_map, pix_offsets, new_map, stream);
+}
+
+extern "C" int bf_shell_regrid_range(int64_t nside, int64_t pix_first, int64_t pix_last, const double *orig_map,
+                                     const double *pix_offsets, double *new_map, void *stream) {
     BF_REQUIRE(nside > 0 && orig_map && pix_offsets && new_map, "null / nside");
     bf_hpx h = bf_hpx_make(nside);
-    shell_regrid_kernel<<<(unsigned)((h.npix + 255) / 256), 256, 0, (cudaStream_t)stream>>>(h, orig_map, pix_offsets,
-                                                                                           new_map);
+    BF_REQUIRE(pix_first >= 0 && pix_first <= pix_last && pix_last <= h.npix, "pixel range");
+    i64 n = pix_last - pix_first;
+    if (n == 0) return BF_OK;
+    shell_regrid_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(h, pix_first, pix_last, orig_map,
+                                                                                      pix_offsets, new_map);
     BF_LAUNCH_OK();
     return BF_OK;
 }

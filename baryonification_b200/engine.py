@@ -134,5 +134,7 @@ class ShellEngine:
             new_d = dv.zeros(self.npix, dev=self.dev)
         else:
             new_d.zero_()
-        _lib.call("bf_shell_regrid", self.nside, dv.ptr(orig_d), dv.ptr(off), dv.ptr(new_d), dv.stream_ptr())
+        # orig_d / off are the engine's pixel slice; new_d is the full sphere
+        _lib.call("bf_shell_regrid_range", self.nside, self.pix_first, self.pix_last, dv.ptr(orig_d), dv.ptr(off),
+                  dv.ptr(new_d), dv.stream_ptr())
         return new_d

@@ -1,0 +1,335 @@
+#!/usr/bin/env python
+"""bench.py -- halo-pixel updates/s of BaryonifyShell on B200 (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W            # our arm (N>1: launched by torchrun)
+    python bench.py --impl reference --gpus N --steps K ...   # the CPU arm (oracle port, all host threads)
+
+Workload (config.workload): BaryonifyShell on a HEALPix NSIDE 4096 mass map with 1e6 synthetic halos,
+epsilon_max 20, 10x10x500 displacement table -- the configuration BASELINE.json's metric is quoted on; it
+fits one B200 (offsets 4.8 GB + maps 3.2 GB + collapsed rows 4 GB), so it is the N=1 workload too.
+
+One "step" = one full pass of the hot path with inputs resident in HBM: (z,M) table collapse, halo binning
+into sky cells, pair evaluation (gather kernel), re-binning (+ the map all-reduce when N>1).  `value` =
+exact pair count / device time.  `e2e` = the same metric through BaryonifyShell(...).process() with HOST
+numpy inputs: host scalar set-up, pinned H2D, kernels, D2H of the new map, mass check.
+N>1 shards the sphere into ring-band ranges of equal pixel count (strong scaling: the same map and catalogue
+are split); each rank bins the replicated catalogue against its own bands only.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+B_PAIR = 48.0      # algorithmic bytes per pair: RMW of 3 f64 offset components
+B_PIXEL = 104.0    # algorithmic bytes per pixel: map read 8 + offsets 24 + 4-neighbour RMW 64 + zero-init 8
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--nside", type=int, default=4096)
+    ap.add_argument("--nhalo", type=int, default=1_000_000)
+    ap.add_argument("--variant", default="gather", choices=["gather", "atomic"])
+    ap.add_argument("--cpu-sample", type=int, default=10_000, help="halos in the bounded CPU-baseline sample")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 8 for n, v in zip(names, r[4:8]) if v.lower() == "active"})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def make_inputs(args):
+    from oracle import ref_shim  # registers the pyccl stand-in when the real one is absent (inputs only)
+    ref_shim.install()
+    from baryonification_b200 import synthetic as syn
+    return syn.config_shell(nside=args.nside, nhalo=args.nhalo)
+
+
+def band_split(nside, world):
+    """Ring-band ranges with (nearly) equal pixel counts."""
+    import ctypes as C
+    from baryonification_b200 import _lib
+    lib = _lib.load()
+    nb = lib.bf_shell_num_bands(nside)
+    npix = 12 * nside * nside
+    f, l = C.c_int64(), C.c_int64()
+    starts = np.empty(nb + 1, dtype=np.int64)
+    for b in range(nb + 1):
+        lib.bf_shell_band_pixel_range(nside, 0, b, C.byref(f), C.byref(l))
+        starts[b] = l.value
+    cuts = [int(np.searchsorted(starts, npix * r / world)) for r in range(world)] + [nb]
+    cuts[0] = 0
+    return [(cuts[r], cuts[r + 1]) for r in range(world)]
+
+
+def cpu_baseline(cfg, args, nthreads):
+    """Oracle port (C, OpenMP over halos) on a bounded sample; regrid timed on a pixel sub-range; both scaled."""
+    from oracle import runners as orc
+    cat = cfg["catalog"]
+    n = len(cat)
+    m = min(args.cpu_sample, n)
+    idx = np.random.default_rng(42).choice(n, size=n, replace=False)[:m]  # the reference's own shuffle (Parallelize.py:255)
+    sub = cat[np.sort(idx)]
+    r = orc.BaryonifyShell(sub, cfg["field"], cfg["epsilon_max"], cfg["model"], nthreads=nthreads)
+    t0 = time.perf_counter()
+    off = r.offsets()
+    t_loop = time.perf_counter() - t0
+    npix = cfg["field"].map.size
+    p1 = min(npix, 4_000_000)
+    new_map = np.zeros(npix)
+    t0 = time.perf_counter()
+    orc._lib().bfo_regrid_shell_range(cfg["field"].NSIDE, 0, p1, np.ascontiguousarray(cfg["field"].map), off, new_map)
+    t_rg = time.perf_counter() - t0
+    return dict(pairs=r.npairs, t_loop=t_loop, t_regrid_sample=t_rg, regrid_pixels=p1, halos=m)
+
+
+def cpu_value(cb, nhalo, npix):
+    scale = nhalo / cb["halos"]
+    t_full = cb["t_loop"] * scale + cb["t_regrid_sample"] * (npix / cb["regrid_pixels"])
+    return cb["pairs"] * scale / t_full, t_full
+
+
+def run_reference(args, rank, world):
+    """CPU arm: the oracle port of the reference's BaryonifyShell loop with all host threads (the reference itself is
+    pure Python and needs pyccl + healpy, neither installable here)."""
+    if rank != 0:
+        return
+    cfg = make_inputs(args)
+    cores = os.cpu_count() or 1
+    npix = cfg["field"].map.size
+    vals, times = [], []
+    for i in range(args.warmup + args.steps):
+        a = argparse.Namespace(**vars(args))
+        a.cpu_sample = max(500, args.cpu_sample // 4)  # each step is a bounded sample
+        t0 = time.perf_counter()
+        cb = cpu_baseline(cfg, a, cores)
+        dt = time.perf_counter() - t0
+        if i >= args.warmup:
+            vals.append(cpu_value(cb, args.nhalo, npix)[0])
+            times.append(dt)
+    v = float(np.mean(vals))
+    sample = (f"{a.cpu_sample} halos of the seed-42 shuffle (offset loop, OpenMP x{cores}) + re-binning of the first "
+              f"{cb['regrid_pixels']} pixels (serial, as the reference's numba loop); scaled linearly to the full job")
+    print(json.dumps({
+        "impl": "reference", "metric": "halo-pixel updates/sec", "value": v, "unit": "pairs/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": float(np.mean(times) * 1e3),
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"BaryonifyShell NSIDE={args.nside}, {args.nhalo} halos, epsilon_max=20, table 10x10x500"},
+        "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def run_ours(args, rank, local_rank, world):
+    import torch
+    import torch.distributed as dist
+    from baryonification_b200 import _device as dv, _lib, engine, host
+    from baryonification_b200._ccl import default_mass_def
+    from baryonification_b200.tables import displacement_host_table
+    import baryonification_b200 as bf
+
+    _lib.load(require_cuda=True)  # no CPU fallback: fail loudly
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    cfg = make_inputs(args)
+    nside, eps = args.nside, cfg["epsilon_max"]
+    npix = 12 * nside * nside
+    bands = band_split(nside, world)[rank] if world > 1 else None
+    if world > 1 and args.variant != "gather":
+        raise SystemExit("multi-GPU sharding needs the gather variant")
+
+    # ---- inputs resident in HBM -------------------------------------------------------------------------
+    s = host.shell_scalars(cfg["catalog"], cfg["catalog"].cosmo, default_mass_def(), eps, cfg["model"], True)
+    eng = engine.ShellEngine(nside, engine.BARYONIFY, displacement_host_table(cfg["model"]), s, dev,
+                             variant=args.variant, bands=bands).upload()
+    orig_host = np.ascontiguousarray(cfg["field"].map)
+    orig_d = dv.to_dev(orig_host[eng.pix_first:eng.pix_last], dev=dev)
+    nloc = eng.pix_last - eng.pix_first
+    off = dv.empty((nloc, 3), dev=dev)
+    new_d = dv.zeros(npix, dev=dev)
+
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    acc_ms = []
+
+    def step(timed):
+        eng.recollapse()
+        eng.bin()
+        a, b = ev(), ev()
+        a.record()
+        eng.accumulate(off)
+        b.record()
+        eng.regrid(orig_d, off, new_d)
+        if world > 1:
+            dist.all_reduce(new_d)
+        if timed:
+            acc_ms.append((a, b))
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    for _ in range(args.warmup):
+        step(False)
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    barrier()
+    t_a, t_b = ev(), ev()
+    t_a.record()
+    for _ in range(args.steps):
+        step(True)
+    t_b.record()
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    ms = torch.tensor([t_a.elapsed_time(t_b) / args.steps, float(np.mean([a.elapsed_time(b) for a, b in acc_ms]))],
+                      dtype=torch.float64, device=dev)
+    pairs = torch.tensor([eng.pair_count()], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(pairs)
+    ms_step, ms_acc = float(ms[0]), float(ms[1])
+    npairs = int(pairs[0])
+    mass_err = abs(float(new_d.sum()) / float(orig_host.sum()) - 1.0)
+
+    # ---- e2e through the public API: host buffers in, host map out ---------------------------------------------
+    e2e = None
+    if not args.no_e2e and world == 1:
+        runner = bf.BaryonifyShell(cfg["catalog"], cfg["field"], eps, cfg["model"], verbose=False, device=local_rank,
+                                   variant=args.variant)
+        runner.process()  # warm-up (page-in, allocator)
+        ts = []
+        for _ in range(max(1, min(args.steps, 3))):
+            t0 = time.perf_counter()
+            out = runner.process()
+            torch.cuda.synchronize(dev)
+            ts.append(time.perf_counter() - t0)
+        t_e2e = float(np.mean(ts))
+        h2d = sum(np.asarray(v).nbytes for v in s.values()) + cfg["model"].raw_input_d.nbytes + orig_host.nbytes
+        e2e = {"value": runner.npairs / t_e2e, "unit": "pairs/s", "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(out.nbytes), "ms": t_e2e * 1e3, "stages_ms":
+                   {k: round(v * 1e3, 2) for k, v in runner.timings.items()}}
+    elif not args.no_e2e:
+        # sharded e2e: every step also moves this rank's map slice H2D and rank 0 reads the reduced map back
+        pin_in = torch.from_numpy(orig_host[eng.pix_first:eng.pix_last]).pin_memory()
+        pin_out = torch.empty(npix, dtype=torch.float64).pin_memory() if rank == 0 else None
+        ts = []
+        for i in range(1 + max(1, min(args.steps, 3))):
+            barrier()
+            t0 = time.perf_counter()
+            orig_d.copy_(pin_in, non_blocking=True)
+            eng.upload()
+            step(False)
+            if rank == 0:
+                pin_out.copy_(new_d, non_blocking=True)
+            barrier()
+            if i > 0:
+                ts.append(time.perf_counter() - t0)
+        t_e2e = float(np.mean(ts))
+        e2e = {"value": npairs / t_e2e, "unit": "pairs/s", "h2d_bytes_per_step": int(pin_in.numel() * 8),
+               "d2h_bytes_per_step": int(npix * 8) if rank == 0 else 0, "ms": t_e2e * 1e3,
+               "note": "host scalar set-up excluded (replicated catalogue prepared once); slice H2D + result D2H included"}
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        alg_bytes = npairs / world * B_PAIR  # per launch (per rank)
+        ach = alg_bytes / (ms_acc * 1e-3) / 1e9
+        res = {
+            "metric": "halo-pixel updates/sec", "value": npairs / (ms_step * 1e-3), "unit": "pairs/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"BaryonifyShell NSIDE={nside}, {args.nhalo} halos, epsilon_max={eps:g}, table 10x10x500",
+                       "variant": args.variant, "parallelism": f"ring-band x{world}", "pairs": npairs,
+                       "l2": "working set (offsets 24 B/pixel + maps) far exceeds the 126 MB L2",
+                       "mass_conservation_relerr": mass_err, "bin_entries": eng.nentries},
+            "roofline": {"bound": "hbm", "kernel": "gather_kernel<1>" if args.variant == "gather" else "shell_atomic_kernel<1>",
+                         "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                         "peak_source": peak_src, "algorithmic_bytes_per_pair": B_PAIR, "kernel_ms": ms_acc,
+                         "note": "pairs are summed in registers: the kernel is fp64-issue bound, HBM traffic is one 24 B write per pixel"},
+            "e2e": e2e, "gpu_launches": 8 * args.steps, "clocks": clocks}
+        if not args.no_cpu:
+            cores = os.cpu_count() or 1
+            cb = cpu_baseline(cfg, args, cores)
+            v, t_full = cpu_value(cb, args.nhalo, npix)
+            res["cpu_baseline"] = {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port",
+                                   "sample": f"{cb['halos']} halos of the seed-42 shuffle (offset loop {cb['t_loop']:.1f} s, OpenMP x{cores}) "
+                                             f"+ re-binning of {cb['regrid_pixels']} pixels ({cb['t_regrid_sample']:.1f} s, serial); "
+                                             f"scaled linearly: full job ~{t_full:.0f} s", "extrapolated": True}
+        print(json.dumps(res))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", 0))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()

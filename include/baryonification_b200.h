@@ -109,6 +109,10 @@ int bf_shell_gather(int64_t nside, int mode, const bf_shell_halos *h_host, const
 /* BaryonifyShell re-binning (HealpixRunner.py:333-341 + regrid_pixels_hpix :13-67). */
 int bf_shell_regrid(int64_t nside, const double *orig_map, const double *pix_offsets, double *new_map,
                     void *stream);
+/* Same for the pixel slice [pix_first, pix_last) (ring sharding): orig_map / pix_offsets are the LOCAL slices,
+ * new_map is the full-sphere accumulator (deposits may land outside the slice: boundary mass). */
+int bf_shell_regrid_range(int64_t nside, int64_t pix_first, int64_t pix_last, const double *orig_map,
+                          const double *pix_offsets, double *new_map, void *stream);
 
 /* ---- Grid runners (Map2DRunner.py) ---- */
 typedef struct {

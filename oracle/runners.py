@@ -38,6 +38,7 @@ def _lib():
         L.bfo_baryonify_shell_offsets.restype = _i64
         L.bfo_baryonify_shell_offsets.argtypes = ([_i64, _i64] + [_dp] * 10 + _TAB + [_dp, C.c_int])
         L.bfo_regrid_shell.argtypes = [_i64, _dp, _dp, _dp]
+        L.bfo_regrid_shell_range.argtypes = [_i64, _i64, _i64, _dp, _dp, _dp]
         L.bfo_grid_halos.restype = _i64
         L.bfo_grid_halos.argtypes = ([C.c_int, C.c_int, _i64, _dp, C.c_double, _i64, _dp, _ip, _dp, _dp, _dp, _dp]
                                      + _TAB + [_dp, C.c_int])
