@@ -47,14 +47,39 @@ struct gather_smem {
     double phi[GT_CMAX], z0[GT_CMAX], xa[GT_CMAX], cosr[GT_CMAX];
     int irmin[GT_CMAX], irmax[GT_CMAX], wn[GT_CMAX], ws[GT_CMAX];
     int2 rng[GT_WARPS][GT_CMAX];
+    unsigned hits[GT_WARPS][GT_CMAX / 32][32];  // [warp][candidate word][lane]: bit c = candidate 32*word+c hits my pixel
 };
 
-__device__ __forceinline__ bool in_range(int2 r, int ip) {
-    return (r.x <= r.y) ? (ip >= r.x && ip <= r.y) : (ip <= r.y || ip >= r.x);
+// bits a..e (inclusive) of a 32-bit word, clipped to the word
+__device__ __forceinline__ unsigned bits_between(int a, int e) {
+    if (e < 0 || a > 31 || e < a) return 0u;
+    a = max(a, 0);
+    e = min(e, 31);
+    return (0xffffffffu >> (31 - e)) & (0xffffffffu << a);
+}
+
+// lanes (pixels b .. b+31 of the ring) covered by a ring-relative range; r.x > r.y encodes the wrapped
+// pair [0, r.y] U [r.x, nr) and (INT_MAX, -1) the empty set
+__device__ __forceinline__ unsigned lanes_of_range(int2 r, int b) {
+    if (r.x <= r.y) return bits_between(r.x - b, r.y - b);
+    return bits_between(-b, r.y - b) | bits_between(r.x - b, 31);
+}
+
+// 32x32 bit-matrix transpose across a warp: lane c gives row c, lane l receives column l
+__device__ __forceinline__ unsigned warp_transpose32(unsigned x, int lane) {
+    unsigned m = 0x0000ffffu;
+#pragma unroll
+    for (int j = 16; j != 0; j >>= 1) {
+        unsigned y = __shfl_xor_sync(0xffffffffu, x, j);
+        if ((lane & j) == 0) x ^= (((x >> j) ^ y) & m) << j;
+        else x ^= ((y >> j) ^ x) & m;
+        m ^= m << (j >> 1);
+    }
+    return x;
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(GT_THREADS, 2) gather_kernel(gather_args A) {
+__global__ void __launch_bounds__(GT_THREADS, 3) gather_kernel(gather_args A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     gather_smem &sm = *reinterpret_cast<gather_smem *>(smem_raw);
     double *g_s = reinterpret_cast<double *>(smem_raw + sizeof(gather_smem));
@@ -133,6 +158,7 @@ __global__ void __launch_bounds__(GT_THREADS, 2) gather_kernel(gather_args A) {
             }
             __syncwarp();
             for (int s = 0; s < nstrip; ++s) {
+                __syncwarp();
                 const int ip = ip0 + s * 32 + lane;
                 const bool valid = ip < nr;
                 double v[3] = {0, 0, 1};
@@ -142,13 +168,24 @@ __global__ void __launch_bounds__(GT_THREADS, 2) gather_kernel(gather_args A) {
                     bfh_loc2vec(z, phi, sth, have, v);
                 }
                 double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0;
-                int cur = valid ? 0 : nc;
+                // hit matrix of this strip: lane c builds candidate c's lane mask from its range, the warp
+                // transposes it, so every lane ends up with one bit per candidate for ITS pixel
+                const int nw = (nc + 31) >> 5;
+                for (int kw = 0; kw < nw; ++kw) {
+                    const int c = kw * 32 + lane;
+                    unsigned m = (c < nc) ? lanes_of_range(sm.rng[w][c], ip0 + s * 32) : 0u;
+                    sm.hits[w][kw][lane] = warp_transpose32(m, lane);
+                }
+                __syncwarp();
+                int kw = 0;
+                unsigned hm = valid ? sm.hits[w][0][lane] : 0u;
                 for (;;) {
-                    while (cur < nc && !in_range(sm.rng[w][cur], ip)) ++cur;
-                    const bool act = cur < nc;
+                    while (hm == 0u && kw + 1 < nw) hm = valid ? sm.hits[w][++kw][lane] : (++kw, 0u);
+                    const bool act = hm != 0u;
                     if (!__any_sync(0xffffffffu, act)) break;
                     if (act) {
-                        const int c = cur++;
+                        const int c = kw * 32 + __ffs((int)hm) - 1;
+                        hm &= hm - 1u;
                         double dx = v[0] - sm.c0[c], dy = v[1] - sm.c1[c], dz = v[2] - sm.c2[c];
                         double d2 = fma(dz, dz, fma(dy, dy, dx * dx));
                         double x = fma(0.5, log(d2), sm.lnDa[c]);
