@@ -206,3 +206,37 @@ def test_snapshot_parity(gpu, dim, side, nhalo):
     for k in "xyz"[:dim]:
         assert np.max(np.abs(got[k] - ref[k])) < 1e-11
     assert np.array_equal(got["M"], ref["M"])
+
+
+# ------------------------------------------------------------------ committed reference fixtures
+import cases  # noqa: E402
+
+
+@pytest.mark.parametrize("name", cases.case_names())
+def test_cuda_path_matches_reference_fixture(gpu, name):
+    """CUDA path (through the C ABI) vs the outputs of the reference itself (tests/golden/*.npz)."""
+    import baryonification_b200 as bf
+    kind, cfg = cases.build(name)
+    _, got = cases.run(bf, kind, cfg)
+    cases.check(kind, got, cases.golden(name), cfg)
+
+
+def test_cuda_readout_matches_reference_fixture(gpu):
+    from baryonification_b200 import _device as dv, synthetic as syn
+    from baryonification_b200.tables import displacement_host_table, profile_host_table
+    g = cases.golden("readout")
+    dm = syn.displacement_model(0.05, 1.2, 20.0)
+    pm = syn.profile_model(0.05, 1.2, zero_beyond=50.0)
+    r = dv.to_dev(g["r"])
+    for i, (M, z) in enumerate(zip(g["M"], g["z"])):
+        a = 1 / (1 + z)
+        R = dm.mass_def.get_radius(dm.cosmo, M, a) / a
+        for htab, mode, want in ((displacement_host_table(dm), 0, g["displacement"][i]),
+                                 (profile_host_table(pm, "2D"), 1, g["projected"][i]),
+                                 (profile_host_table(pm, "3D"), 1, g["real"][i])):
+            T = dv.DeviceTable(htab)
+            rows = T.collapse(dv.to_dev([np.log(1 / a)]), dv.to_dev([np.log(M)]))
+            got = T.readout(rows[0], r, 0.0, 20.0 * R, mode).cpu().numpy()
+            assert np.array_equal(np.isnan(got), np.isnan(want))
+            ok = ~np.isnan(want)
+            assert np.allclose(got[ok], want[ok], rtol=1e-12, atol=1e-300)

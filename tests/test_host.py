@@ -1,0 +1,124 @@
+"""CPU: host-side logic of the product -- vectorised per-halo scalar set-up (bit-identical to the reference's
+halo-by-halo expressions, restated in oracle/runners.py), table export, containers, error behaviour."""
+import numpy as np
+import pytest
+
+from baryonification_b200 import host, synthetic as syn, tables
+from baryonification_b200._ccl import default_mass_def
+
+
+def test_shell_scalars_bit_identical_to_per_halo_loop():
+    from oracle import runners as orc
+    cfg = syn.config_shell(nside=16, nhalo=500)
+    s = host.shell_scalars(cfg["catalog"], cfg["catalog"].cosmo, default_mass_def(), 20.0, cfg["model"], True)
+    o = orc.BaryonifyShell(cfg["catalog"], cfg["field"], 20.0, cfg["model"])._halo_scalars()
+    for k in ("a", "D", "radius", "z_in", "M_in", "lon", "lat"):
+        assert np.array_equal(s[k], o[k]), k
+    assert np.max(np.abs(s["vec"] - o["vec"])) < 3e-16  # numpy vs libm sin/cos, <= 1 ulp
+    cut, shift = orc._model_cut(cfg["model"], o["M"], o["a"])
+    assert np.array_equal(s["cut"], cut) and np.array_equal(s["lnr_shift"], shift)
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_grid_and_snapshot_scalars_match_per_halo_loop(dim):
+    cfg = syn.config_grid(npix=64, nhalo=300, dim=dim, L=(500 / 0.7 if dim == 2 else 100.0))
+    cat, G = cfg["catalog"], cfg["field"]
+    md = default_mass_def()
+    cosmo = host.runner_cosmology(cat.cosmology, with_w0=False)
+    a = 1 / (1 + cat.redshift)
+    for baryonify in (True, False):
+        s = host.grid_scalars(cat, G, md, 20.0, cfg["model"], baryonify)
+        for j in range(0, len(cat), 7):  # Map2DRunner.py:484-497 / :722-733
+            R = md.get_radius(cosmo, cat.cat["M"][j], a)
+            if baryonify:
+                Ns = int((2 * np.clip(20.0 * R / a, 0, np.max(G.bins) / 2) / G.res) // 2) * 2
+            else:
+                Ns = np.clip(int((2 * 20.0 * (R / a) / G.res) // 2) * 2, 2, G.bins.size // 2)
+                assert s["cut"][j] == (R / a) * 20.0
+            assert s["Nsize"][j] == Ns
+            assert s["M_in"][j] == np.float64(np.log(cat.cat["M"][j]))  # float32 log, widened
+        assert s["pos"].shape == (len(cat), dim) and s["pos"].dtype == np.float64
+    snap = syn.config_snapshot(npart_side=8, nhalo=100, dim=dim, L=100.0)
+    ss = host.snapshot_scalars(snap["catalog"], snap["field"], md, 5.0, snap["model"])
+    assert ss["Rq"].max() <= 50.0 and ss["dim"] == dim
+
+
+def test_nd_catalog_is_big_endian_float32_like_the_reference():
+    cfg = syn.config_grid(npix=16, nhalo=10)
+    c = cfg["catalog"].cat
+    assert c.dtype["M"].str == ">f4" and c.dtype["x"].str == ">f4"  # utils/io.py:204-205
+    lc = syn.config_shell(nside=4, nhalo=10)["catalog"].cat
+    assert lc.dtype["M"] == np.float64
+
+
+def test_lightcone_catalog_pole_clip_and_indexing():
+    import baryonification_b200 as bf
+    cat = bf.HaloLightConeCatalog(ra=[0.0, 10.0, 20.0], dec=[90.0, -90.0, 5.0], M=[1e14] * 3, z=[0.1, 0.2, 0.3],
+                                  cosmo=syn.COSMO)
+    assert abs(cat.cat["dec"][0]) < 90 and abs(cat.cat["dec"][1]) < 90  # utils/io.py:65-68
+    sub = cat[np.array([2, 0])]
+    assert isinstance(sub, bf.HaloLightConeCatalog) and len(sub) == 2 and sub.cat["z"][0] == 0.3
+    with pytest.raises(Exception):
+        bf.HaloLightConeCatalog(ra=[0.0], dec=[0.0], M=[1e14], z=[0.1], cosmo={"Omega_m": 0.3})
+
+
+def test_containers_match_reference_containers():
+    from oracle import ref_shim
+    if not ref_shim.reference_available():
+        pytest.skip("reference tree not present")
+    import refmodels as rm
+    bfg = ref_shim.import_reference()
+    cfg = syn.config_grid(npix=16, nhalo=20, dim=3, L=50.0)
+    ours, ref = cfg["catalog"], rm.ref_nd_catalog(bfg, cfg["catalog"], 3)
+    assert ours.cat.dtype == ref.cat.dtype and ours.cat.tobytes() == ref.cat.tobytes()
+    g, gr = cfg["field"], rm.ref_grid(bfg, cfg["field"])
+    assert (g.Npix, g.res, g.is2D) == (gr.Npix, gr.res, gr.is2D)
+    assert np.array_equal(g.inds, gr.inds)
+    sc = syn.config_shell(nside=4, nhalo=20)
+    assert sc["catalog"].cat.tobytes() == rm.ref_lightcone_catalog(bfg, sc["catalog"]).cat.tobytes()
+    assert sc["field"].NSIDE == rm.ref_shell(bfg, sc["field"]).NSIDE
+    sn = syn.config_snapshot(npart_side=4, nhalo=5, L=20.0)
+    assert sn["field"].cat.tobytes() == rm.ref_snapshot(bfg, sn["field"]).cat.tobytes()
+
+
+def test_table_export_and_errors():
+    dm = syn.displacement_model(0.05, 1.2, 20.0)
+    t = tables.displacement_host_table(dm)
+    assert t.values.shape == (10, 10, 500) and not t.is_log
+    pm = syn.profile_model(0.05, 1.2, zero_beyond=50.0)
+    tp = tables.profile_host_table(pm, "2D")
+    assert tp.is_log and np.isneginf(tp.values).any()  # ln 0 kept as -inf (Tabulate.py:237)
+
+    class Analytic:  # an un-tabulated profile: no raw_input_* -> TypeError, never a CPU evaluation
+        def projected(self, *a):
+            return 0
+
+    with pytest.raises(TypeError, match="no tabulated data"):
+        tables.profile_host_table(Analytic(), "2D")
+
+    class Untabulated:  # reference message when setup_interpolator() was not run (BaryonCorrection.py:426)
+        def displacement(self, *a):
+            return 0
+
+    with pytest.raises(NameError, match="No Table created"):
+        tables.displacement_host_table(Untabulated())
+    with pytest.raises(ValueError):
+        tables.HostTable([0, 1], [0, 1], [1, 0], np.zeros((2, 2, 2)), False)
+
+
+def test_runner_constructor_contract():
+    """Positional order and public attributes SplitJoinParallel relies on (utils/Parallelize.py:237-243,271)."""
+    import baryonification_b200 as bf
+    cfg = syn.config_shell(nside=4, nhalo=10)
+    md = default_mass_def()
+    r = bf.PaintProfilesShell(cfg["catalog"], cfg["field"], 20.0, cfg["paint_model"], False, md, False)
+    for attr in ("HaloLightConeCatalog", "LightconeShell", "cosmo", "model", "mass_def", "epsilon_max",
+                 "use_ellipticity", "verbose"):
+        assert hasattr(r, attr)
+    r2 = type(r)(r.HaloLightConeCatalog[np.arange(5)], r.LightconeShell, r.epsilon_max, r.model, r.use_ellipticity,
+                 r.mass_def, verbose=False)
+    assert len(r2.HaloLightConeCatalog) == 5
+    with pytest.raises(NotImplementedError):  # HealpixRunner.py:164-165
+        bf.BaryonifyShell(cfg["catalog"], cfg["field"], 20.0, cfg["model"], True)
+    import pickle
+    pickle.loads(pickle.dumps(r))  # runners stay picklable (joblib/loky), no live CUDA handles on self
