@@ -21,7 +21,7 @@ __all__ = ["DefaultRunnerGrid", "BaryonifyGrid", "PaintProfilesGrid"]
 
 class DefaultRunnerGrid:
     def __init__(self, HaloNDCatalog, GriddedMap, epsilon_max, model, use_ellipticity=False, mass_def=None,
-                 verbose=True, *, device=None):
+                 verbose=True, *, device=None, regrid="sorted"):
         self.HaloNDCatalog = HaloNDCatalog
         self.GriddedMap = GriddedMap
         self.cosmo = HaloNDCatalog.cosmology
@@ -31,6 +31,7 @@ class DefaultRunnerGrid:
         self.verbose = verbose
         self.use_ellipticity = use_ellipticity
         self.device = device
+        self.regrid = regrid  # re-binning: "sorted" (deterministic, default) | "atomic"
         self.npairs = None
         self.timings = {}
         if use_ellipticity:  # Map2DRunner.py:266-272
@@ -83,8 +84,15 @@ class BaryonifyGrid(DefaultRunnerGrid):
             orig = np.ascontiguousarray(G.map, dtype=np.float64).reshape(-1)
             orig_d = dv.to_dev(orig, dev=dev, pinned=True)
             new_d = dv.zeros(orig.size, dev=dev)
-            _lib.call("bf_grid_regrid", 2 if G.is2D else 3, G.Npix, dv.ptr(off), dv.ptr(orig_d), dv.ptr(new_d),
-                      dv.stream_ptr())
+            dim = 2 if G.is2D else 3
+            if self.regrid == "sorted":
+                lib = _lib.load(require_cuda=True)
+                nb = lib.bf_grid_regrid_sorted_ws_bytes(dim, G.Npix)
+                ws = torch.empty(nb, dtype=torch.uint8, device=dev)
+                _lib.call("bf_grid_regrid_sorted", dim, G.Npix, dv.ptr(off), dv.ptr(orig_d), dv.ptr(new_d), dv.ptr(ws),
+                          nb, dv.stream_ptr())
+            else:
+                _lib.call("bf_grid_regrid", dim, G.Npix, dv.ptr(off), dv.ptr(orig_d), dv.ptr(new_d), dv.stream_ptr())
             new_sum = float(new_d.sum().item())
             new_map = new_d.cpu().numpy().reshape(G.map.shape)
             self.timings["process"] = time.perf_counter() - t0

@@ -23,7 +23,7 @@ __all__ = ["DefaultRunner", "BaryonifyShell", "PaintProfilesShell"]
 
 class DefaultRunner:
     def __init__(self, HaloLightConeCatalog, LightconeShell, epsilon_max, model, use_ellipticity=False,
-                 mass_def=None, verbose=True, *, device=None, variant="gather"):
+                 mass_def=None, verbose=True, *, device=None, variant="gather", regrid="sorted", pinned_output=True):
         self.HaloLightConeCatalog = HaloLightConeCatalog
         self.LightconeShell = LightconeShell
         self.cosmo = HaloLightConeCatalog.cosmology
@@ -33,7 +33,9 @@ class DefaultRunner:
         self.verbose = verbose
         self.use_ellipticity = use_ellipticity
         self.device = device
-        self.variant = variant
+        self.variant = variant          # pair stage: "gather" (deterministic, default) | "atomic"
+        self.regrid = regrid            # re-binning: "sorted" (deterministic, default) | "atomic"
+        self.pinned_output = pinned_output
         self.npairs = None
         self.timings = {}
         if use_ellipticity:  # HealpixRunner.py:164-165
@@ -83,16 +85,17 @@ class BaryonifyShell(DefaultRunner):
         dev = dv.device(self.device)
         with torch.cuda.device(dev):
             orig = np.ascontiguousarray(self.LightconeShell.map, dtype=np.float64)
-            NSIDE = self.LightconeShell.NSIDE
+            up = dv.AsyncUpload(orig, dev)  # the 8 B/pixel map travels while halos are set up, binned and evaluated
             off = self.offsets_device(dev)
             t0 = time.perf_counter()
-            orig_d = dv.to_dev(orig, dev=dev, pinned=True)
-            new_d = self._eng.regrid(orig_d, off)
+            orig_d = up.result()
+            new_d = self._eng.regrid(orig_d, off, method=self.regrid)
             self._eng = None
-            new_sum = float(new_d.sum().item())
-            new_map = new_d.cpu().numpy()
-            self._tick("regrid", t0, dev)
-        old_sum = np.sum(orig)  # HealpixRunner.py:344-346
+            new_sum_d, old_sum_d = new_d.sum(), orig_d.sum()  # the reference's two np.sum's, on the device
+            t0 = self._tick("regrid", t0, dev)
+            new_map = dv.to_host(new_d, self.pinned_output)
+            new_sum, old_sum = float(new_sum_d.item()), float(old_sum_d.item())  # HealpixRunner.py:344-346
+            self._tick("d2h", t0, dev)
         assert np.isclose(new_sum, old_sum), \
             "ERROR in pixel regridding, sum(new_map) [%0.14e] != sum(oldmap) [%0.14e]" % (new_sum, old_sum)
         return new_map
@@ -113,4 +116,4 @@ class PaintProfilesShell(DefaultRunner):
     def process(self):
         dev = dv.device(self.device)
         with torch.cuda.device(dev):
-            return self.process_device(dev).cpu().numpy()
+            return dv.to_host(self.process_device(dev), self.pinned_output)

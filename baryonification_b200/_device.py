@@ -34,6 +34,59 @@ def to_dev(a, dtype=np.float64, dev=None, pinned=False):
     return t.to(dev or device(), non_blocking=pinned)
 
 
+class AsyncUpload:
+    """Pageable numpy array -> HBM, off the critical path.
+
+    A helper thread copies the caller's array into page-locked memory (torch's caching host allocator keeps the
+    block for the next call; the CPU copy is multi-threaded) and enqueues the H2D copy on a side stream, while
+    the main thread sets up halos and runs the binning / pair kernels.  ``result()`` joins and makes the current
+    stream wait for the copy."""
+
+    def __init__(self, a, dev, dtype=np.float64):
+        import threading
+        self.dev = dev
+        self.side = torch.cuda.Stream(device=dev)
+        self.done = torch.cuda.Event()
+        self.out = None
+        self.err = None
+        a = np.ascontiguousarray(a, dtype=dtype)
+
+        def work():
+            try:
+                with torch.cuda.device(dev):
+                    src = torch.from_numpy(a) if a.flags.writeable else torch.from_numpy(a.copy())
+                    pin = torch.empty(src.shape, dtype=src.dtype, pin_memory=True)
+                    pin.copy_(src)
+                    with torch.cuda.stream(self.side):
+                        self.out = pin.to(dev, non_blocking=True)
+                        self.done.record(self.side)
+            except BaseException as e:  # re-raised in result()
+                self.err = e
+
+        self.th = threading.Thread(target=work, daemon=True)
+        self.th.start()
+
+    def result(self):
+        self.th.join()
+        if self.err is not None:
+            raise self.err
+        torch.cuda.current_stream(self.dev).wait_event(self.done)
+        self.out.record_stream(torch.cuda.current_stream(self.dev))
+        return self.out
+
+
+def to_host(t, pinned=True):
+    """Device tensor -> numpy array owned by the caller.  With ``pinned`` the array is backed by page-locked
+    memory from torch's caching host allocator (returned to the cache when the array is garbage-collected): the
+    D2H copy then runs at PCIe speed instead of the pageable-staging speed."""
+    if not pinned:
+        return t.cpu().numpy()
+    out = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+    out.copy_(t, non_blocking=True)
+    torch.cuda.current_stream(t.device).synchronize()
+    return out.numpy()
+
+
 def zeros(shape, dtype=torch.float64, dev=None):
     return torch.zeros(shape, dtype=dtype, device=dev or device())
 

@@ -1,0 +1,208 @@
+// bf_regrid_sorted.cu -- deterministic re-binning: sort-by-destination + in-order segmented reduction.
+//
+// The atomic re-binning kernels (bf_shell.cu: shell_regrid_kernel, bf_grid.cu: grid_regrid_kernel) add the
+// 4 (HEALPix) / 2^D (grid) deposits of every displaced pixel with fp64 RED.ADD, so the summation order -- and
+// the last bits of the map -- change from run to run.  This variant reproduces the SERIAL order of the
+// reference's numba loops (regrid_pixels_hpix, Runners/HealpixRunner.py:13-67: for i in parents, for j in 0..3:
+// hmap[child[i,j]] += w[i,j]*val[i];  regrid_pixels_2D/3D, Runners/Map2DRunner.py:14-163):
+//   1. emit   : entry e = i*K + j  ->  key[e] = destination pixel, val[e] = w*val  (masked pixels: key = sentinel)
+//   2. sort   : stable LSD radix sort of (key, val) by key (CUB) -> inside a destination the entries stay in
+//               (i, j) order, i.e. the order in which the reference's loop would have added them
+//   3. reduce : the thread that sees the head of a segment adds the segment left to right and does ONE
+//               non-atomic += on the map.  Segments are short (mean K), so this is a streaming pass.
+// HBM-bound: emit writes 12 B/entry, the sort moves 12 B/entry x 2 x passes, reduce reads 12 B/entry.
+#include <cub/cub.cuh>
+
+#include "bf_healpix.cuh"
+
+typedef unsigned int u32;
+
+struct sorted_ws {
+    u32 *k0, *k1;
+    double *v0, *v1;
+    void *cub_tmp;
+    size_t cub_bytes, total;
+};
+
+static size_t al256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+static sorted_ws sorted_layout(void *base, i64 nent) {
+    sorted_ws w;
+    char *p = (char *)base;
+    size_t o = 0;
+    size_t n = (size_t)(nent > 0 ? nent : 1);
+    w.k0 = (u32 *)(p + o);    o += al256(sizeof(u32) * n);
+    w.k1 = (u32 *)(p + o);    o += al256(sizeof(u32) * n);
+    w.v0 = (double *)(p + o); o += al256(sizeof(double) * n);
+    w.v1 = (double *)(p + o); o += al256(sizeof(double) * n);
+    cub::DoubleBuffer<u32> dk(nullptr, nullptr);
+    cub::DoubleBuffer<double> dv(nullptr, nullptr);
+    size_t cb = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, cb, dk, dv, (i64)n, 0, 32);
+    w.cub_bytes = cb + 256;
+    w.cub_tmp = (void *)(p + o); o += al256(w.cub_bytes);
+    w.total = o;
+    return w;
+}
+
+// head-of-segment thread sums its segment in stored order; sentinel keys (>= nout) are skipped
+__global__ void __launch_bounds__(256) segment_reduce_kernel(i64 n, const u32 *__restrict__ key,
+                                                             const double *__restrict__ val, u32 nout,
+                                                             double *__restrict__ out) {
+    i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    u32 k = key[i];
+    if (k >= nout) return;
+    if (i > 0 && key[i - 1] == k) return;
+    double s = val[i];
+    for (i64 e = i + 1; e < n && key[e] == k; ++e) s += val[e];
+    out[k] += s;
+}
+
+static int sort_and_reduce(sorted_ws &w, i64 nent, u32 nout, double *out, cudaStream_t s) {
+    int bits = 1;
+    while (((u64)1 << bits) <= (u64)nout) ++bits;  // keys 0 .. nout (sentinel) inclusive
+    cub::DoubleBuffer<u32> dk(w.k0, w.k1);
+    cub::DoubleBuffer<double> dv(w.v0, w.v1);
+    size_t cb = w.cub_bytes;
+    BF_CUDA_OK(cub::DeviceRadixSort::SortPairs(w.cub_tmp, cb, dk, dv, nent, 0, bits, s));
+    segment_reduce_kernel<<<(unsigned)((nent + 255) / 256), 256, 0, s>>>(nent, dk.Current(), dv.Current(), nout, out);
+    BF_LAUNCH_OK();
+    return BF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// HEALPix shell (HealpixRunner.py:333-341)
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) shell_emit_kernel(bf_hpx h, i64 pix_first, i64 pix_last,
+                                                         const double *__restrict__ orig,
+                                                         const double *__restrict__ off, u32 *__restrict__ key,
+                                                         double *__restrict__ val) {
+    i64 q = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    i64 p = pix_first + q;
+    if (p >= pix_last) return;
+    double m = orig[q];
+    uint4 kk = make_uint4((u32)h.npix, (u32)h.npix, (u32)h.npix, (u32)h.npix);
+    double vv[4] = {0.0, 0.0, 0.0, 0.0};
+    if (m > 0) {  // :335
+        double v[3];
+        bfh_pix2vec(h, p, v);
+        double x = v[0] + off[3 * q], y = v[1] + off[3 * q + 1], z = v[2] + off[3 * q + 2];
+        double dnorm = sqrt(x * x + y * y + z * z);
+        double theta = acos(z / dnorm);
+        double phi = atan2(y, x);
+        if (phi < 0) phi += BFH_TWOPI;
+        i64 cp[4]; double w[4];
+        bfh_interp_lonlat(h, phi * BFH_RAD2DEG, 90.0 - theta * BFH_RAD2DEG, cp, w);
+        kk = make_uint4((u32)cp[0], (u32)cp[1], (u32)cp[2], (u32)cp[3]);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) vv[k] = w[k] * m;
+    }
+    reinterpret_cast<uint4 *>(key)[q] = kk;
+    reinterpret_cast<double2 *>(val)[2 * q] = make_double2(vv[0], vv[1]);
+    reinterpret_cast<double2 *>(val)[2 * q + 1] = make_double2(vv[2], vv[3]);
+}
+
+extern "C" size_t bf_shell_regrid_sorted_ws_bytes(int64_t nside, int64_t npix_local) {
+    if (nside <= 0 || npix_local < 0) return 0;
+    return sorted_layout(nullptr, 4 * npix_local).total;
+}
+
+extern "C" int bf_shell_regrid_sorted(int64_t nside, int64_t pix_first, int64_t pix_last, const double *orig_map,
+                                      const double *pix_offsets, double *new_map, void *ws, size_t ws_bytes,
+                                      void *stream) {
+    BF_REQUIRE(nside > 0 && orig_map && pix_offsets && new_map, "null / nside");
+    bf_hpx h = bf_hpx_make(nside);
+    BF_REQUIRE(h.npix < 0xffffffffll, "nside too large for 32-bit destination keys");
+    BF_REQUIRE(pix_first >= 0 && pix_first <= pix_last && pix_last <= h.npix, "pixel range");
+    i64 n = pix_last - pix_first;
+    if (n == 0) return BF_OK;
+    sorted_ws w = sorted_layout(ws, 4 * n);
+    if (!ws || ws_bytes < w.total) {
+        bf_set_error("bf_shell_regrid_sorted: workspace %zu < %zu bytes", ws_bytes, w.total);
+        return BF_E_WORKSPACE;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    shell_emit_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(h, pix_first, pix_last, orig_map, pix_offsets, w.k0,
+                                                                  w.v0);
+    BF_LAUNCH_OK();
+    return sort_and_reduce(w, 4 * n, (u32)h.npix, new_map, s);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// periodic grids (Map2DRunner.py:583-607): same CIC decomposition as grid_regrid_kernel (bf_grid.cu)
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ double pymod_s(double a, double n) {
+    double r = fmod(a, n);
+    if (r < 0) r += n;
+    return r;
+}
+
+template <int DIM>
+__global__ void __launch_bounds__(256) grid_emit_kernel(i64 N, const double *__restrict__ off,
+                                                        const double *__restrict__ orig, u32 *__restrict__ key,
+                                                        double *__restrict__ val) {
+    const i64 ncell = (DIM == 2) ? N * N : N * N * N;
+    const int K = 1 << DIM;
+    i64 cell = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell >= ncell) return;
+    i64 a, b, c = 0;
+    if (DIM == 2) { a = cell / N; b = cell - a * N; }
+    else { a = cell / (N * N); i64 rem = cell - a * N * N; b = rem / N; c = rem - b * N; }
+    double o[3] = {0, 0, 0};
+#pragma unroll
+    for (int m = 0; m < DIM; ++m) {
+        double v = off[DIM * cell + m];
+        o[m] = bf_finite(v) ? v : 0.0;
+    }
+    double sft[3] = {pymod_s(o[1] + (double)a, (double)N), pymod_s(o[0] + (double)b, (double)N),
+                     (DIM == 3) ? pymod_s(o[2] + (double)c, (double)N) : 0.0};
+    i64 i0[3]; double w0[3], w1[3];
+#pragma unroll
+    for (int m = 0; m < DIM; ++m) {
+        i0[m] = (i64)sft[m];
+        w0[m] = (double)(i0[m] + 1) - sft[m];
+        w1[m] = (sft[m] + 1.0) - (double)(i0[m] + 1);
+    }
+    double m0 = orig[cell];
+    // the reference scans its neighbourhood with the first axis outermost: (ca, cb[, cc]) ascending in the
+    // UNWRAPPED index is the order in which it adds to the map; a destination cell receives at most one deposit
+    // per source cell (N >= 5), so only the source order matters for the sum and any fixed slot order will do
+#pragma unroll
+    for (int e = 0; e < K; ++e) {
+        int ca = (DIM == 2) ? (e >> 1) : (e >> 2), cb = (DIM == 2) ? (e & 1) : ((e >> 1) & 1), cc = e & 1;
+        double wa = ca ? w1[0] : w0[0], wb = cb ? w1[1] : w0[1], wc = (DIM == 3) ? (cc ? w1[2] : w0[2]) : 1.0;
+        bool okw = (wa > 0) && (wb > 0) && (DIM == 2 || wc > 0);
+        i64 ia = (i0[0] + ca) % N, ib = (i0[1] + cb) % N, ic = (DIM == 3) ? (i0[2] + cc) % N : 0;
+        i64 dst = (DIM == 2) ? ia * N + ib : (ia * N + ib) * N + ic;
+        double wv = (DIM == 2) ? (wb * wa) * m0 : ((wb * wa) * wc) * m0;
+        key[cell * K + e] = okw ? (u32)dst : (u32)ncell;
+        val[cell * K + e] = okw ? wv : 0.0;
+    }
+}
+
+extern "C" size_t bf_grid_regrid_sorted_ws_bytes(int dim, int64_t npix) {
+    if ((dim != 2 && dim != 3) || npix < 1) return 0;
+    i64 ncell = (dim == 2) ? npix * npix : npix * npix * npix;
+    return sorted_layout(nullptr, ncell << dim).total;
+}
+
+extern "C" int bf_grid_regrid_sorted(int dim, int64_t npix, const double *offsets, const double *orig, double *new_map,
+                                     void *ws, size_t ws_bytes, void *stream) {
+    BF_REQUIRE(dim == 2 || dim == 3, "dim must be 2 or 3");
+    BF_REQUIRE(npix >= 5 && offsets && orig && new_map, "npix >= 5 and non-null arrays");
+    i64 ncell = (dim == 2) ? npix * npix : npix * npix * npix;
+    BF_REQUIRE(ncell < 0xffffffffll, "grid too large for 32-bit destination keys");
+    i64 nent = ncell << dim;
+    sorted_ws w = sorted_layout(ws, nent);
+    if (!ws || ws_bytes < w.total) {
+        bf_set_error("bf_grid_regrid_sorted: workspace %zu < %zu bytes", ws_bytes, w.total);
+        return BF_E_WORKSPACE;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    unsigned blocks = (unsigned)((ncell + 255) / 256);
+    if (dim == 2) grid_emit_kernel<2><<<blocks, 256, 0, s>>>(npix, offsets, orig, w.k0, w.v0);
+    else grid_emit_kernel<3><<<blocks, 256, 0, s>>>(npix, offsets, orig, w.k0, w.v0);
+    BF_LAUNCH_OK();
+    return sort_and_reduce(w, nent, (u32)ncell, new_map, s);
+}

@@ -129,12 +129,22 @@ class ShellEngine:
         return self.npairs
 
     # ---- stage 3 (baryonify): re-binning ------------------------------------------------------------
-    def regrid(self, orig_d, off, new_d=None):
+    def regrid(self, orig_d, off, new_d=None, method="sorted"):
+        """orig_d / off are the engine's pixel slice; new_d is the full sphere.  method "sorted" = deterministic
+        sort-by-destination + in-order segmented sum (the reference's summation order); "atomic" = fp64 RED.ADD."""
         if new_d is None:
             new_d = dv.zeros(self.npix, dev=self.dev)
         else:
             new_d.zero_()
-        # orig_d / off are the engine's pixel slice; new_d is the full sphere
-        _lib.call("bf_shell_regrid_range", self.nside, self.pix_first, self.pix_last, dv.ptr(orig_d), dv.ptr(off),
-                  dv.ptr(new_d), dv.stream_ptr())
+        if method == "sorted":
+            need = self.lib.bf_shell_regrid_sorted_ws_bytes(self.nside, self.pix_last - self.pix_first)
+            if getattr(self, "_rg_ws", None) is None or self._rg_ws.numel() < need:
+                self._rg_ws = torch.empty(need, dtype=torch.uint8, device=self.dev)
+            _lib.call("bf_shell_regrid_sorted", self.nside, self.pix_first, self.pix_last, dv.ptr(orig_d), dv.ptr(off),
+                      dv.ptr(new_d), dv.ptr(self._rg_ws), self._rg_ws.numel(), dv.stream_ptr())
+        elif method == "atomic":
+            _lib.call("bf_shell_regrid_range", self.nside, self.pix_first, self.pix_last, dv.ptr(orig_d), dv.ptr(off),
+                      dv.ptr(new_d), dv.stream_ptr())
+        else:
+            raise ValueError(f"unknown regrid method {method!r}")
         return new_d

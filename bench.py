@@ -43,6 +43,8 @@ def parse():
     ap.add_argument("--nside", type=int, default=4096)
     ap.add_argument("--nhalo", type=int, default=1_000_000)
     ap.add_argument("--variant", default="gather", choices=["gather", "atomic"])
+    ap.add_argument("--regrid", default="sorted", choices=["sorted", "atomic"],
+                    help="re-binning: deterministic sort + in-order segmented sum (default) or fp64 atomics")
     ap.add_argument("--cpu-sample", type=int, default=10_000, help="halos in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
@@ -212,18 +214,22 @@ def run_ours(args, rank, local_rank, world):
     ev = lambda: torch.cuda.Event(enable_timing=True)
     acc_ms = []
 
+    rg_ms = []
+
     def step(timed):
         eng.recollapse()
         eng.bin()
-        a, b = ev(), ev()
+        a, b, c = ev(), ev(), ev()
         a.record()
         eng.accumulate(off)
         b.record()
-        eng.regrid(orig_d, off, new_d)
+        eng.regrid(orig_d, off, new_d, method=args.regrid)
+        c.record()
         if world > 1:
             dist.all_reduce(new_d)
         if timed:
             acc_ms.append((a, b))
+            rg_ms.append((b, c))
 
     def barrier():
         torch.cuda.synchronize(dev)
@@ -251,12 +257,25 @@ def run_ours(args, rank, local_rank, world):
     ms_step, ms_acc = float(ms[0]), float(ms[1])
     npairs = int(pairs[0])
     mass_err = abs(float(new_d.sum()) / float(orig_host.sum()) - 1.0)
+    ms_rg = float(np.mean([a.elapsed_time(b) for a, b in rg_ms]))
+    # the other re-binning variant, timed alongside (not part of `value`)
+    other = "atomic" if args.regrid == "sorted" else "sorted"
+    new_alt = dv.zeros(npix, dev=dev)
+    oa, ob = ev(), ev()
+    eng.regrid(orig_d, off, new_alt, method=other)
+    oa.record()
+    eng.regrid(orig_d, off, new_alt, method=other)
+    ob.record()
+    torch.cuda.synchronize(dev)
+    ms_rg_other = oa.elapsed_time(ob)
+    alt_diff = float((new_alt - new_d).abs().max() / new_d.abs().max()) if world == 1 else None
+    del new_alt
 
     # ---- e2e through the public API: host buffers in, host map out ---------------------------------------------
     e2e = None
     if not args.no_e2e and world == 1:
         runner = bf.BaryonifyShell(cfg["catalog"], cfg["field"], eps, cfg["model"], verbose=False, device=local_rank,
-                                   variant=args.variant)
+                                   variant=args.variant, regrid=args.regrid)
         runner.process()  # warm-up (page-in, allocator)
         ts = []
         for _ in range(max(1, min(args.steps, 3))):
@@ -301,12 +320,14 @@ def run_ours(args, rank, local_rank, world):
             "config": {"workload": f"BaryonifyShell NSIDE={nside}, {args.nhalo} halos, epsilon_max={eps:g}, table 10x10x500",
                        "variant": args.variant, "parallelism": f"ring-band x{world}", "pairs": npairs,
                        "l2": "working set (offsets 24 B/pixel + maps) far exceeds the 126 MB L2",
-                       "mass_conservation_relerr": mass_err, "bin_entries": eng.nentries},
+                       "mass_conservation_relerr": mass_err, "bin_entries": eng.nentries,
+                       "regrid": args.regrid, "regrid_ms": {args.regrid: ms_rg, other: ms_rg_other},
+                       "regrid_variants_max_reldiff": alt_diff},
             "roofline": {"bound": "hbm", "kernel": "gather_kernel<1>" if args.variant == "gather" else "shell_atomic_kernel<1>",
                          "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
                          "peak_source": peak_src, "algorithmic_bytes_per_pair": B_PAIR, "kernel_ms": ms_acc,
                          "note": "pairs are summed in registers: the kernel is fp64-issue bound, HBM traffic is one 24 B write per pixel"},
-            "e2e": e2e, "gpu_launches": 8 * args.steps, "clocks": clocks}
+            "e2e": e2e, "gpu_launches": (8 if args.regrid == "atomic" else 10) * args.steps, "clocks": clocks}
         if not args.no_cpu:
             cores = os.cpu_count() or 1
             cb = cpu_baseline(cfg, args, cores)

@@ -114,6 +114,14 @@ int bf_shell_regrid(int64_t nside, const double *orig_map, const double *pix_off
 int bf_shell_regrid_range(int64_t nside, int64_t pix_first, int64_t pix_last, const double *orig_map,
                           const double *pix_offsets, double *new_map, void *stream);
 
+/* Deterministic variant of the re-binning: every deposit is emitted as a (destination pixel, w * mass) entry,
+ * entries are radix-sorted by destination (stable, so a destination's entries stay in source order) and each
+ * segment is summed left to right -- the summation order of the reference's serial numba loop
+ * (regrid_pixels_hpix, HealpixRunner.py:13-67), bit-reproducible.  new_map is += (zero it first). */
+size_t bf_shell_regrid_sorted_ws_bytes(int64_t nside, int64_t npix_local);
+int bf_shell_regrid_sorted(int64_t nside, int64_t pix_first, int64_t pix_last, const double *orig_map,
+                           const double *pix_offsets, double *new_map, void *ws, size_t ws_bytes, void *stream);
+
 /* ---- Grid runners (Map2DRunner.py) ---- */
 typedef struct {
     const double *pos;       /* [nh][dim] halo x,y[,z] (float32 catalogue values widened) */
@@ -132,6 +140,11 @@ int bf_grid_paint_atomic(int dim, int64_t npix, const double *bins, double res, 
                          const bf_table *tab_host, double *out, unsigned long long *npairs, void *stream);
 /* BaryonifyGrid tail (:583-607 + regrid_pixels_2D/3D :14-163): CIC-equivalent periodic deposit. */
 int bf_grid_regrid(int dim, int64_t npix, const double *offsets, const double *orig, double *new_map, void *stream);
+
+/* deterministic (sort-by-cell + in-order segmented sum) variant; new_map is += */
+size_t bf_grid_regrid_sorted_ws_bytes(int dim, int64_t npix);
+int bf_grid_regrid_sorted(int dim, int64_t npix, const double *offsets, const double *orig, double *new_map, void *ws,
+                          size_t ws_bytes, void *stream);
 
 /* ---- Snapshot runner (SnapshotRunner.py) ---- */
 typedef struct {
