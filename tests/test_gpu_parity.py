@@ -292,7 +292,10 @@ def test_shell_regrid_sorted_equals_serial_order_sum(gpu):
         for j in range(4):
             want[ip[i, j]] += iw[i, j] * orig[i]
     got = new.cpu().numpy()
-    assert np.allclose(got, want, rtol=1e-13, atol=0)
+    # numpy's arccos / arctan2 and CUDA's differ by <= 2 ulp in the displaced angles; an interpolation weight
+    # w = (phi - phi_i) / dphi close to 0 turns that into a large RELATIVE change of one tiny deposit, so the
+    # comparison is relative to the map scale (the deposits' absolute error is ~1e-16 * nside * mass)
+    assert np.max(np.abs(got - want)) < 1e-12 * np.max(want)
     # bit-exact wherever the device's own displaced angles agree with numpy's to the last bit (most pixels)
     assert np.mean(got == want) > 0.5
 
