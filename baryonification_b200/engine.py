@@ -18,25 +18,6 @@ from .tables import HostTable
 PAINT, BARYONIFY = 0, 1
 
 
-def estimate_entries(nside, radius, vec_z, band_frac=1.0):
-    """Conservative host estimate of the number of (cell, halo) entries the binning stage will emit."""
-    lib = _lib.load()
-    nb = lib.bf_shell_num_bands(nside)
-    nrmax = 4 * nside
-    cw = max(1, -(-nrmax // (64 * 32)))
-    wc = 32 * cw
-    ncol = -(-nrmax // wc)
-    r = np.minimum(np.asarray(radius, dtype=np.float64), np.pi)
-    theta = np.arccos(np.clip(vec_z, -1, 1))
-    nbands = np.minimum(np.ceil(2 * r * nside / 0.66 / 8) + 2, nb)
-    st = np.maximum(np.minimum(np.sin(np.clip(theta - r, 0, np.pi)), np.sin(np.clip(theta + r, 0, np.pi))), 0.0)
-    polar = (theta - r <= 0) | (theta + r >= np.pi)
-    with np.errstate(divide="ignore", invalid="ignore"):
-        half = np.where(polar | (st <= np.sin(r)), np.pi, np.arcsin(np.clip(np.sin(r) / np.maximum(st, 1e-300), 0, 1)))
-    ncols = np.minimum(np.ceil(2 * half * nrmax / (2 * np.pi) / wc) + 2, ncol)
-    return int(np.sum(nbands * ncols) * 1.05 * band_frac) + 1024
-
-
 class ShellEngine:
     def __init__(self, nside, mode, table: HostTable, scalars: dict, dev, variant="gather", bands=None):
         self.nside, self.mode, self.dev, self.variant = int(nside), int(mode), dev, variant
@@ -80,20 +61,21 @@ class ShellEngine:
     def bin(self):
         if self.variant != "gather":
             return self
-        nb = self.lib.bf_shell_num_bands(self.nside)
+        # first call: a counting pass with a key-less workspace returns the exact number of (cell, halo) entries
+        # (BF_E_WORKSPACE + *nentries_host), the second call is sized for it; later calls reuse the workspace
         if self.ws is None:
-            frac = min(1.0, (self.bands[1] - self.bands[0]) / nb * 1.5 + 0.05) if nb else 1.0
-            self.max_entries = min(estimate_entries(self.nside, self.s["radius"], self.s["vec"][:, 2], frac), 2 ** 31 - 2)
+            self.max_entries = 0
         for _ in range(2):
             need = self.lib.bf_shell_bin_ws_bytes(self.nside, self.nh, self.max_entries)
             if self.ws is None or self.ws.numel() < need:
+                self.ws = None
                 self.ws = torch.empty(need, dtype=torch.uint8, device=self.dev)
             n = C.c_int64()
             rc = self.lib.bf_shell_bin_halos(self.nside, self.mode, C.byref(self.desc), self.bands[0], self.bands[1],
                                              self.max_entries, dv.ptr(self.ws), self.ws.numel(), C.byref(n),
                                              dv.stream_ptr())
-            if rc == -2 and n.value > self.max_entries:  # BF_E_WORKSPACE: grow once to the exact count
-                self.max_entries, self.ws = n.value + 1024, None
+            if rc == -2 and n.value > self.max_entries:  # BF_E_WORKSPACE: grow to the exact count
+                self.max_entries = n.value
                 continue
             _lib.check(rc, "bf_shell_bin_halos")
             self.nentries = n.value

@@ -9,10 +9,55 @@ device as float64 arrays.  Table construction and cosmology stay on the host, as
 """
 from __future__ import annotations
 
+import os
+from concurrent.futures import ThreadPoolExecutor
+
 import numpy as np
 from scipy import interpolate
 
 from ._ccl import get_ccl
+
+# Chunks of the catalogue are set up by a thread pool: numpy ufuncs and scipy's spline evaluation release the GIL,
+# every expression is element-wise over halos, so the result is bit-identical to the serial evaluation.
+_PAR_MIN = 100_000
+_pool = None
+
+
+def _threads():
+    env = os.environ.get("BF_HOST_THREADS")
+    if env:
+        return max(1, int(env))
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    return max(1, min(16, n))
+
+
+def spline_eval(cs, x):
+    """``cs(x)`` of a scipy CubicSpline in numpy, bit-identical to scipy's evaluation (same interval rule, same
+    power-accumulation order c3 + c2 s + c1 s^2 + c0 s^3 with s^3 = (s s) s) but free of the GIL, so catalogue chunks
+    evaluate in parallel.  Checked against scipy in tests/test_host.py."""
+    xb, c = cs.x, cs.c
+    i = np.clip(np.searchsorted(xb, x, side="right") - 1, 0, xb.size - 2)
+    s = x - xb[i]
+    res = c[3, i] + c[2, i] * s
+    s2 = s * s
+    res = res + c[1, i] * s2
+    return res + c[0, i] * (s2 * s)
+
+
+def chunked(fn, n):
+    """Evaluate ``fn(slice) -> dict of arrays`` over [0, n) in parallel chunks and concatenate along axis 0."""
+    global _pool
+    nt = _threads()
+    if n < _PAR_MIN or nt == 1:
+        return fn(slice(0, n))
+    if _pool is None:
+        _pool = ThreadPoolExecutor(max_workers=nt, thread_name_prefix="bf-host")
+    edges = np.linspace(0, n, nt + 1).astype(np.int64)
+    parts = list(_pool.map(fn, [slice(int(edges[i]), int(edges[i + 1])) for i in range(nt)]))
+    return {k: np.concatenate([p[k] for p in parts], axis=0) for k in parts[0]}
 
 
 def runner_cosmology(cosmo: dict, with_w0: bool):
@@ -73,15 +118,24 @@ def shell_scalars(catalog, cosmo_dict, mass_def, epsilon_max, model, baryonify: 
     z_t = np.linspace(0, 30, 1000)  # HealpixRunner.py:279-280
     D_a = interpolate.CubicSpline(z_t, ccl.angular_diameter_distance(cosmo, 1 / (1 + z_t)))
     cat = catalog.cat
-    M, z = cat["M"], cat["z"]
-    a = 1 / (1 + z)
-    R = radius_of(mass_def, cosmo, M, a)
-    D = D_a(z)
-    out = dict(a=a, D=D, radius=R * epsilon_max / D, z_in=np.log(1 / a), M_in=log_native(M),
-               lon=np.asarray(cat["ra"], dtype=np.float64), lat=np.asarray(cat["dec"], dtype=np.float64))
-    out["vec"] = ang2vec_lonlat(out["lon"], out["lat"])
-    out["cut"], out["lnr_shift"] = model_cut(model, M, a, need_cut=baryonify)
-    return out
+    if len(cat) > 0:  # force the back-end's lazy initialisation before threads share the cosmology objects
+        mass_def.get_radius(cosmo, float(cat["M"][0]), 1.0)
+        if baryonify:
+            model.mass_def.get_radius(model.cosmo, float(cat["M"][0]), 1.0)
+
+    def part(sl):
+        c = cat[sl]
+        M, z = c["M"], c["z"]
+        a = 1 / (1 + z)
+        R = radius_of(mass_def, cosmo, M, a)
+        D = spline_eval(D_a, np.asarray(z, dtype=np.float64))
+        out = dict(a=a, D=D, radius=R * epsilon_max / D, z_in=np.log(1 / a), M_in=log_native(M),
+                   lon=np.asarray(c["ra"], dtype=np.float64), lat=np.asarray(c["dec"], dtype=np.float64))
+        out["vec"] = ang2vec_lonlat(out["lon"], out["lat"])
+        out["cut"], out["lnr_shift"] = model_cut(model, M, a, need_cut=baryonify)
+        return out
+
+    return chunked(part, len(cat))
 
 
 def nd_positions(cat, dim):

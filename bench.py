@@ -276,7 +276,8 @@ def run_ours(args, rank, local_rank, world):
     if not args.no_e2e and world == 1:
         runner = bf.BaryonifyShell(cfg["catalog"], cfg["field"], eps, cfg["model"], verbose=False, device=local_rank,
                                    variant=args.variant, regrid=args.regrid)
-        runner.process()  # warm-up (page-in, allocator)
+        for _ in range(max(2, min(args.warmup, 3))):  # warm-up: page-in, pinned staging buffers, allocator
+            runner.process()
         ts = []
         for _ in range(max(1, min(args.steps, 3))):
             t0 = time.perf_counter()

@@ -122,3 +122,20 @@ def test_runner_constructor_contract():
         bf.BaryonifyShell(cfg["catalog"], cfg["field"], 20.0, cfg["model"], True)
     import pickle
     pickle.loads(pickle.dumps(r))  # runners stay picklable (joblib/loky), no live CUDA handles on self
+
+
+def test_spline_eval_is_bit_identical_to_scipy_and_chunked_setup_to_serial(monkeypatch):
+    from scipy import interpolate
+    z_t = np.linspace(0, 30, 1000)
+    cs = interpolate.CubicSpline(z_t, np.sqrt(z_t + 0.3) * 1000 / (1 + z_t))
+    rng = np.random.default_rng(5)
+    x = np.concatenate([rng.uniform(0, 30, 200_000), z_t, [0.0, 30.0, 31.0, -0.5]])
+    assert np.array_equal(host.spline_eval(cs, x), cs(x))
+    cfg = syn.config_shell(nside=8, nhalo=3000)
+    args = (cfg["catalog"], cfg["catalog"].cosmo, default_mass_def(), 20.0, cfg["model"], True)
+    serial = host.shell_scalars(*args)
+    monkeypatch.setattr(host, "_PAR_MIN", 100)
+    monkeypatch.setenv("BF_HOST_THREADS", "4")
+    par = host.shell_scalars(*args)
+    for k, v in serial.items():
+        assert np.array_equal(v, par[k]) and par[k].flags.c_contiguous, k
