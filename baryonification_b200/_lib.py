@@ -76,10 +76,14 @@ _SIGS = {
     "bf_grid_regrid": (C.c_int, [C.c_int, _i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p]),
     "bf_grid_regrid_sorted_ws_bytes": (C.c_size_t, [C.c_int, _i64]),
     "bf_grid_regrid_sorted": (C.c_int, [C.c_int, _i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p, C.c_size_t, C.c_void_p]),
-    "bf_snap_ws_bytes": (C.c_size_t, [C.c_int, _i64, C.c_double, C.c_double]),
+    "bf_snap_grid_cells": (_i64, [C.c_int, C.c_double, C.c_double]),
+    "bf_snap_ws_bytes": (C.c_size_t, [C.c_int, _i64, C.c_double, _i64, _i64]),
+    "bf_snap_bin_halos": (C.c_int, [C.c_int, C.c_double, _i64, _P(SnapHalos), _i64, C.c_void_p, C.c_size_t, _P(_i64),
+                                    C.c_void_p]),
     "bf_snap_displace": (C.c_int, [C.c_int, _i64, _dbl_p, _dbl_p, _dbl_p, C.c_double, C.c_double, _P(SnapHalos),
-                                   _P(Table), C.c_double, _dbl_p, _dbl_p, _dbl_p, _dbl_p, C.c_void_p, C.c_size_t,
-                                   C.c_void_p]),
+                                   _P(Table), _i64, C.c_void_p, _dbl_p, _dbl_p, _dbl_p, _dbl_p, C.c_void_p]),
+    "bf_snap_displace_records": (C.c_int, [C.c_int, _i64, C.c_void_p, C.c_double, C.c_double, _P(SnapHalos), _P(Table),
+                                           _i64, C.c_void_p, C.c_void_p, _dbl_p, C.c_void_p]),
 }
 
 EXPORTED = tuple(_SIGS)

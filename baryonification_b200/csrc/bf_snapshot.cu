@@ -2,74 +2,174 @@
 //
 // Replaces BaryonifySnapshot (Runners/SnapshotRunner.py): the periodic KD-tree build (:92-97), the per-halo
 // query_ball_point + displacement loop (:205-247) and the apply / wrap pass (:250-260).
-// Instead of "for each halo: find its particles, scatter-add", every particle looks up the halos whose
-// query ball can reach it: halos are binned into a periodic cell list with cell size >= max R_q, so the
-// 3^D neighbouring cells hold every candidate; membership is the KD-tree's own criterion (minimum-image
-// distance^2 <= R_q^2).  Contributions are summed in registers in a fixed order (cell order, then
-// catalogue order inside a cell): no atomics, bit-reproducible, one coalesced read and one coalesced
-// write per particle coordinate -- the streaming HBM bound of SURVEY.md section 8d (88 B / particle).
+//
+// Instead of "for each halo: find its particles, scatter-add", every particle looks up the halos whose query
+// ball can reach it.  Halos are binned into a FINE periodic grid (cell ~ one mean query radius): a halo is
+// listed in every cell its ball overlaps (halo binning into grid tiles, north_star kernel work (1)), the
+// (cell, halo) keys are radix-sorted by cell so that each cell's list is contiguous and in catalogue order.
+// A particle then reads ONE cell list (most are empty: query balls cover a few per cent of the box) and tests
+// membership with the KD-tree's own criterion (minimum-image distance^2 <= R_q^2).
+//
+// The particle kernel works in three block-wide phases so that the expensive part (sqrt, log, table lerp,
+// divisions) runs with full lanes although only ~1 particle in 10 has a pair:
+//   1. every thread counts the halos that reach its particle;            (cheap, one 32 B halo record per test)
+//   2. a block scan gives every hit a slot in a shared-memory queue, a second pass over the candidates fills it;
+//   3. the queue is evaluated densely (thread q evaluates pair q), results go to shared memory and every
+//      thread adds ITS pairs in slot order = catalogue order: the reference's summation order
+//      (tot_offsets[inds] += ... for j in range(N_halo)), no atomics, bit-reproducible.
+// HBM traffic: one coalesced read and one coalesced write of the particle records (32 B each way for the
+// reference's (M, x, y, z) float64 records, SURVEY.md section 8d counts 88 B / particle for the reference's
+// separate offsets array).
+#include <cub/cub.cuh>
+
 #include "bf_common.cuh"
 
 #define SN_THREADS 256
+#define SN_WQ 1024
+#define SN_NG_MAX_3D 256
+#define SN_NG_MAX_2D 4096
 
-struct snap_cells {
-    int ng, ncell, dim;
-    double inv_cs;  // ng / L
+struct snap_grid {
+    int ng, dim;
+    i64 ncell;
+    double inv_cs, cs, L;
 };
 
-__device__ __forceinline__ int cell_coord(double x, const snap_cells &C) {
-    int g = (int)floor(x * C.inv_cs);
-    return max(0, min(g, C.ng - 1));
+static snap_grid make_grid(int dim, double L, i64 ng) {
+    snap_grid G;
+    G.dim = dim;
+    G.ng = (int)ng;
+    G.ncell = (dim == 3) ? ng * ng * ng : ng * ng;
+    G.inv_cs = (double)ng / L;
+    G.cs = L / (double)ng;
+    G.L = L;
+    return G;
 }
 
-__global__ void snap_count_kernel(snap_cells C, i64 nh, const double *__restrict__ pos, int *__restrict__ count) {
-    i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= nh) return;
-    int c = 0;
-    for (int m = 0; m < C.dim; ++m) c = c * C.ng + cell_coord(pos[C.dim * j + m], C);
-    atomicAdd(count + c, 1);
+__device__ __forceinline__ int snap_cell_coord(double x, const snap_grid &G) {
+    int g = (int)floor(x * G.inv_cs) % G.ng;  // x = L (allowed by the single wrap, :259-260) lands in cell 0
+    return (g < 0) ? g + G.ng : g;
 }
 
-// exclusive scan of count[0..n) into start[0..n], single block
-__global__ void __launch_bounds__(1024) snap_scan_kernel(int n, const int *__restrict__ count, int *__restrict__ start) {
-    __shared__ int part[1024];
-    int t = threadIdx.x, per = (n + 1023) / 1024;
-    int b = t * per, e = min(n, b + per), s = 0;
-    for (int i = b; i < e; ++i) s += count[i];
-    part[t] = s;
-    __syncthreads();
-    for (int d = 1; d < 1024; d <<= 1) {
-        int add = (t >= d) ? part[t - d] : 0;
-        __syncthreads();
-        part[t] += add;
-        __syncthreads();
+struct snap_hdr {  // first 256 bytes of the workspace, written by bf_snap_bin_halos, read by the particle kernel
+    const int *entj;  // [nentries] halo index of every (cell, halo) entry, cell-sorted, catalogue order inside a cell
+};
+
+struct snap_ws {
+    snap_hdr *hdr;
+    i64 *counts, *offsets;
+    int *cell_start;   // [ncell + 1] entries [start[c], start[c+1]) belong to cell c
+    double4 *hrec;     // [nh] (x, y, z, R_q): one 32-byte sector per membership test, L2-resident (3.2 MB at 1e5 halos)
+    u64 *keys, *keys_alt;
+    int *entj;
+    void *cub_tmp;
+    size_t cub_bytes, total;
+};
+
+static size_t sn_al256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+static snap_ws snap_layout(void *base, const snap_grid &G, i64 nh, i64 max_entries) {
+    snap_ws w;
+    char *p = (char *)base;
+    size_t o = 0;
+    w.hdr = (snap_hdr *)(p + o);     o += 256;
+    w.counts = (i64 *)(p + o);       o += sn_al256(sizeof(i64) * (size_t)(nh + 1));
+    w.offsets = (i64 *)(p + o);      o += sn_al256(sizeof(i64) * (size_t)(nh + 2));
+    w.cell_start = (int *)(p + o);   o += sn_al256(sizeof(int) * (size_t)(G.ncell + 1));
+    w.hrec = (double4 *)(p + o);     o += sn_al256(sizeof(double4) * (size_t)(nh + 1));
+    w.keys = (u64 *)(p + o);         o += sn_al256(sizeof(u64) * (size_t)(max_entries + 1));
+    w.keys_alt = (u64 *)(p + o);     o += sn_al256(sizeof(u64) * (size_t)(max_entries + 1));
+    w.entj = (int *)(p + o);         o += sn_al256(sizeof(int) * (size_t)(max_entries + 1));
+    size_t a = 0, b = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, a, (i64 *)nullptr, (i64 *)nullptr, (int)(nh + 1));
+    cub::DoubleBuffer<u64> db(nullptr, nullptr);
+    cub::DeviceRadixSort::SortKeys(nullptr, b, db, (int)(max_entries > 0 ? max_entries : 1), 0, 64);
+    w.cub_bytes = (a > b ? a : b) + 256;
+    w.cub_tmp = (void *)(p + o);     o += sn_al256(w.cub_bytes);
+    w.total = o;
+    return w;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// halo binning: one warp per halo enumerates the cells of its ball's bounding box (unwrapped indices), keeps
+// those whose box is within R_q of the centre (slightly inflated: the test must never drop a cell that holds
+// a particle the exact membership test would accept) and emits (cell << 32 | halo).
+// ---------------------------------------------------------------------------------------------------
+template <int DIM, bool FILL>
+__global__ void __launch_bounds__(128) snap_bin_kernel(snap_grid G, bf_snap_halos H, i64 *__restrict__ counts,
+                                                       const i64 *__restrict__ offsets, u64 *__restrict__ keys,
+                                                       double4 *__restrict__ hrec) {
+    i64 j = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (j >= H.nh) return;
+    double p[3] = {H.pos[DIM * j], H.pos[DIM * j + 1], (DIM == 3) ? H.pos[DIM * j + 2] : 0.0};
+    double R = H.Rq[j];
+    if (!FILL && lane == 0) hrec[j] = make_double4(p[0], p[1], p[2], R);
+    if (!(R >= 0.0)) { if (!FILL && lane == 0) counts[j] = 0; return; }  // NaN / negative radius: no particles
+    i64 lo[3] = {0, 0, 0}, n[3] = {1, 1, 1};
+    bool full[3] = {false, false, false};
+#pragma unroll
+    for (int m = 0; m < DIM; ++m) {
+        i64 g0 = (i64)floor((p[m] - R) * G.inv_cs - 1e-9);
+        i64 g1 = (i64)floor((p[m] + R) * G.inv_cs + 1e-9);
+        lo[m] = g0;
+        n[m] = g1 - g0 + 1;
+        if (n[m] >= G.ng) { lo[m] = 0; n[m] = G.ng; full[m] = true; }
     }
-    int run = part[t] - s;
-    for (int i = b; i < e; ++i) { start[i] = run; run += count[i]; }
-    if (t == 1023) start[n] = part[1023];
-}
-
-__global__ void snap_fill_kernel(snap_cells C, i64 nh, const double *__restrict__ pos, const int *__restrict__ start,
-                                 int *__restrict__ cursor, int *__restrict__ list) {
-    i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= nh) return;
-    int c = 0;
-    for (int m = 0; m < C.dim; ++m) c = c * C.ng + cell_coord(pos[C.dim * j + m], C);
-    list[start[c] + atomicAdd(cursor + c, 1)] = (int)j;
-}
-
-// catalogue order inside each cell (makes the summation order independent of the atomics above)
-__global__ void snap_sort_kernel(int ncell, const int *__restrict__ start, int *__restrict__ list) {
-    int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= ncell) return;
-    int b = start[c], e = start[c + 1];
-    for (int i = b + 1; i < e; ++i) {
-        int v = list[i], k = i - 1;
-        while (k >= b && list[k] > v) { list[k + 1] = list[k]; --k; }
-        list[k + 1] = v;
+    const i64 nbox = n[0] * n[1] * n[2];
+    const double R2 = R * R * (1.0 + 1e-9) + 1e-300;
+    i64 total = 0;
+    const i64 base = FILL ? offsets[j] : 0;
+    for (i64 b0 = 0; b0 < nbox; b0 += 32) {
+        i64 idx = b0 + lane;
+        bool hit = false;
+        i64 cell = 0;
+        if (idx < nbox) {
+            i64 i0 = idx / (n[1] * n[2]), rem = idx - i0 * (n[1] * n[2]);
+            i64 i1 = rem / n[2], i2 = rem - i1 * n[2];
+            i64 u[3] = {lo[0] + i0, lo[1] + i1, lo[2] + i2};
+            double dsq = 0.0;
+#pragma unroll
+            for (int m = 0; m < DIM; ++m) {
+                if (!full[m]) {
+                    double a = (double)u[m] * G.cs - p[m], b = p[m] - (double)(u[m] + 1) * G.cs;
+                    double d = fmax(0.0, fmax(a, b)) - 1e-9 * G.cs;
+                    if (d > 0.0) dsq += d * d;
+                }
+                i64 g = u[m] % G.ng;
+                if (g < 0) g += G.ng;
+                cell = cell * G.ng + g;
+            }
+            hit = dsq <= R2;
+        }
+        unsigned bal = __ballot_sync(0xffffffffu, hit);
+        if (FILL && hit) keys[base + total + __popc(bal & ((1u << lane) - 1u))] = ((u64)cell << 32) | (u64)j;
+        total += __popc(bal);
     }
+    if (!FILL && lane == 0) counts[j] = total;
 }
 
+// after the sort: cell_start[c] = first entry of cell c (empty cells included), entj = halo index per entry.
+// The tables a particle touches at random (cell_start 4 B/cell, entj 4 B/entry, hrec 32 B/halo) are kept small so
+// that they stay L2-resident while the particle records stream through with evict-first hints.
+__global__ void snap_entries_kernel(i64 n, i64 ncell, const u64 *__restrict__ keys, int *__restrict__ cell_start,
+                                    int *__restrict__ entj) {
+    i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    u64 k = keys[i];
+    i64 c = (i64)(k >> 32);
+    i64 pc = (i == 0) ? -1 : (i64)(keys[i - 1] >> 32);
+    for (i64 cc = pc + 1; cc <= c; ++cc) cell_start[cc] = (int)i;
+    if (i == n - 1)
+        for (i64 cc = c + 1; cc <= ncell; ++cc) cell_start[cc] = (int)n;
+    entj[i] = (int)(k & 0xffffffffull);
+}
+
+__global__ void snap_hdr_kernel(snap_hdr *hdr, const int *entj) { hdr->entj = entj; }
+
+// ---------------------------------------------------------------------------------------------------
+// particle kernel
+// ---------------------------------------------------------------------------------------------------
 __device__ __forceinline__ double wrap_half(double dx, double L) {  // :124-125, :152-153
     if (dx > L / 2) dx = dx - L;
     if (dx < -L / 2) dx = dx + L;
@@ -82,115 +182,315 @@ __device__ __forceinline__ double wrap_box(double v, double L) {  // :259-260
     return v;
 }
 
+#ifndef SN_PPT
+#define SN_PPT 2
+#endif
+// particles per thread: independent loads in flight hide the record -> cell -> entry latency chain
+#define SN_TILE (SN_THREADS * SN_PPT)
+#ifndef SN_MINBLOCKS
+#define SN_MINBLOCKS 4
+#endif
+
+struct snap_args {
+    snap_grid G;
+    i64 np;
+    const double *x, *y, *z;  // SoA input (REC = false)
+    double *xo, *yo, *zo;
+    const double4 *rec;       // (M, x, y, z) records (REC = true)
+    double4 *rec_out;
+    double a;
+    bf_snap_halos H;
+    bf_raxis ax;
+    const int *cell_start;
+    const double4 *hrec;
+    const snap_hdr *hdr;
+    u64 *npairs;
+};
+
+struct __align__(16) snap_q {  // one queued pair: min-image separation in, displacement vector out (in place)
+    double v[3];
+    int j, src;
+};
+
+#define SN_WQ 64  // queue slots per warp (a warp owns 32 * SN_PPT particles, ~0.1 pairs each on a uniform box)
+
+struct snap_smem {
+    snap_q q[SN_THREADS / 32][SN_WQ];
+};
+
+__device__ __forceinline__ double4 ldg_rec(const double4 *p) {  // one 32-byte sector through the read-only path
+    const double2 *q = reinterpret_cast<const double2 *>(p);
+    double2 a = __ldg(q), b = __ldg(q + 1);
+    return make_double4(a.x, a.y, b.x, b.y);
+}
+
 template <int DIM>
-__global__ void __launch_bounds__(SN_THREADS) snap_gather_kernel(
-    snap_cells C, i64 np, const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ z,
-    double L, double a, bf_snap_halos H, bf_raxis ax, const int *__restrict__ start, const int *__restrict__ list,
-    double *__restrict__ xo, double *__restrict__ yo, double *__restrict__ zo, u64 *npairs) {
-    i64 p = (i64)blockIdx.x * blockDim.x + threadIdx.x;
-    u64 my_pairs = 0;
-    if (p < np) {
-        double P[3] = {x[p], y[p], (DIM == 3) ? z[p] : 0.0};
-        int g[3] = {cell_coord(P[0], C), cell_coord(P[1], C), (DIM == 3) ? cell_coord(P[2], C) : 0};
-        double tot[3] = {0.0, 0.0, 0.0};
-        const int span = (C.ng >= 3) ? 3 : C.ng;  // ng < 3: visit every cell once instead of +-1 with repeats
-        for (int ia = 0; ia < span; ++ia)
-            for (int ib = 0; ib < span; ++ib)
-                for (int ic = 0; ic < ((DIM == 3) ? span : 1); ++ic) {
-                    int ca = (C.ng >= 3) ? (g[0] + ia - 1 + C.ng) % C.ng : ia;
-                    int cb = (C.ng >= 3) ? (g[1] + ib - 1 + C.ng) % C.ng : ib;
-                    int cc = (DIM == 3) ? ((C.ng >= 3) ? (g[2] + ic - 1 + C.ng) % C.ng : ic) : 0;
-                    int cell = (DIM == 3) ? (ca * C.ng + cb) * C.ng + cc : ca * C.ng + cb;
-                    for (int s = start[cell]; s < start[cell + 1]; ++s) {
-                        int j = list[s];
-                        double dx[3] = {0, 0, 0}, dsq = 0.0;
+__device__ __forceinline__ bool snap_member(const double P[3], const double4 h, double L, double dx[3]) {
+    dx[0] = wrap_half(P[0] - h.x, L);  // :235-238
+    dx[1] = wrap_half(P[1] - h.y, L);
+    double dsq = dx[0] * dx[0] + dx[1] * dx[1];
+    dx[2] = 0.0;
+    if (DIM == 3) { dx[2] = wrap_half(P[2] - h.z, L); dsq += dx[2] * dx[2]; }
+    return dsq <= h.w * h.w;  // query_ball_point (:219 / :234)
+}
+
+template <int DIM, bool REC>
+__global__ void __launch_bounds__(SN_THREADS, SN_MINBLOCKS) snap_gather_kernel(snap_args A) {
+    __shared__ snap_smem sm;
+    const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
+    const i64 tile = (i64)blockIdx.x * SN_TILE + (i64)wid * (32 * SN_PPT);  // this WARP's particles
+    snap_q *__restrict__ wq = sm.q[wid];
+    const double L = A.G.L;
+    const int *__restrict__ entj = A.hdr->entj;
+    double P[SN_PPT][3], M[SN_PPT];
+    int beg[SN_PPT], cnt[SN_PPT], num[SN_PPT];
 #pragma unroll
-                        for (int m = 0; m < DIM; ++m) {
-                            dx[m] = wrap_half(P[m] - H.pos[DIM * j + m], L);  // :235-238
-                            dsq += dx[m] * dx[m];
+    for (int i = 0; i < SN_PPT; ++i) {
+        const i64 p = tile + i * 32 + lane;
+        P[i][0] = P[i][1] = P[i][2] = 0.0; M[i] = 0.0;
+        if (p < A.np) {
+            if (REC) {
+                const double2 *r = reinterpret_cast<const double2 *>(A.rec + p);
+                double2 r0 = __ldcs(r), r1 = __ldcs(r + 1);  // streamed once: evict-first, keep L2 for the tables
+                M[i] = r0.x; P[i][0] = r0.y; P[i][1] = r1.x; P[i][2] = r1.y;
+            } else {
+                P[i][0] = __ldcs(A.x + p); P[i][1] = __ldcs(A.y + p);
+                if (DIM == 3) P[i][2] = __ldcs(A.z + p);
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < SN_PPT; ++i) {
+        const i64 p = tile + i * 32 + lane;
+        beg[i] = 0; num[i] = 0;
+        if (p < A.np) {
+            int c = snap_cell_coord(P[i][0], A.G) * A.G.ng + snap_cell_coord(P[i][1], A.G);
+            if (DIM == 3) c = c * A.G.ng + snap_cell_coord(P[i][2], A.G);
+            beg[i] = __ldg(A.cell_start + c);
+            num[i] = __ldg(A.cell_start + c + 1) - beg[i];
+        }
+    }
+    // phase 1: count the halos that reach each particle
+    int mine = 0;
+    int smax = 0;
+#pragma unroll
+    for (int i = 0; i < SN_PPT; ++i) { cnt[i] = 0; smax = max(smax, num[i]); }
+    for (int s = 0; s < smax; ++s) {  // the SN_PPT lists advance together: independent 32-byte loads in flight
+#pragma unroll
+        for (int i = 0; i < SN_PPT; ++i)
+            if (s < num[i]) {
+                double dx[3];
+                cnt[i] += snap_member<DIM>(P[i], ldg_rec(A.hrec + __ldg(entj + beg[i] + s)), L, dx) ? 1 : 0;
+            }
+    }
+#pragma unroll
+    for (int i = 0; i < SN_PPT; ++i) mine += cnt[i];
+    // warp exclusive scan of the per-lane totals: warps never wait for each other (no block barrier anywhere)
+    int inc = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        int v = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += v;
+    }
+    const int base = inc - mine, nq = __shfl_sync(0xffffffffu, inc, 31);
+    double tot[SN_PPT][3];
+#pragma unroll
+    for (int i = 0; i < SN_PPT; ++i) tot[i][0] = tot[i][1] = tot[i][2] = 0.0;
+
+    for (int r0 = 0; r0 < nq; r0 += SN_WQ) {  // one round unless > SN_WQ pairs fall into this tile
+        // phase 2: fill this thread's queue slots [base, base + mine) that fall into the round
+        if (mine > 0 && base < r0 + SN_WQ && base + mine > r0) {
+            int k = base;
+#pragma unroll
+            for (int i = 0; i < SN_PPT; ++i) {
+                if (cnt[i] == 0) continue;
+                for (int s = 0; s < num[i]; ++s) {
+                    double dx[3];
+                    const int j = __ldg(entj + beg[i] + s);
+                    if (snap_member<DIM>(P[i], ldg_rec(A.hrec + j), L, dx)) {
+                        if (k >= r0 && k < r0 + SN_WQ) {
+                            snap_q &e = wq[k - r0];
+                            e.v[0] = dx[0]; e.v[1] = dx[1]; e.v[2] = dx[2];
+                            e.j = j;
+                            e.src = i * 32 + lane;
                         }
-                        double R = H.Rq[j];
-                        if (!(dsq <= R * R)) continue;  // query_ball_point (:219 / :234)
-                        double d = sqrt(dsq);
-                        double v = bf_row_lerp(ax, H.rows + (i64)j * ax.nr, log(d) - H.lnr_shift[j]);
-                        v = (d < H.cut[j]) ? v : 0.0;  // BaryonCorrection.py:381-382
-                        double off = v * a;            // :228 / :245  (x a_j, reproduced as is)
-                        if (!bf_finite(off)) off = 0.0;
-#pragma unroll
-                        for (int m = 0; m < DIM; ++m) tot[m] += off * (dx[m] / d);  // :247 (0/0 -> NaN kept)
-                        ++my_pairs;
+                        ++k;
                     }
                 }
-        xo[p] = wrap_box(P[0] + tot[0], L);
-        yo[p] = wrap_box(P[1] + tot[1], L);
-        if (DIM == 3) zo[p] = wrap_box(P[2] + tot[2], L);
+            }
+        }
+        __syncwarp();
+        // phase 3: dense evaluation, thread q evaluates pair q
+        const int nround = min(SN_WQ, nq - r0);
+        for (int q = lane; q < nround; q += 32) {
+            snap_q &e = wq[q];
+            const int j = e.j;
+            double dx[3] = {e.v[0], e.v[1], e.v[2]};
+            double dsq = dx[0] * dx[0] + dx[1] * dx[1];
+            if (DIM == 3) dsq += dx[2] * dx[2];
+            double d = sqrt(dsq);
+            double v = bf_row_lerp(A.ax, A.H.rows + (i64)j * A.ax.nr, log(d) - A.H.lnr_shift[j]);
+            v = (d < A.H.cut[j]) ? v : 0.0;  // BaryonCorrection.py:381-382
+            double off = v * A.a;            // :228 / :245  (x a_j, reproduced as is)
+            if (!bf_finite(off)) off = 0.0;
+#pragma unroll
+            for (int m = 0; m < 3; ++m) e.v[m] = (m < DIM) ? off * (dx[m] / d) : 0.0;  // :247 (0/0 -> NaN kept)
+        }
+        __syncwarp();
+        // every particle adds its own pairs in catalogue order
+        int k = base;
+#pragma unroll
+        for (int i = 0; i < SN_PPT; ++i) {
+            const int k0 = max(k, r0), k1 = min(k + cnt[i], r0 + SN_WQ);
+            for (int kk = k0; kk < k1; ++kk) {
+                tot[i][0] += wq[kk - r0].v[0];
+                tot[i][1] += wq[kk - r0].v[1];
+                if (DIM == 3) tot[i][2] += wq[kk - r0].v[2];
+            }
+            k += cnt[i];
+        }
+        __syncwarp();
     }
-    for (int s = 16; s > 0; s >>= 1) my_pairs += __shfl_down_sync(0xffffffffu, my_pairs, s);
-    if ((threadIdx.x & 31) == 0 && npairs && my_pairs) atomicAdd(npairs, my_pairs);
+#pragma unroll
+    for (int i = 0; i < SN_PPT; ++i) {
+        const i64 p = tile + i * 32 + lane;
+        if (p < A.np) {
+            double nx = wrap_box(P[i][0] + tot[i][0], L), ny = wrap_box(P[i][1] + tot[i][1], L);
+            double nz = (DIM == 3) ? wrap_box(P[i][2] + tot[i][2], L) : P[i][2];
+            if (REC) {
+                double2 *o = reinterpret_cast<double2 *>(A.rec_out + p);
+                __stcs(o, make_double2(M[i], nx));
+                __stcs(o + 1, make_double2(ny, nz));
+            } else {
+                __stcs(A.xo + p, nx); __stcs(A.yo + p, ny);
+                if (DIM == 3) __stcs(A.zo + p, nz);
+            }
+        }
+    }
+    if (lane == 0 && A.npairs && nq) atomicAdd(A.npairs, (u64)nq);
 }
 
-static snap_cells make_cells(int dim, double L, double Rq_max) {
-    snap_cells C;
-    C.dim = dim;
-    int ngmax = (dim == 3) ? 96 : 1024;
-    double n = (Rq_max > 0) ? floor(L / Rq_max) : (double)ngmax;
+// ---------------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------------
+extern "C" int64_t bf_snap_grid_cells(int dim, double L, double Rq_mean) {
+    if ((dim != 2 && dim != 3) || !(L > 0)) return 0;
+    i64 cap = (dim == 3) ? SN_NG_MAX_3D : SN_NG_MAX_2D;
+    if (!(Rq_mean > 0)) return cap;
+    double n = floor(L / Rq_mean);
     if (!(n >= 1)) n = 1;
-    if (n > ngmax) n = ngmax;
-    C.ng = (int)n;
-    C.ncell = (dim == 3) ? C.ng * C.ng * C.ng : C.ng * C.ng;
-    C.inv_cs = (double)C.ng / L;
-    return C;
+    if (n > (double)cap) n = (double)cap;
+    return (i64)n;
 }
 
-static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
-
-extern "C" size_t bf_snap_ws_bytes(int dim, int64_t nh, double L, double Rq_max) {
-    if ((dim != 2 && dim != 3) || nh < 0 || !(L > 0)) return 0;
-    snap_cells C = make_cells(dim, L, Rq_max);
-    return 3 * align256(sizeof(int) * ((size_t)C.ncell + 1)) + align256(sizeof(int) * (size_t)(nh + 1));
+extern "C" size_t bf_snap_ws_bytes(int dim, int64_t nh, double L, int64_t ng, int64_t max_entries) {
+    if ((dim != 2 && dim != 3) || nh < 0 || !(L > 0) || ng < 1 || max_entries < 0) return 0;
+    if (ng > ((dim == 3) ? SN_NG_MAX_3D : SN_NG_MAX_2D)) return 0;
+    return snap_layout(nullptr, make_grid(dim, L, ng), nh, max_entries).total;
 }
 
-extern "C" int bf_snap_displace(int dim, int64_t np, const double *x, const double *y, const double *z, double L,
-                                double a, const bf_snap_halos *H, const bf_table *T, double Rq_max, double *xo,
-                                double *yo, double *zo, unsigned long long *npairs, void *ws, size_t ws_bytes,
-                                void *stream) {
+extern "C" int bf_snap_bin_halos(int dim, double L, int64_t ng, const bf_snap_halos *H, int64_t max_entries, void *ws,
+                                 size_t ws_bytes, int64_t *nentries_host, void *stream) {
     BF_REQUIRE(dim == 2 || dim == 3, "dim must be 2 or 3");
-    BF_REQUIRE(np >= 0 && L > 0, "np / L");
-    BF_REQUIRE(bf_check_table(T), "bad table");
+    BF_REQUIRE(L > 0 && ng >= 1 && ng <= ((dim == 3) ? SN_NG_MAX_3D : SN_NG_MAX_2D), "L / ng");
     BF_REQUIRE(H && H->nh >= 0 && H->nh < (1ll << 31), "halo record");
-    if (np == 0) return BF_OK;
-    BF_REQUIRE(x && y && xo && yo && (dim == 2 || (z && zo)), "null particle array");
-    BF_REQUIRE(H->nh == 0 || (H->pos && H->Rq && H->cut && H->lnr_shift && H->rows), "null per-halo array");
-    size_t need = bf_snap_ws_bytes(dim, H->nh, L, Rq_max);
-    if (ws_bytes < need || !ws) {
-        bf_set_error("bf_snap_displace: workspace %zu < %zu bytes", ws_bytes, need);
+    BF_REQUIRE(H->nh == 0 || (H->pos && H->Rq), "null per-halo array");
+    BF_REQUIRE(ws && nentries_host, "null outputs");
+    BF_REQUIRE(max_entries >= 0 && max_entries < (1ll << 31), "max_entries must fit int32");
+    snap_grid G = make_grid(dim, L, ng);
+    snap_ws w = snap_layout(ws, G, H->nh, max_entries);
+    if (ws_bytes < w.total) {
+        bf_set_error("bf_snap_bin_halos: workspace %zu < %zu bytes", ws_bytes, w.total);
         return BF_E_WORKSPACE;
     }
     cudaStream_t s = (cudaStream_t)stream;
-    snap_cells C = make_cells(dim, L, Rq_max);
-    size_t csz = align256(sizeof(int) * ((size_t)C.ncell + 1));
-    char *w = (char *)ws;
-    int *count = (int *)w, *start = (int *)(w + csz), *cursor = (int *)(w + 2 * csz), *list = (int *)(w + 3 * csz);
-    BF_CUDA_OK(cudaMemsetAsync(count, 0, csz, s));
-    BF_CUDA_OK(cudaMemsetAsync(cursor, 0, csz, s));
-    BF_CUDA_OK(cudaMemsetAsync(start, 0, csz, s));
-    if (H->nh > 0) {
-        unsigned hb = (unsigned)((H->nh + 255) / 256);
-        snap_count_kernel<<<hb, 256, 0, s>>>(C, H->nh, H->pos, count);
-        BF_LAUNCH_OK();
-        snap_scan_kernel<<<1, 1024, 0, s>>>(C.ncell, count, start);
-        BF_LAUNCH_OK();
-        snap_fill_kernel<<<hb, 256, 0, s>>>(C, H->nh, H->pos, start, cursor, list);
-        BF_LAUNCH_OK();
-        snap_sort_kernel<<<(unsigned)((C.ncell + 255) / 256), 256, 0, s>>>(C.ncell, start, list);
-        BF_LAUNCH_OK();
+    BF_CUDA_OK(cudaMemsetAsync(w.cell_start, 0, sizeof(int) * (size_t)(G.ncell + 1), s));
+    snap_hdr_kernel<<<1, 1, 0, s>>>(w.hdr, w.entj);
+    BF_LAUNCH_OK();
+    BF_CUDA_OK(cudaMemsetAsync(w.counts, 0, sizeof(i64) * (size_t)(H->nh + 1), s));
+    *nentries_host = 0;
+    if (H->nh == 0) return BF_OK;
+    unsigned blocks = (unsigned)((H->nh * 32 + 127) / 128);
+    if (dim == 2) snap_bin_kernel<2, false><<<blocks, 128, 0, s>>>(G, *H, w.counts, nullptr, nullptr, w.hrec);
+    else snap_bin_kernel<3, false><<<blocks, 128, 0, s>>>(G, *H, w.counts, nullptr, nullptr, w.hrec);
+    BF_LAUNCH_OK();
+    size_t cb = w.cub_bytes;
+    BF_CUDA_OK(cub::DeviceScan::ExclusiveSum(w.cub_tmp, cb, w.counts, w.offsets, (int)(H->nh + 1), s));
+    i64 total = 0;
+    BF_CUDA_OK(cudaMemcpyAsync(&total, w.offsets + H->nh, sizeof(i64), cudaMemcpyDeviceToHost, s));
+    BF_CUDA_OK(cudaStreamSynchronize(s));
+    *nentries_host = total;
+    if (total > max_entries) {
+        bf_set_error("bf_snap_bin_halos: %lld entries exceed max_entries %lld", (long long)total, (long long)max_entries);
+        return BF_E_WORKSPACE;
     }
-    unsigned pb = (unsigned)((np + SN_THREADS - 1) / SN_THREADS);
-    bf_raxis ax = bf_make_raxis(T);
-    if (dim == 2)
-        snap_gather_kernel<2><<<pb, SN_THREADS, 0, s>>>(C, np, x, y, z, L, a, *H, ax, start, list, xo, yo, zo, npairs);
-    else
-        snap_gather_kernel<3><<<pb, SN_THREADS, 0, s>>>(C, np, x, y, z, L, a, *H, ax, start, list, xo, yo, zo, npairs);
+    if (total == 0) return BF_OK;
+    if (dim == 2) snap_bin_kernel<2, true><<<blocks, 128, 0, s>>>(G, *H, w.counts, w.offsets, w.keys, w.hrec);
+    else snap_bin_kernel<3, true><<<blocks, 128, 0, s>>>(G, *H, w.counts, w.offsets, w.keys, w.hrec);
+    BF_LAUNCH_OK();
+    int cell_bits = 1;
+    while (((i64)1 << cell_bits) < G.ncell) ++cell_bits;
+    cub::DoubleBuffer<u64> db(w.keys, w.keys_alt);
+    cb = w.cub_bytes;
+    // stable sort on the cell bits only: keys were emitted halo by halo, so every cell's list stays in catalogue order
+    BF_CUDA_OK(cub::DeviceRadixSort::SortKeys(w.cub_tmp, cb, db, (int)total, 32, 32 + cell_bits, s));
+    snap_entries_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(total, G.ncell, db.Current(), w.cell_start, w.entj);
     BF_LAUNCH_OK();
     return BF_OK;
+}
+
+static int snap_launch(int dim, int64_t np, snap_args &A, double L, int64_t ng, const bf_snap_halos *H, const bf_table *T,
+                       const void *ws, bool rec, void *stream) {
+    BF_REQUIRE(dim == 2 || dim == 3, "dim must be 2 or 3");
+    BF_REQUIRE(np >= 0 && L > 0, "np / L");
+    BF_REQUIRE(ng >= 1 && ng <= ((dim == 3) ? SN_NG_MAX_3D : SN_NG_MAX_2D), "ng");
+    BF_REQUIRE(bf_check_table(T), "bad table");
+    BF_REQUIRE(H && H->nh >= 0 && H->nh < (1ll << 31), "halo record");
+    BF_REQUIRE(H->nh == 0 || (H->pos && H->Rq && H->cut && H->lnr_shift && H->rows), "null per-halo array");
+    BF_REQUIRE(ws, "workspace (from bf_snap_bin_halos) is NULL");
+    if (np == 0) return BF_OK;
+    A.G = make_grid(dim, L, ng);
+    snap_ws w = snap_layout(const_cast<void *>(ws), A.G, H->nh, 0);  // the fixed part does not depend on max_entries
+    A.np = np;
+    A.H = *H;
+    A.ax = bf_make_raxis(T);
+    A.cell_start = w.cell_start;
+    A.hrec = w.hrec;
+    A.hdr = w.hdr;
+    unsigned pb = (unsigned)((np + SN_TILE - 1) / SN_TILE);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (dim == 2) {
+        if (rec) snap_gather_kernel<2, true><<<pb, SN_THREADS, 0, s>>>(A);
+        else snap_gather_kernel<2, false><<<pb, SN_THREADS, 0, s>>>(A);
+    } else {
+        if (rec) snap_gather_kernel<3, true><<<pb, SN_THREADS, 0, s>>>(A);
+        else snap_gather_kernel<3, false><<<pb, SN_THREADS, 0, s>>>(A);
+    }
+    BF_LAUNCH_OK();
+    return BF_OK;
+}
+
+extern "C" int bf_snap_displace(int dim, int64_t np, const double *x, const double *y, const double *z, double L,
+                                double a, const bf_snap_halos *H, const bf_table *T, int64_t ng, const void *ws,
+                                double *xo, double *yo, double *zo, unsigned long long *npairs, void *stream) {
+    BF_REQUIRE(np == 0 || (x && y && xo && yo && (dim == 2 || (z && zo))), "null particle array");
+    snap_args A;
+    A.x = x; A.y = y; A.z = z; A.xo = xo; A.yo = yo; A.zo = zo;
+    A.rec = nullptr; A.rec_out = nullptr;
+    A.a = a;
+    A.npairs = npairs;
+    return snap_launch(dim, np, A, L, ng, H, T, ws, false, stream);
+}
+
+extern "C" int bf_snap_displace_records(int dim, int64_t np, const void *cat, double L, double a,
+                                        const bf_snap_halos *H, const bf_table *T, int64_t ng, const void *ws,
+                                        void *cat_out, unsigned long long *npairs, void *stream) {
+    BF_REQUIRE(np == 0 || (cat && cat_out), "null particle records");
+    BF_REQUIRE((((uintptr_t)cat | (uintptr_t)cat_out) & 15) == 0, "particle records must be 16-byte aligned");
+    snap_args A;
+    A.x = A.y = A.z = nullptr; A.xo = A.yo = A.zo = nullptr;
+    A.rec = (const double4 *)cat; A.rec_out = (double4 *)cat_out;
+    A.a = a;
+    A.npairs = npairs;
+    return snap_launch(dim, np, A, L, ng, H, T, ws, true, stream);
 }

@@ -154,12 +154,26 @@ typedef struct {
     int64_t nh;
 } bf_snap_halos;
 
-size_t bf_snap_ws_bytes(int dim, int64_t nh, double L, double Rq_max);
-/* Periodic ball query + displacement (SnapshotRunner.py:205-247) as a particle-centric gather over a
- * halo cell list, then add + single wrap (:250-260).  x,y,z in / out are separate arrays (z NULL in 2-D). */
+/* The periodic KD-tree (SnapshotRunner.py:92-97) is replaced by a fine periodic halo grid: every halo is listed in
+ * each cell its query ball overlaps, lists are in catalogue order.  `ng` = cells per side;
+ * bf_snap_grid_cells() proposes one cell per mean query radius (capped at 256 in 3-D, 4096 in 2-D). */
+int64_t bf_snap_grid_cells(int dim, double L, double Rq_mean);
+size_t bf_snap_ws_bytes(int dim, int64_t nh, double L, int64_t ng, int64_t max_entries);
+/* Same protocol as bf_shell_bin_halos: *nentries_host = exact number of (cell, halo) entries; BF_E_WORKSPACE when
+ * it exceeds max_entries (call again with a workspace sized for it).  Synchronises `stream` once. */
+int bf_snap_bin_halos(int dim, double L, int64_t ng, const bf_snap_halos *h_host, int64_t max_entries, void *ws,
+                      size_t ws_bytes, int64_t *nentries_host, void *stream);
+/* Periodic ball query + displacement (SnapshotRunner.py:205-247) as a particle-centric gather over the binned
+ * halos, then add + single wrap (:250-260).  x,y,z in / out are separate arrays (z NULL in 2-D). */
 int bf_snap_displace(int dim, int64_t np, const double *x, const double *y, const double *z, double L, double a,
-                     const bf_snap_halos *h_host, const bf_table *tab_host, double Rq_max, double *xo, double *yo,
-                     double *zo, unsigned long long *npairs, void *ws, size_t ws_bytes, void *stream);
+                     const bf_snap_halos *h_host, const bf_table *tab_host, int64_t ng, const void *ws, double *xo,
+                     double *yo, double *zo, unsigned long long *npairs, void *stream);
+/* Same on the reference's own particle records: ParticleSnapshot.cat is a structured array of float64
+ * (M, x, y, z) (utils/io.py:581-589; z is a filler in 2-D).  cat / cat_out are [np] 32-byte records, 16-byte
+ * aligned; cat_out receives M unchanged and the displaced, wrapped coordinates (new_cat, SnapshotRunner.py:250). */
+int bf_snap_displace_records(int dim, int64_t np, const void *cat, double L, double a, const bf_snap_halos *h_host,
+                             const bf_table *tab_host, int64_t ng, const void *ws, void *cat_out,
+                             unsigned long long *npairs, void *stream);
 
 #ifdef __cplusplus
 }

@@ -50,7 +50,8 @@ def test_host_only_entry_points():
     assert lib.bf_shell_band_pixel_range(64, 3, 2, C.byref(f), C.byref(l)) == -1  # BF_E_INVALID
     assert b"band range" in lib.bf_last_error()
     assert lib.bf_shell_bin_ws_bytes(64, 1000, 5000) > 0
-    assert lib.bf_snap_ws_bytes(3, 1000, 100.0, 7.0) > 0
+    assert lib.bf_snap_grid_cells(3, 100.0, 7.0) == 14 and lib.bf_snap_grid_cells(2, 100.0, 1e-9) == 4096
+    assert lib.bf_snap_ws_bytes(3, 1000, 100.0, 14, 5000) > 0 and lib.bf_snap_ws_bytes(3, 10, 100.0, 257, 0) == 0
 
 
 def test_no_cpu_fallback():

@@ -192,20 +192,52 @@ def test_grid_parity(gpu, dim, npix, nhalo, eps):
     assert relmax(g, r) < 1e-11
 
 
-@pytest.mark.parametrize("dim,side,nhalo", [(3, 64, 400), (2, 400, 300)])
-def test_snapshot_parity(gpu, dim, side, nhalo):
+@pytest.mark.parametrize("layout", ["reference", "extra_column"])
+@pytest.mark.parametrize("dim,side,nhalo,eps", [(3, 64, 400, 5.0), (2, 400, 300, 5.0), (3, 40, 60, 60.0)])
+def test_snapshot_parity(gpu, dim, side, nhalo, eps, layout):
+    """eps = 60 drives R_q to the L/2 clip (SnapshotRunner.py:215): query balls wrap the whole box."""
     import baryonification_b200 as bf
     from baryonification_b200 import synthetic as syn
     from oracle import runners as orc
-    cfg = syn.config_snapshot(npart_side=side, nhalo=nhalo, dim=dim, epsilon_max=5.0, L=(100.0 if dim == 3 else 300.0))
+    cfg = syn.config_snapshot(npart_side=side, nhalo=nhalo, dim=dim, epsilon_max=eps, L=(100.0 if dim == 3 else 300.0))
+    if layout == "extra_column":  # not the 32-byte (M, x, y, z) record: the field-by-field path
+        old = cfg["field"].cat
+        cat = np.zeros(old.size, dtype=old.dtype.descr + [("id", "i8")])
+        for k in old.dtype.names:
+            cat[k] = old[k]
+        cat["id"] = np.arange(old.size)
+        cfg["field"].cat = cat
+    got_r = bf.BaryonifySnapshot(cfg["catalog"], cfg["field"], eps, cfg["model"], verbose=False)
+    ref_r = orc.BaryonifySnapshot(cfg["catalog"], cfg["field"], eps, cfg["model"])
+    got, ref = got_r.process(), ref_r.process()
+    assert got_r.npairs == ref_r.npairs and ref_r.npairs > 100
+    assert got.dtype == ref.dtype and got.shape == ref.shape
+    for k in "xyz"[:dim]:
+        assert np.max(np.abs(got[k] - ref[k])) < 1e-11
+    for k in got.dtype.names:
+        if k not in "xyz"[:dim]:
+            assert np.array_equal(got[k], ref[k])
+    again = bf.BaryonifySnapshot(cfg["catalog"], cfg["field"], eps, cfg["model"], verbose=False).process()
+    assert all(np.array_equal(got[k], again[k]) for k in got.dtype.names)  # no atomics: bit-reproducible
+
+
+def test_snapshot_dense_block_uses_several_queue_rounds(gpu):
+    """More than SN_QCAP pairs inside one 256-particle block (particles piled onto a few halos)."""
+    import baryonification_b200 as bf
+    from baryonification_b200 import synthetic as syn
+    from oracle import runners as orc
+    cfg = syn.config_snapshot(npart_side=24, nhalo=300, dim=3, epsilon_max=5.0, L=100.0)
+    cat, hc = cfg["field"].cat, cfg["catalog"].cat
+    rng = np.random.default_rng(11)
+    for k in "xyz":  # all particles within 1.5 Mpc of the halo cloud's corner, halos crowded there too
+        cat[k] = rng.uniform(10.0, 11.5, cat.size)
+        hc[k] = rng.uniform(9.5, 12.0, hc.size).astype(hc.dtype[k])
     got_r = bf.BaryonifySnapshot(cfg["catalog"], cfg["field"], 5.0, cfg["model"], verbose=False)
     ref_r = orc.BaryonifySnapshot(cfg["catalog"], cfg["field"], 5.0, cfg["model"])
     got, ref = got_r.process(), ref_r.process()
-    assert got_r.npairs == ref_r.npairs and ref_r.npairs > 100
-    assert got.dtype == ref.dtype
-    for k in "xyz"[:dim]:
-        assert np.max(np.abs(got[k] - ref[k])) < 1e-11
-    assert np.array_equal(got["M"], ref["M"])
+    assert got_r.npairs == ref_r.npairs and ref_r.npairs > 50 * cat.size
+    for k in "xyz":
+        assert np.max(np.abs(got[k] - ref[k])) < 1e-9
 
 
 # ------------------------------------------------------------------ committed reference fixtures
