@@ -7,6 +7,7 @@ is a cell-list gather on the device, there is no tree to build.
 from __future__ import annotations
 
 import ctypes as C
+import os
 import time
 
 import numpy as np
@@ -62,6 +63,8 @@ class BaryonifySnapshot(DefaultRunnerSnapshot):
                               t["lnr_shift"].data_ptr(), rows.data_ptr(), nh)
         L = float(S.L)
         ng = lib.bf_snap_grid_cells(dim, L, float(s["Rq"].mean()) if nh else 0.0)
+        if os.environ.get("BF_SNAP_NG"):  # tuning experiments only
+            ng = int(os.environ["BF_SNAP_NG"])
         max_entries, ws = 0, None
         for _ in range(2):  # counting pass first (exact size), then the real one
             need = lib.bf_snap_ws_bytes(dim, nh, L, ng, max_entries)

@@ -25,7 +25,6 @@
 #include "bf_common.cuh"
 
 #define SN_THREADS 256
-#define SN_WQ 1024
 #define SN_NG_MAX_3D 256
 #define SN_NG_MAX_2D 4096
 
@@ -47,18 +46,21 @@ static snap_grid make_grid(int dim, double L, i64 ng) {
 }
 
 __device__ __forceinline__ int snap_cell_coord(double x, const snap_grid &G) {
-    int g = (int)floor(x * G.inv_cs) % G.ng;  // x = L (allowed by the single wrap, :259-260) lands in cell 0
-    return (g < 0) ? g + G.ng : g;
+    int g = (int)floor(x * G.inv_cs);  // x = L (allowed by the single wrap, :259-260) lands in cell 0
+    if ((unsigned)g >= (unsigned)G.ng) { g %= G.ng; if (g < 0) g += G.ng; }
+    return g;
 }
 
 struct snap_hdr {  // first 256 bytes of the workspace, written by bf_snap_bin_halos, read by the particle kernel
-    const int *entj;  // [nentries] halo index of every (cell, halo) entry, cell-sorted, catalogue order inside a cell
+    const int *entj;  // [nentries] halo index of every (cell, halo) entry, cell-sorted, catalogue order inside a cell;
+                      // the last entry of a cell is stored as ~j
 };
 
 struct snap_ws {
     snap_hdr *hdr;
     i64 *counts, *offsets;
-    int *cell_start;   // [ncell + 1] entries [start[c], start[c+1]) belong to cell c
+    int *cell_tab;     // [ncell] 0 = no halo reaches the cell; -(j+1) = only halo j; s+1 = list entj[s ...] (>= 2 halos)
+    double2 *hpar;     // [nh] (cut, lnr_shift)
     double4 *hrec;     // [nh] (x, y, z, R_q): one 32-byte sector per membership test, L2-resident (3.2 MB at 1e5 halos)
     u64 *keys, *keys_alt;
     int *entj;
@@ -75,7 +77,8 @@ static snap_ws snap_layout(void *base, const snap_grid &G, i64 nh, i64 max_entri
     w.hdr = (snap_hdr *)(p + o);     o += 256;
     w.counts = (i64 *)(p + o);       o += sn_al256(sizeof(i64) * (size_t)(nh + 1));
     w.offsets = (i64 *)(p + o);      o += sn_al256(sizeof(i64) * (size_t)(nh + 2));
-    w.cell_start = (int *)(p + o);   o += sn_al256(sizeof(int) * (size_t)(G.ncell + 1));
+    w.cell_tab = (int *)(p + o);     o += sn_al256(sizeof(int) * (size_t)(G.ncell + 1));
+    w.hpar = (double2 *)(p + o);     o += sn_al256(sizeof(double2) * (size_t)(nh + 1));
     w.hrec = (double4 *)(p + o);     o += sn_al256(sizeof(double4) * (size_t)(nh + 1));
     w.keys = (u64 *)(p + o);         o += sn_al256(sizeof(u64) * (size_t)(max_entries + 1));
     w.keys_alt = (u64 *)(p + o);     o += sn_al256(sizeof(u64) * (size_t)(max_entries + 1));
@@ -98,13 +101,16 @@ static snap_ws snap_layout(void *base, const snap_grid &G, i64 nh, i64 max_entri
 template <int DIM, bool FILL>
 __global__ void __launch_bounds__(128) snap_bin_kernel(snap_grid G, bf_snap_halos H, i64 *__restrict__ counts,
                                                        const i64 *__restrict__ offsets, u64 *__restrict__ keys,
-                                                       double4 *__restrict__ hrec) {
+                                                       double4 *__restrict__ hrec, double2 *__restrict__ hpar) {
     i64 j = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (j >= H.nh) return;
     double p[3] = {H.pos[DIM * j], H.pos[DIM * j + 1], (DIM == 3) ? H.pos[DIM * j + 2] : 0.0};
     double R = H.Rq[j];
-    if (!FILL && lane == 0) hrec[j] = make_double4(p[0], p[1], p[2], R);
+    if (!FILL && lane == 0) {
+        hrec[j] = make_double4(p[0], p[1], p[2], R);
+        hpar[j] = make_double2(H.cut ? H.cut[j] : 0.0, H.lnr_shift ? H.lnr_shift[j] : 0.0);
+    }
     if (!(R >= 0.0)) { if (!FILL && lane == 0) counts[j] = 0; return; }  // NaN / negative radius: no particles
     i64 lo[3] = {0, 0, 0}, n[3] = {1, 1, 1};
     bool full[3] = {false, false, false};
@@ -149,20 +155,20 @@ __global__ void __launch_bounds__(128) snap_bin_kernel(snap_grid G, bf_snap_halo
     if (!FILL && lane == 0) counts[j] = total;
 }
 
-// after the sort: cell_start[c] = first entry of cell c (empty cells included), entj = halo index per entry.
-// The tables a particle touches at random (cell_start 4 B/cell, entj 4 B/entry, hrec 32 B/halo) are kept small so
-// that they stay L2-resident while the particle records stream through with evict-first hints.
-__global__ void snap_entries_kernel(i64 n, i64 ncell, const u64 *__restrict__ keys, int *__restrict__ cell_start,
+// after the sort: the cell table and the per-entry halo indices.  The tables a particle touches at random
+// (cell_tab 4 B/cell, entj 4 B/entry, hrec 32 B/halo) are small enough to stay L2-resident while the particle
+// records stream through with evict-first hints; a cell reached by ONE halo (the common case) names it in the
+// cell table itself, which saves a dependent load.
+__global__ void snap_entries_kernel(i64 n, const u64 *__restrict__ keys, int *__restrict__ cell_tab,
                                     int *__restrict__ entj) {
     i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     u64 k = keys[i];
-    i64 c = (i64)(k >> 32);
-    i64 pc = (i == 0) ? -1 : (i64)(keys[i - 1] >> 32);
-    for (i64 cc = pc + 1; cc <= c; ++cc) cell_start[cc] = (int)i;
-    if (i == n - 1)
-        for (i64 cc = c + 1; cc <= ncell; ++cc) cell_start[cc] = (int)n;
-    entj[i] = (int)(k & 0xffffffffull);
+    u64 c = k >> 32;
+    int j = (int)(k & 0xffffffffull);
+    bool first = (i == 0) || (keys[i - 1] >> 32) != c, last = (i == n - 1) || (keys[i + 1] >> 32) != c;
+    if (first) cell_tab[c] = last ? -(j + 1) : (int)(i + 1);
+    entj[i] = last ? ~j : j;
 }
 
 __global__ void snap_hdr_kernel(snap_hdr *hdr, const int *entj) { hdr->entj = entj; }
@@ -201,8 +207,9 @@ struct snap_args {
     double a;
     bf_snap_halos H;
     bf_raxis ax;
-    const int *cell_start;
+    const int *cell_tab;
     const double4 *hrec;
+    const double2 *hpar;
     const snap_hdr *hdr;
     u64 *npairs;
 };
@@ -224,6 +231,18 @@ __device__ __forceinline__ double4 ldg_rec(const double4 *p) {  // one 32-byte s
     return make_double4(a.x, a.y, b.x, b.y);
 }
 
+// next candidate halo of a cell (see snap_entries_kernel for the encoding), -1 when the list is exhausted
+__device__ __forceinline__ int snap_next(const int *__restrict__ entj, int &pend, int &pos) {
+    int j = -1;
+    if (pend >= 0) { j = pend; pend = -1; }
+    else if (pos >= 0) {
+        int e = __ldg(entj + pos);
+        if (e < 0) { j = ~e; pos = -1; }
+        else { j = e; ++pos; }
+    }
+    return j;
+}
+
 template <int DIM>
 __device__ __forceinline__ bool snap_member(const double P[3], const double4 h, double L, double dx[3]) {
     dx[0] = wrap_half(P[0] - h.x, L);  // :235-238
@@ -243,7 +262,7 @@ __global__ void __launch_bounds__(SN_THREADS, SN_MINBLOCKS) snap_gather_kernel(s
     const double L = A.G.L;
     const int *__restrict__ entj = A.hdr->entj;
     double P[SN_PPT][3], M[SN_PPT];
-    int beg[SN_PPT], cnt[SN_PPT], num[SN_PPT];
+    int tab[SN_PPT], cnt[SN_PPT];
 #pragma unroll
     for (int i = 0; i < SN_PPT; ++i) {
         const i64 p = tile + i * 32 + lane;
@@ -262,26 +281,37 @@ __global__ void __launch_bounds__(SN_THREADS, SN_MINBLOCKS) snap_gather_kernel(s
 #pragma unroll
     for (int i = 0; i < SN_PPT; ++i) {
         const i64 p = tile + i * 32 + lane;
-        beg[i] = 0; num[i] = 0;
+        tab[i] = 0;
         if (p < A.np) {
             int c = snap_cell_coord(P[i][0], A.G) * A.G.ng + snap_cell_coord(P[i][1], A.G);
             if (DIM == 3) c = c * A.G.ng + snap_cell_coord(P[i][2], A.G);
-            beg[i] = __ldg(A.cell_start + c);
-            num[i] = __ldg(A.cell_start + c + 1) - beg[i];
+            tab[i] = __ldg(A.cell_tab + c);
         }
     }
     // phase 1: count the halos that reach each particle
     int mine = 0;
-    int smax = 0;
+    {
+        int pend[SN_PPT], pos[SN_PPT];
+        bool any = false;
 #pragma unroll
-    for (int i = 0; i < SN_PPT; ++i) { cnt[i] = 0; smax = max(smax, num[i]); }
-    for (int s = 0; s < smax; ++s) {  // the SN_PPT lists advance together: independent 32-byte loads in flight
+        for (int i = 0; i < SN_PPT; ++i) {
+            cnt[i] = 0;
+            pend[i] = (tab[i] < 0) ? -tab[i] - 1 : -1;
+            pos[i] = (tab[i] > 0) ? tab[i] - 1 : -1;
+            any |= tab[i] != 0;
+        }
+        while (any) {  // the SN_PPT candidate lists advance together: independent loads in flight
+            any = false;
 #pragma unroll
-        for (int i = 0; i < SN_PPT; ++i)
-            if (s < num[i]) {
-                double dx[3];
-                cnt[i] += snap_member<DIM>(P[i], ldg_rec(A.hrec + __ldg(entj + beg[i] + s)), L, dx) ? 1 : 0;
+            for (int i = 0; i < SN_PPT; ++i) {
+                int j = snap_next(entj, pend[i], pos[i]);
+                if (j >= 0) {
+                    double dx[3];
+                    cnt[i] += snap_member<DIM>(P[i], ldg_rec(A.hrec + j), L, dx) ? 1 : 0;
+                }
+                any |= (pend[i] >= 0) || (pos[i] >= 0);
             }
+        }
     }
 #pragma unroll
     for (int i = 0; i < SN_PPT; ++i) mine += cnt[i];
@@ -304,9 +334,11 @@ __global__ void __launch_bounds__(SN_THREADS, SN_MINBLOCKS) snap_gather_kernel(s
 #pragma unroll
             for (int i = 0; i < SN_PPT; ++i) {
                 if (cnt[i] == 0) continue;
-                for (int s = 0; s < num[i]; ++s) {
+                int pend = (tab[i] < 0) ? -tab[i] - 1 : -1, pos = (tab[i] > 0) ? tab[i] - 1 : -1;
+                for (;;) {
+                    const int j = snap_next(entj, pend, pos);
+                    if (j < 0) break;
                     double dx[3];
-                    const int j = __ldg(entj + beg[i] + s);
                     if (snap_member<DIM>(P[i], ldg_rec(A.hrec + j), L, dx)) {
                         if (k >= r0 && k < r0 + SN_WQ) {
                             snap_q &e = wq[k - r0];
@@ -329,8 +361,9 @@ __global__ void __launch_bounds__(SN_THREADS, SN_MINBLOCKS) snap_gather_kernel(s
             double dsq = dx[0] * dx[0] + dx[1] * dx[1];
             if (DIM == 3) dsq += dx[2] * dx[2];
             double d = sqrt(dsq);
-            double v = bf_row_lerp(A.ax, A.H.rows + (i64)j * A.ax.nr, log(d) - A.H.lnr_shift[j]);
-            v = (d < A.H.cut[j]) ? v : 0.0;  // BaryonCorrection.py:381-382
+            const double2 hp = __ldg(A.hpar + j);  // (cut, lnr_shift)
+            double v = bf_row_lerp(A.ax, A.H.rows + (i64)j * A.ax.nr, log(d) - hp.y);
+            v = (d < hp.x) ? v : 0.0;  // BaryonCorrection.py:381-382
             double off = v * A.a;            // :228 / :245  (x a_j, reproduced as is)
             if (!bf_finite(off)) off = 0.0;
 #pragma unroll
@@ -404,15 +437,15 @@ extern "C" int bf_snap_bin_halos(int dim, double L, int64_t ng, const bf_snap_ha
         return BF_E_WORKSPACE;
     }
     cudaStream_t s = (cudaStream_t)stream;
-    BF_CUDA_OK(cudaMemsetAsync(w.cell_start, 0, sizeof(int) * (size_t)(G.ncell + 1), s));
+    BF_CUDA_OK(cudaMemsetAsync(w.cell_tab, 0, sizeof(int) * (size_t)(G.ncell + 1), s));
     snap_hdr_kernel<<<1, 1, 0, s>>>(w.hdr, w.entj);
     BF_LAUNCH_OK();
     BF_CUDA_OK(cudaMemsetAsync(w.counts, 0, sizeof(i64) * (size_t)(H->nh + 1), s));
     *nentries_host = 0;
     if (H->nh == 0) return BF_OK;
     unsigned blocks = (unsigned)((H->nh * 32 + 127) / 128);
-    if (dim == 2) snap_bin_kernel<2, false><<<blocks, 128, 0, s>>>(G, *H, w.counts, nullptr, nullptr, w.hrec);
-    else snap_bin_kernel<3, false><<<blocks, 128, 0, s>>>(G, *H, w.counts, nullptr, nullptr, w.hrec);
+    if (dim == 2) snap_bin_kernel<2, false><<<blocks, 128, 0, s>>>(G, *H, w.counts, nullptr, nullptr, w.hrec, w.hpar);
+    else snap_bin_kernel<3, false><<<blocks, 128, 0, s>>>(G, *H, w.counts, nullptr, nullptr, w.hrec, w.hpar);
     BF_LAUNCH_OK();
     size_t cb = w.cub_bytes;
     BF_CUDA_OK(cub::DeviceScan::ExclusiveSum(w.cub_tmp, cb, w.counts, w.offsets, (int)(H->nh + 1), s));
@@ -425,8 +458,8 @@ extern "C" int bf_snap_bin_halos(int dim, double L, int64_t ng, const bf_snap_ha
         return BF_E_WORKSPACE;
     }
     if (total == 0) return BF_OK;
-    if (dim == 2) snap_bin_kernel<2, true><<<blocks, 128, 0, s>>>(G, *H, w.counts, w.offsets, w.keys, w.hrec);
-    else snap_bin_kernel<3, true><<<blocks, 128, 0, s>>>(G, *H, w.counts, w.offsets, w.keys, w.hrec);
+    if (dim == 2) snap_bin_kernel<2, true><<<blocks, 128, 0, s>>>(G, *H, w.counts, w.offsets, w.keys, w.hrec, w.hpar);
+    else snap_bin_kernel<3, true><<<blocks, 128, 0, s>>>(G, *H, w.counts, w.offsets, w.keys, w.hrec, w.hpar);
     BF_LAUNCH_OK();
     int cell_bits = 1;
     while (((i64)1 << cell_bits) < G.ncell) ++cell_bits;
@@ -434,7 +467,7 @@ extern "C" int bf_snap_bin_halos(int dim, double L, int64_t ng, const bf_snap_ha
     cb = w.cub_bytes;
     // stable sort on the cell bits only: keys were emitted halo by halo, so every cell's list stays in catalogue order
     BF_CUDA_OK(cub::DeviceRadixSort::SortKeys(w.cub_tmp, cb, db, (int)total, 32, 32 + cell_bits, s));
-    snap_entries_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(total, G.ncell, db.Current(), w.cell_start, w.entj);
+    snap_entries_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(total, db.Current(), w.cell_tab, w.entj);
     BF_LAUNCH_OK();
     return BF_OK;
 }
@@ -454,8 +487,9 @@ static int snap_launch(int dim, int64_t np, snap_args &A, double L, int64_t ng, 
     A.np = np;
     A.H = *H;
     A.ax = bf_make_raxis(T);
-    A.cell_start = w.cell_start;
+    A.cell_tab = w.cell_tab;
     A.hrec = w.hrec;
+    A.hpar = w.hpar;
     A.hdr = w.hdr;
     unsigned pb = (unsigned)((np + SN_TILE - 1) / SN_TILE);
     cudaStream_t s = (cudaStream_t)stream;
