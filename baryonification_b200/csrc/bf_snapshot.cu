@@ -10,16 +10,18 @@
 // A particle then reads ONE cell list (most are empty: query balls cover a few per cent of the box) and tests
 // membership with the KD-tree's own criterion (minimum-image distance^2 <= R_q^2).
 //
-// The particle kernel works in three block-wide phases so that the expensive part (sqrt, log, table lerp,
-// divisions) runs with full lanes although only ~1 particle in 10 has a pair:
-//   1. every thread counts the halos that reach its particle;            (cheap, one 32 B halo record per test)
-//   2. a block scan gives every hit a slot in a shared-memory queue, a second pass over the candidates fills it;
-//   3. the queue is evaluated densely (thread q evaluates pair q), results go to shared memory and every
-//      thread adds ITS pairs in slot order = catalogue order: the reference's summation order
-//      (tot_offsets[inds] += ... for j in range(N_halo)), no atomics, bit-reproducible.
+// The particle kernel (snap_gather_kernel below) is a per-warp pipeline without block barriers:
+//   1. stream: read the records of 2 x 32 particles, look up their cells; particles no halo reaches are written
+//      straight back, the others are parked in a shared-memory queue;
+//   2. whenever 32 particles are parked, one lane each: test the candidate halos (the first 4 with independent
+//      loads), a warp scan gives every hit a slot in a second queue;
+//   3. the pair queue is evaluated densely (sqrt, log, table lerp, divisions run with full lanes although only
+//      ~1 particle in 10 has a pair) and every particle adds ITS pairs in slot order = catalogue order: the
+//      reference's summation order (tot_offsets[inds] += ... for j in range(N_halo)), no atomics, bit-reproducible.
 // HBM traffic: one coalesced read and one coalesced write of the particle records (32 B each way for the
-// reference's (M, x, y, z) float64 records, SURVEY.md section 8d counts 88 B / particle for the reference's
-// separate offsets array).
+// reference's (M, x, y, z) float64 records; SURVEY.md section 8d counts 88 B / particle for the reference's
+// separate offsets array); the randomly accessed tables (4 B / cell, 4 B / entry, 32 B / halo) are kept small
+// enough to live in L2 and the records are streamed with evict-first hints.
 #include <cub/cub.cuh>
 
 #include "bf_common.cuh"
@@ -59,7 +61,7 @@ struct snap_hdr {  // first 256 bytes of the workspace, written by bf_snap_bin_h
 struct snap_ws {
     snap_hdr *hdr;
     i64 *counts, *offsets;
-    int *cell_tab;     // [ncell] 0 = no halo reaches the cell; -(j+1) = only halo j; s+1 = list entj[s ...] (>= 2 halos)
+    int *cell_tab;     // [ncell] 0 = no halo reaches the cell; -(j+1) = only halo j; (s << 6 | min(n, 63)) = list entj[s .. s+n)
     double2 *hpar;     // [nh] (cut, lnr_shift)
     double4 *hrec;     // [nh] (x, y, z, R_q): one 32-byte sector per membership test, L2-resident (3.2 MB at 1e5 halos)
     u64 *keys, *keys_alt;
@@ -167,7 +169,14 @@ __global__ void snap_entries_kernel(i64 n, const u64 *__restrict__ keys, int *__
     u64 c = k >> 32;
     int j = (int)(k & 0xffffffffull);
     bool first = (i == 0) || (keys[i - 1] >> 32) != c, last = (i == n - 1) || (keys[i + 1] >> 32) != c;
-    if (first) cell_tab[c] = last ? -(j + 1) : (int)(i + 1);
+    if (first) {
+        if (last) cell_tab[c] = -(j + 1);
+        else {
+            int nn = 1;  // list length, saturating at 63 (the kernel follows the ~j sentinel beyond SN_K entries)
+            while (nn < 63 && i + nn < n && (keys[i + nn] >> 32) == c) ++nn;
+            cell_tab[c] = (int)(i << 6) | nn;
+        }
+    }
     entj[i] = last ? ~j : j;
 }
 
@@ -188,14 +197,23 @@ __device__ __forceinline__ double wrap_box(double v, double L) {  // :259-260
     return v;
 }
 
-#ifndef SN_PPT
-#define SN_PPT 2
+// A warp streams a chunk of SN_TILES x 32 consecutive particles.  Particles whose cell no halo reaches (the
+// majority) are written straight back out; the others are parked in a per-warp shared-memory queue and processed
+// 32 at a time, so that the candidate tests run with every lane busy although only ~1 particle in 3 has a
+// candidate; their hits go to a second queue that is evaluated densely (sqrt, log, table lerp, divisions), and
+// every particle adds ITS pairs in slot order = catalogue order.  No block barrier anywhere: warps never wait for
+// each other, which is what hides the record -> cell -> halo latency chain.
+#ifndef SN_TILES
+#define SN_TILES 16
 #endif
-// particles per thread: independent loads in flight hide the record -> cell -> entry latency chain
-#define SN_TILE (SN_THREADS * SN_PPT)
 #ifndef SN_MINBLOCKS
-#define SN_MINBLOCKS 4
+#define SN_MINBLOCKS 3
 #endif
+#define SN_CHUNK (32 * SN_TILES)       // particles per warp
+#define SN_TILE (SN_CHUNK * (SN_THREADS / 32))  // particles per block
+#define SN_AQ 96   // parked particles per warp (drained whenever 32 are waiting: <= 31 left over + 2 tiles)
+#define SN_WQ 64   // queued pairs per warp per round
+#define SN_K 4     // candidates handled with independent loads before the sentinel-terminated tail loop
 
 struct snap_args {
     snap_grid G;
@@ -219,9 +237,13 @@ struct __align__(16) snap_q {  // one queued pair: min-image separation in, disp
     int j, src;
 };
 
-#define SN_WQ 64  // queue slots per warp (a warp owns 32 * SN_PPT particles, ~0.1 pairs each on a uniform box)
+struct __align__(8) snap_act {  // one parked particle
+    double M, x, y, z;
+    int tab, idx;  // cell-table word, particle index relative to the warp's chunk
+};
 
 struct snap_smem {
+    snap_act act[SN_THREADS / 32][SN_AQ];
     snap_q q[SN_THREADS / 32][SN_WQ];
 };
 
@@ -229,18 +251,6 @@ __device__ __forceinline__ double4 ldg_rec(const double4 *p) {  // one 32-byte s
     const double2 *q = reinterpret_cast<const double2 *>(p);
     double2 a = __ldg(q), b = __ldg(q + 1);
     return make_double4(a.x, a.y, b.x, b.y);
-}
-
-// next candidate halo of a cell (see snap_entries_kernel for the encoding), -1 when the list is exhausted
-__device__ __forceinline__ int snap_next(const int *__restrict__ entj, int &pend, int &pos) {
-    int j = -1;
-    if (pend >= 0) { j = pend; pend = -1; }
-    else if (pos >= 0) {
-        int e = __ldg(entj + pos);
-        if (e < 0) { j = ~e; pos = -1; }
-        else { j = e; ++pos; }
-    }
-    return j;
 }
 
 template <int DIM>
@@ -254,107 +264,98 @@ __device__ __forceinline__ bool snap_member(const double P[3], const double4 h, 
 }
 
 template <int DIM, bool REC>
-__global__ void __launch_bounds__(SN_THREADS, SN_MINBLOCKS) snap_gather_kernel(snap_args A) {
-    __shared__ snap_smem sm;
-    const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
-    const i64 tile = (i64)blockIdx.x * SN_TILE + (i64)wid * (32 * SN_PPT);  // this WARP's particles
-    snap_q *__restrict__ wq = sm.q[wid];
+__device__ __forceinline__ void snap_store(const snap_args &A, i64 p, double M, double nx, double ny, double nz) {
+    if (REC) {
+        double2 *o = reinterpret_cast<double2 *>(A.rec_out + p);
+        __stcs(o, make_double2(M, nx));
+        __stcs(o + 1, make_double2(ny, nz));
+    } else {
+        __stcs(A.xo + p, nx); __stcs(A.yo + p, ny);
+        if (DIM == 3) __stcs(A.zo + p, nz);
+    }
+}
+
+// Process the first `nact` (<= 32) parked particles of this warp, one per lane.  Returns the number of pairs.
+template <int DIM, bool REC>
+__device__ __forceinline__ int snap_drain(const snap_args &A, const int *__restrict__ entj, const snap_act *act,
+                                          snap_q *wq, int nact, i64 chunk0, int lane) {
     const double L = A.G.L;
-    const int *__restrict__ entj = A.hdr->entj;
-    double P[SN_PPT][3], M[SN_PPT];
-    int tab[SN_PPT], cnt[SN_PPT];
+    const bool on = lane < nact;
+    double P[3] = {0.0, 0.0, 0.0}, M = 0.0;
+    int tab = 0, idx = 0;
+    if (on) {
+        const snap_act &e = act[lane];
+        M = e.M; P[0] = e.x; P[1] = e.y; P[2] = e.z; tab = e.tab; idx = e.idx;
+    }
+    // candidate halos: the first SN_K with independent loads, the rest through the sentinel-terminated list
+    int jj[SN_K], n4 = 0, tail = -1, hm = 0, cnt = 0;
 #pragma unroll
-    for (int i = 0; i < SN_PPT; ++i) {
-        const i64 p = tile + i * 32 + lane;
-        P[i][0] = P[i][1] = P[i][2] = 0.0; M[i] = 0.0;
-        if (p < A.np) {
-            if (REC) {
-                const double2 *r = reinterpret_cast<const double2 *>(A.rec + p);
-                double2 r0 = __ldcs(r), r1 = __ldcs(r + 1);  // streamed once: evict-first, keep L2 for the tables
-                M[i] = r0.x; P[i][0] = r0.y; P[i][1] = r1.x; P[i][2] = r1.y;
-            } else {
-                P[i][0] = __ldcs(A.x + p); P[i][1] = __ldcs(A.y + p);
-                if (DIM == 3) P[i][2] = __ldcs(A.z + p);
-            }
-        }
+    for (int k = 0; k < SN_K; ++k) jj[k] = 0;
+    if (tab < 0) { jj[0] = -tab - 1; n4 = 1; }
+    else if (tab > 0) {
+        const int start = tab >> 6, nn = tab & 63;
+        n4 = min(nn, SN_K);
+#pragma unroll
+        for (int k = 0; k < SN_K; ++k)
+            if (k < n4) { int e = __ldg(entj + start + k); jj[k] = (e < 0) ? ~e : e; }
+        if (nn > SN_K) tail = start + SN_K;
     }
 #pragma unroll
-    for (int i = 0; i < SN_PPT; ++i) {
-        const i64 p = tile + i * 32 + lane;
-        tab[i] = 0;
-        if (p < A.np) {
-            int c = snap_cell_coord(P[i][0], A.G) * A.G.ng + snap_cell_coord(P[i][1], A.G);
-            if (DIM == 3) c = c * A.G.ng + snap_cell_coord(P[i][2], A.G);
-            tab[i] = __ldg(A.cell_tab + c);
+    for (int k = 0; k < SN_K; ++k)
+        if (k < n4) {
+            double dx[3];
+            if (snap_member<DIM>(P, ldg_rec(A.hrec + jj[k]), L, dx)) { hm |= 1 << k; ++cnt; }
         }
+    for (int pos = tail; pos >= 0;) {
+        int e = __ldg(entj + pos);
+        const bool last = e < 0;
+        double dx[3];
+        cnt += snap_member<DIM>(P, ldg_rec(A.hrec + (last ? ~e : e)), L, dx) ? 1 : 0;
+        pos = last ? -1 : pos + 1;
     }
-    // phase 1: count the halos that reach each particle
-    int mine = 0;
-    {
-        int pend[SN_PPT], pos[SN_PPT];
-        bool any = false;
-#pragma unroll
-        for (int i = 0; i < SN_PPT; ++i) {
-            cnt[i] = 0;
-            pend[i] = (tab[i] < 0) ? -tab[i] - 1 : -1;
-            pos[i] = (tab[i] > 0) ? tab[i] - 1 : -1;
-            any |= tab[i] != 0;
-        }
-        while (any) {  // the SN_PPT candidate lists advance together: independent loads in flight
-            any = false;
-#pragma unroll
-            for (int i = 0; i < SN_PPT; ++i) {
-                int j = snap_next(entj, pend[i], pos[i]);
-                if (j >= 0) {
-                    double dx[3];
-                    cnt[i] += snap_member<DIM>(P[i], ldg_rec(A.hrec + j), L, dx) ? 1 : 0;
-                }
-                any |= (pend[i] >= 0) || (pos[i] >= 0);
-            }
-        }
-    }
-#pragma unroll
-    for (int i = 0; i < SN_PPT; ++i) mine += cnt[i];
-    // warp exclusive scan of the per-lane totals: warps never wait for each other (no block barrier anywhere)
-    int inc = mine;
+    // warp exclusive scan of the hit counts -> queue slots
+    int inc = cnt;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
         int v = __shfl_up_sync(0xffffffffu, inc, d);
         if (lane >= d) inc += v;
     }
-    const int base = inc - mine, nq = __shfl_sync(0xffffffffu, inc, 31);
-    double tot[SN_PPT][3];
-#pragma unroll
-    for (int i = 0; i < SN_PPT; ++i) tot[i][0] = tot[i][1] = tot[i][2] = 0.0;
-
-    for (int r0 = 0; r0 < nq; r0 += SN_WQ) {  // one round unless > SN_WQ pairs fall into this tile
-        // phase 2: fill this thread's queue slots [base, base + mine) that fall into the round
-        if (mine > 0 && base < r0 + SN_WQ && base + mine > r0) {
+    const int base = inc - cnt, nq = __shfl_sync(0xffffffffu, inc, 31);
+    double tot[3] = {0.0, 0.0, 0.0};
+    for (int r0 = 0; r0 < nq; r0 += SN_WQ) {  // one round unless > SN_WQ pairs are waiting
+        if (cnt > 0 && base < r0 + SN_WQ && base + cnt > r0) {
             int k = base;
 #pragma unroll
-            for (int i = 0; i < SN_PPT; ++i) {
-                if (cnt[i] == 0) continue;
-                int pend = (tab[i] < 0) ? -tab[i] - 1 : -1, pos = (tab[i] > 0) ? tab[i] - 1 : -1;
-                for (;;) {
-                    const int j = snap_next(entj, pend, pos);
-                    if (j < 0) break;
-                    double dx[3];
-                    if (snap_member<DIM>(P[i], ldg_rec(A.hrec + j), L, dx)) {
-                        if (k >= r0 && k < r0 + SN_WQ) {
-                            snap_q &e = wq[k - r0];
-                            e.v[0] = dx[0]; e.v[1] = dx[1]; e.v[2] = dx[2];
-                            e.j = j;
-                            e.src = i * 32 + lane;
-                        }
-                        ++k;
+            for (int kk = 0; kk < SN_K; ++kk)
+                if (hm >> kk & 1) {
+                    if (k >= r0 && k < r0 + SN_WQ) {
+                        double dx[3];
+                        snap_member<DIM>(P, ldg_rec(A.hrec + jj[kk]), L, dx);
+                        snap_q &e = wq[k - r0];
+                        e.v[0] = dx[0]; e.v[1] = dx[1]; e.v[2] = dx[2];
+                        e.j = jj[kk]; e.src = lane;
                     }
+                    ++k;
                 }
+            for (int pos = tail; pos >= 0;) {
+                int ej = __ldg(entj + pos);
+                const bool last = ej < 0;
+                const int j = last ? ~ej : ej;
+                double dx[3];
+                if (snap_member<DIM>(P, ldg_rec(A.hrec + j), L, dx)) {
+                    if (k >= r0 && k < r0 + SN_WQ) {
+                        snap_q &e = wq[k - r0];
+                        e.v[0] = dx[0]; e.v[1] = dx[1]; e.v[2] = dx[2];
+                        e.j = j; e.src = lane;
+                    }
+                    ++k;
+                }
+                pos = last ? -1 : pos + 1;
             }
         }
         __syncwarp();
-        // phase 3: dense evaluation, thread q evaluates pair q
         const int nround = min(SN_WQ, nq - r0);
-        for (int q = lane; q < nround; q += 32) {
+        for (int q = lane; q < nround; q += 32) {  // dense evaluation: lane q evaluates pair q
             snap_q &e = wq[q];
             const int j = e.j;
             double dx[3] = {e.v[0], e.v[1], e.v[2]};
@@ -364,43 +365,100 @@ __global__ void __launch_bounds__(SN_THREADS, SN_MINBLOCKS) snap_gather_kernel(s
             const double2 hp = __ldg(A.hpar + j);  // (cut, lnr_shift)
             double v = bf_row_lerp(A.ax, A.H.rows + (i64)j * A.ax.nr, log(d) - hp.y);
             v = (d < hp.x) ? v : 0.0;  // BaryonCorrection.py:381-382
-            double off = v * A.a;            // :228 / :245  (x a_j, reproduced as is)
+            double off = v * A.a;      // :228 / :245  (x a_j, reproduced as is)
             if (!bf_finite(off)) off = 0.0;
 #pragma unroll
             for (int m = 0; m < 3; ++m) e.v[m] = (m < DIM) ? off * (dx[m] / d) : 0.0;  // :247 (0/0 -> NaN kept)
         }
         __syncwarp();
-        // every particle adds its own pairs in catalogue order
-        int k = base;
-#pragma unroll
-        for (int i = 0; i < SN_PPT; ++i) {
-            const int k0 = max(k, r0), k1 = min(k + cnt[i], r0 + SN_WQ);
-            for (int kk = k0; kk < k1; ++kk) {
-                tot[i][0] += wq[kk - r0].v[0];
-                tot[i][1] += wq[kk - r0].v[1];
-                if (DIM == 3) tot[i][2] += wq[kk - r0].v[2];
-            }
-            k += cnt[i];
+        const int k0 = max(base, r0), k1 = min(base + cnt, r0 + SN_WQ);
+        for (int k = k0; k < k1; ++k) {  // this particle's pairs, in catalogue order
+            tot[0] += wq[k - r0].v[0];
+            tot[1] += wq[k - r0].v[1];
+            if (DIM == 3) tot[2] += wq[k - r0].v[2];
         }
         __syncwarp();
     }
+    if (on)
+        snap_store<DIM, REC>(A, chunk0 + idx, M, wrap_box(P[0] + tot[0], L), wrap_box(P[1] + tot[1], L),
+                             (DIM == 3) ? wrap_box(P[2] + tot[2], L) : P[2]);
+    return nq;
+}
+
+template <int DIM, bool REC>
+__global__ void __launch_bounds__(SN_THREADS, SN_MINBLOCKS) snap_gather_kernel(snap_args A) {
+    __shared__ snap_smem sm;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const i64 chunk0 = ((i64)blockIdx.x * (SN_THREADS / 32) + wid) * SN_CHUNK;  // this WARP's particles
+    if (chunk0 >= A.np) return;
+    snap_act *act = sm.act[wid];
+    snap_q *wq = sm.q[wid];
+    const int *__restrict__ entj = A.hdr->entj;
+    int nwait = 0, npairs = 0;
+    for (int t0 = 0; t0 < SN_TILES; t0 += 2) {  // two tiles per pass: independent loads in flight
+        double P[2][3], M[2];
+        int tab[2];
 #pragma unroll
-    for (int i = 0; i < SN_PPT; ++i) {
-        const i64 p = tile + i * 32 + lane;
-        if (p < A.np) {
-            double nx = wrap_box(P[i][0] + tot[i][0], L), ny = wrap_box(P[i][1] + tot[i][1], L);
-            double nz = (DIM == 3) ? wrap_box(P[i][2] + tot[i][2], L) : P[i][2];
-            if (REC) {
-                double2 *o = reinterpret_cast<double2 *>(A.rec_out + p);
-                __stcs(o, make_double2(M[i], nx));
-                __stcs(o + 1, make_double2(ny, nz));
-            } else {
-                __stcs(A.xo + p, nx); __stcs(A.yo + p, ny);
-                if (DIM == 3) __stcs(A.zo + p, nz);
+        for (int u = 0; u < 2; ++u) {
+            const i64 p = chunk0 + (t0 + u) * 32 + lane;
+            P[u][0] = P[u][1] = P[u][2] = 0.0; M[u] = 0.0;
+            if (p < A.np) {
+                if (REC) {
+                    const double2 *r = reinterpret_cast<const double2 *>(A.rec + p);
+                    double2 r0 = __ldcs(r), r1 = __ldcs(r + 1);  // streamed once: evict-first, L2 is for the tables
+                    M[u] = r0.x; P[u][0] = r0.y; P[u][1] = r1.x; P[u][2] = r1.y;
+                } else {
+                    P[u][0] = __ldcs(A.x + p); P[u][1] = __ldcs(A.y + p);
+                    if (DIM == 3) P[u][2] = __ldcs(A.z + p);
+                }
             }
         }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const i64 p = chunk0 + (t0 + u) * 32 + lane;
+            tab[u] = 0;
+            if (p < A.np) {
+                int c = snap_cell_coord(P[u][0], A.G) * A.G.ng + snap_cell_coord(P[u][1], A.G);
+                if (DIM == 3) c = c * A.G.ng + snap_cell_coord(P[u][2], A.G);
+                tab[u] = __ldg(A.cell_tab + c);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const i64 p = chunk0 + (t0 + u) * 32 + lane;
+            const bool park = tab[u] != 0;
+            if (p < A.np && !park)  // no halo reaches this cell: the particle does not move (single wrap still applies)
+                snap_store<DIM, REC>(A, p, M[u], wrap_box(P[u][0], A.G.L), wrap_box(P[u][1], A.G.L),
+                                     (DIM == 3) ? wrap_box(P[u][2], A.G.L) : P[u][2]);
+            const unsigned bal = __ballot_sync(0xffffffffu, park);
+            if (park) {
+                snap_act &e = act[nwait + __popc(bal & ((1u << lane) - 1u))];
+                e.M = M[u]; e.x = P[u][0]; e.y = P[u][1]; e.z = P[u][2];
+                e.tab = tab[u]; e.idx = (t0 + u) * 32 + lane;
+            }
+            nwait += __popc(bal);
+        }
+        __syncwarp();
+        // drain whenever a full warp's worth is waiting (every lane busy), and whatever is left at the very end
+        const bool flush = t0 + 2 >= SN_TILES;
+        while (nwait >= 32 || (flush && nwait > 0)) {
+            const int take = min(nwait, 32);
+            npairs += snap_drain<DIM, REC>(A, entj, act, wq, take, chunk0, lane);
+            __syncwarp();
+            snap_act keep[2];
+            const int left = nwait - take;
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+                if (lane + 32 * h < left) keep[h] = act[take + lane + 32 * h];
+            __syncwarp();
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+                if (lane + 32 * h < left) act[lane + 32 * h] = keep[h];
+            nwait = left;
+            __syncwarp();
+        }
     }
-    if (lane == 0 && A.npairs && nq) atomicAdd(A.npairs, (u64)nq);
+    if (lane == 0 && A.npairs && npairs) atomicAdd(A.npairs, (u64)npairs);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -429,7 +487,7 @@ extern "C" int bf_snap_bin_halos(int dim, double L, int64_t ng, const bf_snap_ha
     BF_REQUIRE(H && H->nh >= 0 && H->nh < (1ll << 31), "halo record");
     BF_REQUIRE(H->nh == 0 || (H->pos && H->Rq), "null per-halo array");
     BF_REQUIRE(ws && nentries_host, "null outputs");
-    BF_REQUIRE(max_entries >= 0 && max_entries < (1ll << 31), "max_entries must fit int32");
+    BF_REQUIRE(max_entries >= 0 && max_entries < (1ll << 25), "max_entries must be < 2^25 (use fewer cells)");
     snap_grid G = make_grid(dim, L, ng);
     snap_ws w = snap_layout(ws, G, H->nh, max_entries);
     if (ws_bytes < w.total) {
@@ -453,6 +511,10 @@ extern "C" int bf_snap_bin_halos(int dim, double L, int64_t ng, const bf_snap_ha
     BF_CUDA_OK(cudaMemcpyAsync(&total, w.offsets + H->nh, sizeof(i64), cudaMemcpyDeviceToHost, s));
     BF_CUDA_OK(cudaStreamSynchronize(s));
     *nentries_host = total;
+    if (total >= (1ll << 25)) {
+        bf_set_error("bf_snap_bin_halos: %lld (cell, halo) entries do not fit the cell table; use a smaller ng", (long long)total);
+        return BF_E_INVALID;
+    }
     if (total > max_entries) {
         bf_set_error("bf_snap_bin_halos: %lld entries exceed max_entries %lld", (long long)total, (long long)max_entries);
         return BF_E_WORKSPACE;
