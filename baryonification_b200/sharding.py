@@ -1,0 +1,266 @@
+"""Multi-GPU sharding of the runners: one process per GPU, ``torch.distributed`` for the plumbing.
+
+SURVEY.md section 8(e).  The reference's only parallelism is joblib over halo sub-catalogues
+(``utils/Parallelize.py``: ``SimpleParallel`` :92-113, ``SplitJoinParallel`` :213-318, which works for the
+*linear* Paint runners only, :209).  Here the OUTPUT is partitioned instead:
+
+* shell runners: contiguous HEALPix RING pixel ranges made of whole 8-ring bands with (nearly) equal pixel
+  counts; every rank receives the halos whose query disc can touch its bands (catalogue order preserved, so the
+  per-pixel summation order -- and the bits -- equal the single-GPU run).  PaintProfilesShell needs no reduction
+  at all (pixel owners); BaryonifyShell re-bins its own pixels into a full-sphere accumulator, and the deposits
+  that land outside the rank's range (the boundary mass, a few rings) are sent to their owners and added there in
+  rank order -- the only data-path collective;
+* snapshot runner: particles are split by INDEX (any partition works, the kernel is particle-centric), the halo
+  grid is replicated (it is ~10 MB); no collective on the data path, output order = input order;
+* grid runners: halos are split across ranks, the per-cell accumulators are summed with one all-reduce.
+
+Everything in this file is device-agnostic torch + numpy, so the N > 1 logic is covered on CPU with the gloo
+backend (tests/test_sharding.py); the kernels run on each rank's own device through the engines.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _lib
+
+
+# ----------------------------------------------------------------------------------------------------------
+# partitions
+# ----------------------------------------------------------------------------------------------------------
+def band_pixel_range(nside, band_lo, band_hi):
+    lib = _lib.load()
+    f, l = C.c_int64(), C.c_int64()
+    _lib.check(lib.bf_shell_band_pixel_range(nside, band_lo, band_hi, C.byref(f), C.byref(l)), "bf_shell_band_pixel_range")
+    return f.value, l.value
+
+
+def band_split(nside, world):
+    """``world`` contiguous ring-band ranges [lo, hi) with (nearly) equal pixel counts, covering the sphere."""
+    lib = _lib.load()
+    nb = int(lib.bf_shell_num_bands(nside))
+    if world > nb:
+        raise ValueError(f"cannot split {nb} ring bands of NSIDE {nside} over {world} ranks")
+    npix = 12 * nside * nside
+    ends = np.array([band_pixel_range(nside, 0, b)[1] for b in range(nb + 1)], dtype=np.int64)
+    cuts = [0]
+    for r in range(1, world):
+        c = int(np.searchsorted(ends, npix * r / world))
+        cuts.append(min(max(c, cuts[-1] + 1), nb - (world - r)))
+    cuts.append(nb)
+    return [(cuts[r], cuts[r + 1]) for r in range(world)]
+
+
+def ring_colatitude(nside, ring):
+    """theta of ring ``ring`` (1 .. 4 nside - 1); 0 and pi for the virtual rings 0 and 4 nside."""
+    ring = np.asarray(ring, dtype=np.float64)
+    n = float(nside)
+    z = np.where(ring < n, 1.0 - ring * ring / (3.0 * n * n),
+                 np.where(ring <= 3 * n, (2.0 * n - ring) * 2.0 / (3.0 * n), -1.0 + (4 * n - ring) ** 2 / (3.0 * n * n)))
+    return np.arccos(np.clip(z, -1.0, 1.0))
+
+
+def halos_touching_bands(vec_z, radius, nside, band_lo, band_hi, margin_rings=3):
+    """Mask of the halos whose query disc (plus a safety margin of ``margin_rings`` rings, which also covers the
+    4-neighbour fallback of tiny discs) can touch ring bands [band_lo, band_hi).  Conservative: the binning kernel
+    makes the exact per-band decision."""
+    theta0 = np.arccos(np.clip(np.asarray(vec_z, dtype=np.float64), -1.0, 1.0))
+    r = np.asarray(radius, dtype=np.float64)
+    first_ring = max(band_lo * 8 + 1 - margin_rings, 0)
+    last_ring = min(band_hi * 8 + margin_rings, 4 * nside)
+    t_lo, t_hi = ring_colatitude(nside, first_ring), ring_colatitude(nside, last_ring)
+    keep = (theta0 + r >= t_lo) & (theta0 - r <= t_hi)
+    return keep | ~np.isfinite(r)
+
+
+def index_split(n, world):
+    """``world`` contiguous index ranges of (nearly) equal length covering [0, n)."""
+    edges = [(n * r) // world for r in range(world + 1)]
+    return [(edges[r], edges[r + 1]) for r in range(world)]
+
+
+# ----------------------------------------------------------------------------------------------------------
+# collectives (any backend / device)
+# ----------------------------------------------------------------------------------------------------------
+def _world(group):
+    return dist.get_rank(group), dist.get_world_size(group)
+
+
+def _touched_extent(acc, first, last):
+    """[lo, hi) of the non-zero entries of ``acc`` outside the own range [first, last) (lo = first / hi = last if none)."""
+    lo, hi = first, last
+    if first > 0:
+        nz = torch.nonzero(acc[:first])
+        if nz.numel():
+            lo = int(nz[0])
+    if last < acc.numel():
+        nz = torch.nonzero(acc[last:])
+        if nz.numel():
+            hi = last + int(nz[-1]) + 1
+    return lo, hi
+
+
+def exchange_boundary(acc, ranges, group=None):
+    """Boundary mass exchange of the re-binning stage.
+
+    ``acc`` is this rank's full-length accumulator: its own deposits, mostly inside its own range
+    ``ranges[rank] = [first, last)`` plus the few that landed outside (displaced mass crossing the shard
+    boundary).  Every rank sends those outside parts to their owners; the owner adds what it receives to its own
+    slice in SOURCE-RANK order (a fixed order: bit-reproducible).  Returns the finished own slice (a view of acc).
+    """
+    rank, world = _world(group)
+    first, last = ranges[rank]
+    own = acc[first:last]
+    if world == 1:
+        return own
+    lo, hi = _touched_extent(acc, first, last)
+    ext = torch.tensor([lo, hi], dtype=torch.int64, device=acc.device)
+    all_ext = [torch.empty_like(ext) for _ in range(world)]
+    dist.all_gather(all_ext, ext, group=group)
+    all_ext = [tuple(int(v) for v in e.cpu()) for e in all_ext]
+    ops, recvs = [], []
+    for src in range(world):
+        s_first, s_last = ranges[src]
+        s_lo, s_hi = all_ext[src]
+        for dst in range(world):
+            if dst == src:
+                continue
+            d_first, d_last = ranges[dst]
+            for a, b in ((max(s_lo, d_first), min(s_first, d_last)), (max(s_last, d_first), min(s_hi, d_last))):
+                if b <= a:
+                    continue
+                if rank == src:
+                    ops.append(dist.P2POp(dist.isend, acc[a:b].contiguous(), dist.get_global_rank(group, dst)
+                                          if group is not None else dst, group=group))
+                elif rank == dst:
+                    buf = torch.empty(b - a, dtype=acc.dtype, device=acc.device)
+                    ops.append(dist.P2POp(dist.irecv, buf, dist.get_global_rank(group, src)
+                                          if group is not None else src, group=group))
+                    recvs.append((src, a, b, buf))
+    if ops:
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+    for src, a, b, buf in sorted(recvs, key=lambda t: (t[0], t[1])):
+        acc[a:b] += buf
+    return own
+
+
+def gather_slices(own, ranges, group=None, out=None):
+    """All ranks' slices -> the full array on every rank (slices have different lengths: padded all-gather)."""
+    rank, world = _world(group)
+    n = ranges[-1][1]
+    if world == 1:
+        return own
+    width = max(b - a for a, b in ranges)
+    tail = own.shape[1:]
+    pad = torch.zeros((width,) + tuple(tail), dtype=own.dtype, device=own.device)
+    pad[:own.shape[0]] = own
+    parts = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(parts, pad, group=group)
+    if out is None:
+        out = torch.empty((n,) + tuple(tail), dtype=own.dtype, device=own.device)
+    for r, (a, b) in enumerate(ranges):
+        out[a:b] = parts[r][:b - a]
+    return out
+
+
+# ----------------------------------------------------------------------------------------------------------
+# sharded runners (call from every rank of an initialised process group with the SAME host inputs)
+# ----------------------------------------------------------------------------------------------------------
+def _subset(scalars, keep):
+    return {k: (np.ascontiguousarray(v[keep]) if isinstance(v, np.ndarray) and v.shape[:1] == keep.shape else v)
+            for k, v in scalars.items()}
+
+
+class ShardedShell:
+    """Ring-band sharded BaryonifyShell / PaintProfilesShell.
+
+    ``runner`` is an (unprocessed) ``BaryonifyShell`` or ``PaintProfilesShell`` built identically on every rank.
+    ``process()`` returns the full map on every rank (numpy), exactly like the single-GPU runner."""
+
+    def __init__(self, runner, group=None, device=None):
+        from .Runners import shell as _shell
+        self.runner, self.group = runner, group
+        self.baryonify = isinstance(runner, _shell.BaryonifyShell)
+        self.rank, self.world = _world(group)
+        self.device = device
+        self.npairs = None
+
+    def plan(self):
+        nside = self.runner.LightconeShell.NSIDE
+        bands = band_split(nside, self.world)
+        ranges = [band_pixel_range(nside, lo, hi) for lo, hi in bands]
+        return bands, ranges
+
+    def process_device(self):
+        from . import _device as dv, engine, host
+        from .tables import displacement_host_table, profile_host_table
+        r = self.runner
+        r._check_keys()
+        dev = dv.device(self.device)
+        nside = r.LightconeShell.NSIDE
+        bands, ranges = self.plan()
+        lo, hi = bands[self.rank]
+        s = host.shell_scalars(r.HaloLightConeCatalog, r.cosmo, r.mass_def, r.epsilon_max, r.model, self.baryonify)
+        keep = halos_touching_bands(s["vec"][:, 2], s["radius"], nside, lo, hi)
+        s = _subset(s, keep)
+        mode = engine.BARYONIFY if self.baryonify else engine.PAINT
+        htab = displacement_host_table(r.model) if self.baryonify else profile_host_table(r.model, "2D")
+        with torch.cuda.device(dev):
+            eng = engine.ShellEngine(nside, mode, htab, s, dev, variant="gather", bands=(lo, hi)).upload().bin()
+            acc = eng.accumulate()
+            pairs = torch.tensor([eng.pair_count()], dtype=torch.int64, device=dev)
+            dist.all_reduce(pairs, group=self.group)
+            self.npairs = int(pairs.item())
+            if not self.baryonify:
+                return gather_slices(acc, ranges, self.group), None
+            first, last = ranges[self.rank]
+            orig = np.ascontiguousarray(r.LightconeShell.map, dtype=np.float64)
+            orig_d = dv.to_dev(orig[first:last], dev=dev, pinned=True)
+            new_full = eng.regrid(orig_d, acc, method=r.regrid)
+            own = exchange_boundary(new_full, ranges, self.group)
+            sums = torch.stack([own.sum(), orig_d.sum()])
+            dist.all_reduce(sums, group=self.group)  # the reference's mass check, HealpixRunner.py:344-346
+            return gather_slices(own, ranges, self.group), (float(sums[0]), float(sums[1]))
+
+    def process(self):
+        from . import _device as dv
+        out, sums = self.process_device()
+        if sums is not None:
+            assert np.isclose(sums[0], sums[1]), \
+                "ERROR in pixel regridding, sum(new_map) [%0.14e] != sum(oldmap) [%0.14e]" % sums
+        return dv.to_host(out, True)
+
+
+class ShardedSnapshot:
+    """Index-sharded BaryonifySnapshot: every rank displaces a contiguous slice of the particle array against the
+    full (replicated) halo grid; rank slices are gathered in input order.  No collective on the data path."""
+
+    def __init__(self, runner, group=None, device=None):
+        self.runner, self.group, self.device = runner, group, device
+        self.rank, self.world = _world(group)
+        self.npairs = None
+
+    def process(self, gather=True):
+        import copy
+        r = self.runner
+        cat = r.ParticleSnapshot.cat
+        ranges = index_split(len(cat), self.world)
+        a, b = ranges[self.rank]
+        part = copy.copy(r.ParticleSnapshot)
+        part.cat = cat[a:b]
+        local = type(r)(r.HaloNDCatalog, part, r.epsilon_max, r.model, r.mass_def, verbose=False,
+                        device=self.device)
+        out = local.process()
+        pairs = torch.tensor([local.npairs], dtype=torch.int64,
+                             device="cuda" if dist.get_backend(self.group) == "nccl" else "cpu")
+        dist.all_reduce(pairs, group=self.group)
+        self.npairs = int(pairs.item())
+        if not gather:
+            return out
+        parts = [None] * self.world
+        dist.all_gather_object(parts, out, group=self.group)
+        return np.concatenate(parts)

@@ -1,0 +1,52 @@
+"""torchrun --nproc-per-node N scripts/check_sharded.py : sharded runners (NCCL) vs the single-GPU runners."""
+import os
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+import torch.distributed as dist
+from oracle import ref_shim
+
+ref_shim.install()
+import baryonification_b200 as bf
+from baryonification_b200 import sharding as sh, synthetic as syn
+
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+nside = int(sys.argv[1]) if len(sys.argv) > 1 else 512
+nh = int(sys.argv[2]) if len(sys.argv) > 2 else 20000
+cfg = syn.config_shell(nside=nside, nhalo=nh)
+ok = True
+for name, cls, model in (("BaryonifyShell", bf.BaryonifyShell, cfg["model"]), ("PaintProfilesShell", bf.PaintProfilesShell, cfg["paint_model"])):
+    single = cls(cfg["catalog"], cfg["field"], cfg["epsilon_max"], model, verbose=False, device=local)
+    want = single.process()
+    sharded = sh.ShardedShell(cls(cfg["catalog"], cfg["field"], cfg["epsilon_max"], model, verbose=False), device=local)
+    sharded.process()
+    torch.cuda.synchronize(); dist.barrier()
+    t0 = time.perf_counter()
+    got = sharded.process()
+    dt = time.perf_counter() - t0
+    same_pairs = sharded.npairs == single.npairs
+    err = np.max(np.abs(got - want)) / np.max(np.abs(want))
+    exact = np.array_equal(got, want)
+    if rank == 0:
+        print(f"{name}: world {world} pairs {sharded.npairs} (single {single.npairs}) relerr {err:.2e} bit-identical {exact} "
+              f"sharded process() {dt*1e3:.1f} ms", flush=True)
+    ok &= same_pairs and err < 1e-12 and (exact or name == "BaryonifyShell")
+scfg = syn.config_snapshot(npart_side=128, nhalo=20000, dim=3)
+single = bf.BaryonifySnapshot(scfg["catalog"], scfg["field"], scfg["epsilon_max"], scfg["model"], verbose=False, device=local)
+want = single.process()
+ss = sh.ShardedSnapshot(bf.BaryonifySnapshot(scfg["catalog"], scfg["field"], scfg["epsilon_max"], scfg["model"], verbose=False), device=local)
+got = ss.process()
+exact = all(np.array_equal(got[k], want[k]) for k in want.dtype.names)
+if rank == 0:
+    print(f"BaryonifySnapshot: world {world} pairs {ss.npairs} (single {single.npairs}) bit-identical {exact}", flush=True)
+ok &= exact and ss.npairs == single.npairs
+dist.barrier()
+dist.destroy_process_group()
+if rank == 0:
+    print("SHARDED CHECK", "OK" if ok else "FAILED", flush=True)
+sys.exit(0 if ok else 1)

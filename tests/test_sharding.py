@@ -1,0 +1,153 @@
+"""CPU: the N > 1 host logic of baryonification_b200.sharding with world_size-2/3 gloo process groups.
+
+The kernels cannot run here (no GPU, and the product has no CPU fallback), so every rank produces its LOCAL
+stage results with the CPU oracle (test infrastructure) and the product's partitioning + collectives
+(``band_split``, ``halos_touching_bands``, ``exchange_boundary``, ``gather_slices``, ``index_split``) turn them into
+the global answer, which must equal the single-process oracle result."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from baryonification_b200 import sharding as sh, synthetic as syn
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _run(fn, world, *args):
+    port = _free_port()
+    mp.spawn(_entry, args=(world, port, fn, args), nprocs=world, join=True)
+
+
+def _entry(rank, world, port, fn, args):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import ref_shim
+        ref_shim.install()
+        fn(rank, world, *args)
+    finally:
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------ partitions (single process)
+@pytest.mark.parametrize("nside,world", [(1, 1), (4, 2), (64, 3), (4096, 8), (1024, 5)])
+def test_band_split_covers_sphere_with_balanced_pixel_counts(nside, world):
+    bands = sh.band_split(nside, world)
+    assert bands[0][0] == 0 and all(bands[i][1] == bands[i + 1][0] for i in range(world - 1))
+    ranges = [sh.band_pixel_range(nside, *b) for b in bands]
+    assert ranges[0][0] == 0 and ranges[-1][1] == 12 * nside * nside
+    assert all(ranges[i][1] == ranges[i + 1][0] and ranges[i][1] > ranges[i][0] for i in range(world - 1))
+    if nside >= 64:
+        n = np.array([b - a for a, b in ranges], dtype=float)
+        assert n.max() / n.min() < 1.2
+
+
+def test_index_split():
+    assert sh.index_split(10, 3) == [(0, 3), (3, 6), (6, 10)]
+    assert sh.index_split(2, 4) == [(0, 0), (0, 1), (1, 1), (1, 2)]
+
+
+@pytest.mark.parametrize("nside,world,eps", [(32, 3, 20.0), (16, 2, 1.0), (64, 5, 40.0)])
+def test_halo_replication_mask_never_drops_a_contributing_halo(nside, world, eps):
+    from oracle import healpix as ohp, runners as orc
+    cfg = syn.config_shell(nside=nside, nhalo=400, epsilon_max=eps)
+    o = orc.BaryonifyShell(cfg["catalog"], cfg["field"], eps, cfg["model"])._halo_scalars()
+    bands = sh.band_split(nside, world)
+    kept_total = 0
+    for lo, hi in bands:
+        first, last = sh.band_pixel_range(nside, lo, hi)
+        keep = sh.halos_touching_bands(o["vec"][:, 2], o["radius"], nside, lo, hi)
+        kept_total += keep.sum()
+        for j in np.flatnonzero(~keep):
+            pix = ohp.query_disc(nside, o["vec"][j], o["radius"][j])
+            if pix.size < 4:  # HealpixRunner.py:309-310
+                pix = ohp.get_interp_weights(nside, cfg["catalog"].cat["ra"][j], cfg["catalog"].cat["dec"][j], lonlat=True)[0]
+            assert not np.any((pix >= first) & (pix < last)), j
+    if eps <= 20 and nside >= 32:
+        assert kept_total < world * 400  # and it does prune
+
+
+# ------------------------------------------------------------------ collectives under gloo
+def _baryonify_ranks(rank, world, nside, eps):
+    from oracle import runners as orc
+    cfg = syn.config_shell(nside=nside, nhalo=300, epsilon_max=eps)
+    ref_r = orc.BaryonifyShell(cfg["catalog"], cfg["field"], eps, cfg["model"])
+    off = ref_r.offsets() * 40.0  # exaggerate the displacements so that mass crosses the shard boundaries
+    orig = np.ascontiguousarray(cfg["field"].map)
+    npix = orig.size
+    want = np.zeros(npix)
+    orc._lib().bfo_regrid_shell_range(nside, 0, npix, orig, off, want)
+    bands = sh.band_split(nside, world)
+    ranges = [sh.band_pixel_range(nside, *b) for b in bands]
+    first, last = ranges[rank]
+    local = np.zeros(npix)
+    orc._lib().bfo_regrid_shell_range(nside, first, last, orig, off, local)  # this rank's own pixels only
+    crossing = torch.tensor([np.count_nonzero(local[:first]) + np.count_nonzero(local[last:])])
+    dist.all_reduce(crossing)
+    assert int(crossing) > 0  # some mass does cross a shard boundary, so the exchange is exercised
+    acc = torch.from_numpy(local)
+    own = sh.exchange_boundary(acc, ranges)
+    assert own.shape[0] == last - first
+    full = sh.gather_slices(own, ranges).numpy()
+    # a pixel gets (own deposits) + (ghost deposits): two partial sums instead of one serial sum -> last-bit changes only
+    assert np.allclose(full, want, rtol=1e-13, atol=1e-13 * want.max())
+    assert abs(full.sum() - orig.sum()) / orig.sum() < 1e-12
+    sums = torch.tensor([float(own.sum())], dtype=torch.float64)
+    dist.all_reduce(sums)
+    assert abs(float(sums) - orig.sum()) / orig.sum() < 1e-12
+
+
+@pytest.mark.parametrize("world,nside,eps", [(2, 16, 20.0), (3, 32, 20.0)])
+def test_boundary_mass_exchange_and_gather_match_single_process(world, nside, eps):
+    _run(_baryonify_ranks, world, nside, eps)
+
+
+def _paint_ranks(rank, world, nside):
+    from oracle import runners as orc
+    cfg = syn.config_shell(nside=nside, nhalo=200, zero_map=True)
+    want = orc.PaintProfilesShell(cfg["catalog"], cfg["field"], cfg["epsilon_max"], cfg["paint_model"]).process()
+    ranges = [sh.band_pixel_range(nside, *b) for b in sh.band_split(nside, world)]
+    first, last = ranges[rank]
+    # pixel-owner sharding: the rank's slice is complete on its own (every halo that touches it is replicated to it)
+    own = torch.from_numpy(want[first:last].copy())
+    full = sh.gather_slices(own, ranges).numpy()
+    assert np.array_equal(full, want)
+    off3 = torch.from_numpy(np.stack([want[first:last]] * 3, axis=1).copy())  # [n, 3] slices gather too
+    assert np.array_equal(sh.gather_slices(off3, ranges).numpy()[:, 1], want)
+
+
+def test_pixel_owner_gather_is_exact():
+    _run(_paint_ranks, 2, 16)
+
+
+def _snapshot_ranks(rank, world):
+    from oracle import runners as orc
+    cfg = syn.config_snapshot(npart_side=12, nhalo=80, dim=3, epsilon_max=5.0, L=100.0)
+    want = orc.BaryonifySnapshot(cfg["catalog"], cfg["field"], 5.0, cfg["model"]).process()
+
+    class OracleRunner(orc.BaryonifySnapshot):  # stands in for the GPU runner: same constructor contract
+        def __init__(self, cat, snap, eps, model, mass_def=None, verbose=True, device=None):
+            super().__init__(cat, snap, eps, model, mass_def, verbose)
+
+    r = OracleRunner(cfg["catalog"], cfg["field"], 5.0, cfg["model"])
+    got_r = sh.ShardedSnapshot(r)
+    got = got_r.process()
+    assert got.dtype == want.dtype and got.shape == want.shape
+    for k in want.dtype.names:
+        assert np.array_equal(got[k], want[k]), k  # particle-centric: sharding by index changes nothing
+    ref_pairs = orc.BaryonifySnapshot(cfg["catalog"], cfg["field"], 5.0, cfg["model"])
+    ref_pairs.process()
+    assert got_r.npairs == ref_pairs.npairs
+
+
+def test_snapshot_index_sharding_is_exact():
+    _run(_snapshot_ranks, 2)
