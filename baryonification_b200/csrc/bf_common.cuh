@@ -67,6 +67,50 @@ __device__ __forceinline__ int bf_find_cell(const bf_raxis &ax, double x) {
     return k;
 }
 
+// Same cell with one corrective step each way (enough whenever the uniform-grid guess is within +-1 of the
+// bisection cell, which holds for np.geomspace axes); falls back to the search loops otherwise.
+__device__ __forceinline__ int bf_find_cell_fast(const bf_raxis &ax, double x) {
+    int k = (int)((x - ax.g0) * ax.inv_dx);
+    k = max(0, min(k, ax.nr - 2));
+    k -= (k > 0 && x < ax.g[k]) ? 1 : 0;
+    k += (k < ax.nr - 2 && x >= ax.g[k + 1]) ? 1 : 0;
+    if (x < ax.g[k] || (k < ax.nr - 2 && x >= ax.g[k + 1])) {  // non-uniform axis: search
+        while (k > 0 && x < ax.g[k]) --k;
+        while (k < ax.nr - 2 && x >= ax.g[k + 1]) ++k;
+    }
+    return k;
+}
+
+// ------------------------------------------------------------------------------------------
+// ln(x) for finite x > 0 from a 128-entry shared-memory table: x = 2^e m, m in [1, 2); the top 7 mantissa
+// bits pick c with |m / c - 1| <= 2^-8, and ln m = ln c' + log1p(r), r = m * (1/c)' - 1 (one FMA, exact for the
+// ROUNDED reciprocal, whose own logarithm the table stores), log1p by its degree-6 series (truncation 2e-18).
+// Absolute error ~2e-16 * (1 + |e|): the table coordinate ln r only needs ~1e-13.  ~14 fp64 instructions
+// instead of the ~80 of the correctly rounded library log.  x = 0 or subnormal gives a large negative number
+// (below any table), which is all the callers need.
+// ------------------------------------------------------------------------------------------
+#define BF_LOGTAB 128
+__device__ __forceinline__ void bf_logtab_init(double2 *tab, int t, int nthreads) {
+    for (int i = t; i < BF_LOGTAB; i += nthreads) {
+        double ic = 1.0 / (1.0 + ((double)i + 0.5) / (double)BF_LOGTAB);
+        tab[i] = make_double2(ic, -log(ic));
+    }
+}
+
+__device__ __forceinline__ double bf_fastlog(const double2 *__restrict__ tab, double x) {
+    const int hi = __double2hiint(x);
+    const int e = (hi >> 20) - 1023;
+    const double m = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(x));
+    const double2 t = tab[(hi >> 13) & (BF_LOGTAB - 1)];
+    const double r = fma(m, t.x, -1.0);
+    double p = fma(r, -1.0 / 6.0, 0.2);
+    p = fma(r, p, -0.25);
+    p = fma(r, p, 1.0 / 3.0);
+    p = fma(r, p, -0.5);
+    p = fma(r, p, 1.0);
+    return fma((double)e, 0.693147180559945309417232121458, fma(r, p, t.y));
+}
+
 // value of one collapsed row at ln r = x; NaN outside the table (fill_value).  The two-product form
 // keeps scipy's inf/NaN propagation: a zero weight still multiplies (0 * -inf = NaN).
 __device__ __forceinline__ double bf_row_lerp(const bf_raxis &ax, const double *__restrict__ row, double x) {

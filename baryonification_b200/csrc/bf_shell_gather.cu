@@ -25,7 +25,12 @@
 
 #define GT_WARPS BF_BAND_RINGS
 #define GT_THREADS (32 * GT_WARPS)
-#define GT_CMAX 256
+#ifndef GT_CMAX
+#define GT_CMAX 192
+#endif
+#ifndef GT_MINBLOCKS
+#define GT_MINBLOCKS 4
+#endif
 
 struct gather_args {
     bf_hpx h;
@@ -79,11 +84,12 @@ __device__ __forceinline__ unsigned warp_transpose32(unsigned x, int lane) {
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(GT_THREADS, 3) gather_kernel(gather_args A) {
+__global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather_args A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     gather_smem &sm = *reinterpret_cast<gather_smem *>(smem_raw);
     double *g_s = reinterpret_cast<double *>(smem_raw + sizeof(gather_smem));
     double *ig_s = g_s + A.ax.nr;
+    double2 *logtab = reinterpret_cast<double2 *>((reinterpret_cast<uintptr_t>(ig_s + A.ax.nr) + 15) & ~(uintptr_t)15);
 
     const bf_hpx &h = A.h;
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
@@ -113,6 +119,7 @@ __global__ void __launch_bounds__(GT_THREADS, 3) gather_kernel(gather_args A) {
     }
 
     for (int k = t; k < A.ax.nr; k += GT_THREADS) g_s[k] = A.ax.g[k];
+    bf_logtab_init(logtab, t, GT_THREADS);
     __syncthreads();
     for (int k = t; k < A.ax.nr - 1; k += GT_THREADS) ig_s[k] = 1.0 / (g_s[k + 1] - g_s[k]);
     bf_raxis ax = A.ax;
@@ -188,10 +195,10 @@ __global__ void __launch_bounds__(GT_THREADS, 3) gather_kernel(gather_args A) {
                         hm &= hm - 1u;
                         double dx = v[0] - sm.c0[c], dy = v[1] - sm.c1[c], dz = v[2] - sm.c2[c];
                         double d2 = fma(dz, dz, fma(dy, dy, dx * dx));
-                        double x = fma(0.5, log(d2), sm.lnDa[c]);
+                        double x = fma(0.5, bf_fastlog(logtab, d2), sm.lnDa[c]);
                         double val = nan("");
                         if (x >= ax.g0 && x <= ax.glast) {
-                            int k = bf_find_cell(ax, x);
+                            int k = bf_find_cell_fast(ax, x);
                             double tt = (x - g_s[k]) * ig_s[k];
                             const double *row = sm.row[c];
                             val = fma(__ldg(row + k + 1), tt, __ldg(row + k) * (1.0 - tt));
@@ -280,7 +287,7 @@ extern "C" int bf_shell_gather(int64_t nside, int mode, const bf_shell_halos *S,
     A.pix_base = pix_base;
     A.accumulate = accumulate;
     A.npairs = npairs;
-    size_t smem = sizeof(gather_smem) + 2 * sizeof(double) * (size_t)T->nr;
+    size_t smem = sizeof(gather_smem) + 2 * sizeof(double) * (size_t)T->nr + sizeof(double2) * BF_LOGTAB + 16;
     BF_REQUIRE(smem <= 200 * 1024, "table r-axis too long for the shared-memory stage");
     unsigned grid = (unsigned)((band_hi - band_lo) * BF_MAX_COLS);
     if (mode == 0) {

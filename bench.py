@@ -106,23 +106,6 @@ def make_inputs(args):
     return syn.config_shell(nside=args.nside, nhalo=args.nhalo)
 
 
-def band_split(nside, world):
-    """Ring-band ranges with (nearly) equal pixel counts."""
-    import ctypes as C
-    from baryonification_b200 import _lib
-    lib = _lib.load()
-    nb = lib.bf_shell_num_bands(nside)
-    npix = 12 * nside * nside
-    f, l = C.c_int64(), C.c_int64()
-    starts = np.empty(nb + 1, dtype=np.int64)
-    for b in range(nb + 1):
-        lib.bf_shell_band_pixel_range(nside, 0, b, C.byref(f), C.byref(l))
-        starts[b] = l.value
-    cuts = [int(np.searchsorted(starts, npix * r / world)) for r in range(world)] + [nb]
-    cuts[0] = 0
-    return [(cuts[r], cuts[r + 1]) for r in range(world)]
-
-
 def cpu_baseline(cfg, args, nthreads):
     """Oracle port (C, OpenMP over halos) on a bounded sample; regrid timed on a pixel sub-range; both scaled."""
     from oracle import runners as orc
@@ -197,12 +180,18 @@ def run_ours(args, rank, local_rank, world):
     cfg = make_inputs(args)
     nside, eps = args.nside, cfg["epsilon_max"]
     npix = 12 * nside * nside
-    bands = band_split(nside, world)[rank] if world > 1 else None
+    from baryonification_b200 import sharding as sh
+    all_bands = sh.band_split(nside, world)
+    ranges = [sh.band_pixel_range(nside, lo, hi) for lo, hi in all_bands]
+    bands = all_bands[rank] if world > 1 else None
     if world > 1 and args.variant != "gather":
         raise SystemExit("multi-GPU sharding needs the gather variant")
 
     # ---- inputs resident in HBM -------------------------------------------------------------------------
     s = host.shell_scalars(cfg["catalog"], cfg["catalog"].cosmo, default_mass_def(), eps, cfg["model"], True)
+    if world > 1:  # halos replicated to every shard their footprint overlaps (catalogue order kept)
+        keep = sh.halos_touching_bands(s["vec"][:, 2], s["radius"], nside, *bands)
+        s = sh._subset(s, keep)
     eng = engine.ShellEngine(nside, engine.BARYONIFY, displacement_host_table(cfg["model"]), s, dev,
                              variant=args.variant, bands=bands).upload()
     orig_host = np.ascontiguousarray(cfg["field"].map)
@@ -210,6 +199,7 @@ def run_ours(args, rank, local_rank, world):
     nloc = eng.pix_last - eng.pix_first
     off = dv.empty((nloc, 3), dev=dev)
     new_d = dv.zeros(npix, dev=dev)
+    full_d = dv.zeros(npix, dev=dev) if world > 1 else new_d
 
     ev = lambda: torch.cuda.Event(enable_timing=True)
     acc_ms = []
@@ -225,8 +215,9 @@ def run_ours(args, rank, local_rank, world):
         b.record()
         eng.regrid(orig_d, off, new_d, method=args.regrid)
         c.record()
-        if world > 1:
-            dist.all_reduce(new_d)
+        if world > 1:  # boundary mass exchange + gather of the finished band slices (the only collectives)
+            own = sh.exchange_boundary(new_d, ranges)
+            sh.gather_slices(own, ranges, out=full_d)
         if timed:
             acc_ms.append((a, b))
             rg_ms.append((b, c))
@@ -256,7 +247,7 @@ def run_ours(args, rank, local_rank, world):
         dist.all_reduce(pairs)
     ms_step, ms_acc = float(ms[0]), float(ms[1])
     npairs = int(pairs[0])
-    mass_err = abs(float(new_d.sum()) / float(orig_host.sum()) - 1.0)
+    mass_err = abs(float(full_d.sum()) / float(orig_host.sum()) - 1.0)
     ms_rg = float(np.mean([a.elapsed_time(b) for a, b in rg_ms]))
     # the other re-binning variant, timed alongside (not part of `value`)
     other = "atomic" if args.regrid == "sorted" else "sorted"
@@ -268,7 +259,7 @@ def run_ours(args, rank, local_rank, world):
     ob.record()
     torch.cuda.synchronize(dev)
     ms_rg_other = oa.elapsed_time(ob)
-    alt_diff = float((new_alt - new_d).abs().max() / new_d.abs().max()) if world == 1 else None
+    alt_diff = float((new_alt - new_d).abs().max() / new_d.abs().max()) if world == 1 else None  # (sharded: new_d holds ghosts)
     del new_alt
 
     # ---- e2e through the public API: host buffers in, host map out ---------------------------------------------
@@ -301,7 +292,7 @@ def run_ours(args, rank, local_rank, world):
             eng.upload()
             step(False)
             if rank == 0:
-                pin_out.copy_(new_d, non_blocking=True)
+                pin_out.copy_(full_d, non_blocking=True)
             barrier()
             if i > 0:
                 ts.append(time.perf_counter() - t0)
