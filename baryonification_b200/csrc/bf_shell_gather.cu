@@ -198,8 +198,14 @@ __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather
                         double x = fma(0.5, bf_fastlog(logtab, d2), sm.lnDa[c]);
                         double val = nan("");
                         if (x >= ax.g0 && x <= ax.glast) {
-                            int k = bf_find_cell_fast(ax, x);
-                            double tt = (x - g_s[k]) * ig_s[k];
+                            int k = (int)((x - ax.g0) * ax.inv_dx);  // uniform-grid guess, verified against the stored grid
+                            k = max(0, min(k, ax.nr - 2));
+                            double gk = g_s[k];
+                            if (x < gk || (x >= g_s[k + 1] && k < ax.nr - 2)) {  // rounding at a node / non-uniform axis
+                                k = bf_find_cell(ax, x);
+                                gk = g_s[k];
+                            }
+                            double tt = (x - gk) * ig_s[k];
                             const double *row = sm.row[c];
                             val = fma(__ldg(row + k + 1), tt, __ldg(row + k) * (1.0 - tt));
                         }
