@@ -45,20 +45,17 @@ class DefaultRunnerGrid:
         keys = vars(self.model).get("p_keys", [])
         if len(keys) > 0:
             raise NotImplementedError(f"property-keyed tables {keys} are not yet supported by the B200 runners")
-        if self.use_ellipticity:
-            if not self.GriddedMap.is2D:  # Map2DRunner.py:565 / :790
-                if baryonify:
-                    raise NotImplementedError("Currently not able to ellipticities with 3D maps.")
-                raise ValueError("use_ellipticity is not implemented for 3D maps")
-            raise NotImplementedError("use_ellipticity = True is not yet supported by the B200 grid runners")
         G = self.GriddedMap
+        rmat = host.grid_rmat(self.HaloNDCatalog, G, self.use_ellipticity, baryonify)  # 3-D raises (:565 / :790)
         table = dv.DeviceTable(table_host, dev=dev)
         s = host.grid_scalars(self.HaloNDCatalog, G, self.mass_def, self.epsilon_max, self.model, baryonify)
         t = {k: dv.to_dev(s[k], dev=dev) for k in ("pos", "cut", "lnr_shift", "z_in", "M_in")}
         t["Nsize"] = dv.to_dev(s["Nsize"], dtype=np.int64, dev=dev)
         rows = table.collapse(t["z_in"], t["M_in"])
+        t["Rmat"] = dv.to_dev(rmat, dev=dev) if rmat is not None else None
         desc = _lib.GridHalos(t["pos"].data_ptr(), t["Nsize"].data_ptr(), t["cut"].data_ptr(),
-                              t["lnr_shift"].data_ptr(), rows.data_ptr(), s["cut"].size)
+                              t["lnr_shift"].data_ptr(), rows.data_ptr(),
+                              t["Rmat"].data_ptr() if rmat is not None else None, s["cut"].size)
         bins = dv.to_dev(G.bins, dev=dev)
         return table, s, desc, bins, (t, rows)
 

@@ -34,7 +34,7 @@ class ShellHalos(C.Structure):
 
 class GridHalos(C.Structure):
     _fields_ = [("pos", C.c_void_p), ("Nsize", C.c_void_p), ("cut", C.c_void_p), ("lnr_shift", C.c_void_p),
-                ("rows", C.c_void_p), ("nh", _i64)]
+                ("rows", C.c_void_p), ("Rmat", C.c_void_p), ("nh", _i64)]
 
 
 class SnapHalos(C.Structure):

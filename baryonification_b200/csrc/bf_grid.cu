@@ -64,6 +64,9 @@ __global__ void __launch_bounds__(GR_THREADS) grid_atomic_kernel(i64 npix, const
         }
         const double *row = G.rows + j * (i64)ax.nr;
         double cut = G.cut[j], shift = (MODE == 0) ? G.lnr_shift[j] : 0.0;
+        const bool ell = (DIM == 2) && (G.Rmat != nullptr);  // build_Rmat shear (:525-530 / :758-763)
+        double R00 = 1, R01 = 0, R10 = 0, R11 = 1;
+        if (ell) { R00 = G.Rmat[4 * j]; R01 = G.Rmat[4 * j + 1]; R10 = G.Rmat[4 * j + 2]; R11 = G.Rmat[4 * j + 3]; }
         i64 total = (DIM == 2) ? W * W : W * W * W;
         for (i64 k = threadIdx.x; k < total; k += GR_THREADS) {
             i64 ia, ib, ic = 0;
@@ -75,16 +78,21 @@ __global__ void __launch_bounds__(GR_THREADS) grid_atomic_kernel(i64 npix, const
             double r = (DIM == 3) ? sqrt(gx * gx + gy * gy + gz * gz) : sqrt(gx * gx + gy * gy);
             i64 cell = wrap_once(cen[0] - w + ia, npix) * npix + wrap_once(cen[1] - w + ib, npix);
             if (DIM == 3) cell = cell * npix + wrap_once(cen[2] - w + ic, npix);
-            double v = bf_row_lerp(ax, row, log(r) - shift);
+            double rt = r;  // radius handed to the model; the unit vector below keeps the round radius (:520-522)
+            if (ell) {
+                double ex = gx * R00 + gy * R10, ey = gx * R01 + gy * R11;  // coords @ Rmat
+                rt = sqrt(ex * ex + ey * ey);
+            }
+            double v = bf_row_lerp(ax, row, log(rt) - shift);
             if (MODE == 0) {
-                v = (r < cut) ? v : 0.0;  // BaryonCorrection.py:381-382
+                v = (rt < cut) ? v : 0.0;  // BaryonCorrection.py:381-382
                 double offset = v / res;  // :534 / :577
                 atomicAdd(out + DIM * cell + 0, offset * (gx / r));
                 atomicAdd(out + DIM * cell + 1, offset * (gy / r));
                 if (DIM == 3) atomicAdd(out + DIM * cell + 2, offset * (gz / r));
             } else {
                 v = exp(v);
-                if (bf_finite(v) && (r < cut) && v != 0.0) atomicAdd(out + cell, v);  // :803-810
+                if (bf_finite(v) && (rt < cut) && v != 0.0) atomicAdd(out + cell, v);  // :803-810
             }
             ++my_pairs;
         }
@@ -103,6 +111,7 @@ static int launch_grid(int dim, int64_t npix, const double *bins, double res, co
     BF_REQUIRE(G && G->nh >= 0, "halo record");
     if (G->nh == 0) return BF_OK;
     BF_REQUIRE(G->pos && G->Nsize && G->cut && G->rows && (MODE == 1 || G->lnr_shift), "null per-halo array");
+    BF_REQUIRE(dim == 2 || G->Rmat == nullptr, "ellipticity (Rmat) is only defined for 2-D grids");
     i64 grid = (i64)bf_sm_count() * 8;
     if (grid > G->nh) grid = G->nh;
     cudaStream_t s = (cudaStream_t)stream;

@@ -138,6 +138,32 @@ def shell_scalars(catalog, cosmo_dict, mass_def, epsilon_max, model, baryonify: 
     return chunked(part, len(cat))
 
 
+def _native(a):
+    a = np.asarray(a)
+    return a.astype(a.dtype.newbyteorder("=")) if a.dtype.byteorder == ">" else a
+
+
+def shear_matrices(cat):
+    """Per-halo 2x2 matrices of ``build_Rmat`` (Map2DRunner.py:275-344, the galsim-style shear of axis ratio
+    ``q_ell`` along ``A_ell``) for all halos at once, [n, 4] row-major.  Same expressions and dtypes as the
+    reference's per-halo code (the catalogue columns are float32, so eta = -log(q) and the normalisations are
+    float32 operations)."""
+    q = _native(cat["q_ell"])
+    A = _native(cat["A_ell"])
+    assert np.all(q > 0), "The axis ratio in halo %d is not positive" % int(np.argmin(q > 0))
+    A = A / np.sqrt(np.sum(A ** 2, axis=1))[:, None]                      # :491 / :728
+    A = A / np.sqrt(A[:, 0] * A[:, 0] + A[:, 1] * A[:, 1])[:, None]       # build_Rmat: A /= np.linalg.norm(A)
+    beta = np.arccos(A[:, 0].astype(np.float64) * 1.0 + A[:, 1].astype(np.float64) * 0.0)  # np.dot(A, [1, 0])
+    eta = -np.log(q)
+    etasq = eta * eta
+    with np.errstate(divide="ignore", invalid="ignore"):
+        eta2g = np.where(eta > 1e-4, np.tanh(0.5 * eta) / eta, 0.5 + etasq * ((-1 / 24) + etasq * (1 / 240)))
+    g = (eta2g * eta) * np.exp(2j * beta)
+    g1, g2 = g.real, g.imag
+    det = np.sqrt(1 - np.abs(g) ** 2)
+    return np.ascontiguousarray(np.stack([(1 + g1) / det, g2 / det, g2 / det, (1 - g1) / det], axis=1))
+
+
 def nd_positions(cat, dim):
     return np.ascontiguousarray(np.stack([np.asarray(cat[k], dtype=np.float64) for k in ("x", "y", "z")[:dim]], axis=1))
 
@@ -166,6 +192,17 @@ def grid_scalars(catalog, gmap, mass_def, epsilon_max, model, baryonify: bool):
     dim = 2 if gmap.is2D else 3
     return dict(pos=nd_positions(cat, dim), Nsize=Nsize, cut=np.asarray(cut, dtype=np.float64), lnr_shift=shift,
                 z_in=np.log(1 / a), M_in=log_native(M), dim=dim, a=a_j)
+
+
+def grid_rmat(catalog, gmap, use_ellipticity, baryonify):
+    """Shear matrices for the 2-D grid runners, or None; 3-D raises like the reference (:565 / :790)."""
+    if not use_ellipticity:
+        return None
+    if not gmap.is2D:
+        if baryonify:
+            raise NotImplementedError("Currently not able to ellipticities with 3D maps.")
+        raise ValueError("use_ellipticity is not implemented for 3D maps")
+    return shear_matrices(catalog.cat)
 
 
 def snapshot_scalars(catalog, snap, mass_def, epsilon_max, model):

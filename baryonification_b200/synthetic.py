@@ -102,15 +102,23 @@ def grid_bins(npix, L):
 # --------------------------------------------------------------------------------------
 # the five BASELINE.json configurations (sizes overridable so tests can shrink them)
 # --------------------------------------------------------------------------------------
-def config_grid(npix=512, nhalo=2000, dim=2, L=500.0 / 0.7, seed=SEED0 + 1, epsilon_max=20.0):
+def config_grid(npix=512, nhalo=2000, dim=2, L=500.0 / 0.7, seed=SEED0 + 1, epsilon_max=20.0, ellipticity=False):
     halos = box_halos(nhalo, seed, L, dim=dim)
+    if ellipticity:  # q_ell axis ratios, A_ell major-axis directions (+ c_ell in 3-D), Map2DRunner.py:266-272
+        rng = np.random.default_rng(seed + 77)
+        halos["q_ell"] = rng.uniform(0.4, 1.0, nhalo)
+        halos["q_ell"][:3] = [1.0, 0.99995, 0.5]  # round halo, the small-eta series branch, a flat one
+        halos["A_ell"] = rng.normal(size=(nhalo, dim))
+        if dim == 3:
+            halos["c_ell"] = rng.uniform(0.3, 1.0, nhalo)
     field = lognormal_field((npix,) * dim, seed + 1000)
     cat = HaloNDCatalog(**halos)
     gmap = GriddedMap(map=field, redshift=halos["redshift"], bins=grid_bins(npix, L), cosmo=COSMO)
     z = halos["redshift"]
     model = displacement_model(z * 0.5, z * 2.0, epsilon_max)
     pmodel = profile_model(z * 0.5, z * 2.0)
-    return dict(catalog=cat, field=gmap, model=model, paint_model=pmodel, epsilon_max=epsilon_max)
+    return dict(catalog=cat, field=gmap, model=model, paint_model=pmodel, epsilon_max=epsilon_max,
+                use_ellipticity=bool(ellipticity))
 
 
 def config_shell(nside=1024, nhalo=100_000, seed=SEED0 + 2, epsilon_max=20.0, zero_map=False, zero_beyond=None):

@@ -129,6 +129,8 @@ typedef struct {
     const double *cut;       /* baryonify: model cut; paint: R_j*epsilon_max (:804) */
     const double *lnr_shift;
     const double *rows;      /* [nh][nr] */
+    const double *Rmat;      /* optional [nh][4]: 2x2 shear matrix of build_Rmat (:275-344), row-major; 2-D only.
+                                The table radius becomes |(x, y) @ Rmat| (:525-530, :758-763); NULL = round halos */
     int64_t nh;
 } bf_grid_halos;
 

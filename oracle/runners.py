@@ -40,8 +40,8 @@ def _lib():
         L.bfo_regrid_shell.argtypes = [_i64, _dp, _dp, _dp]
         L.bfo_regrid_shell_range.argtypes = [_i64, _i64, _i64, _dp, _dp, _dp]
         L.bfo_grid_halos.restype = _i64
-        L.bfo_grid_halos.argtypes = ([C.c_int, C.c_int, _i64, _dp, C.c_double, _i64, _dp, _ip, _dp, _dp, _dp, _dp]
-                                     + _TAB + [_dp, C.c_int])
+        L.bfo_grid_halos.argtypes = ([C.c_int, C.c_int, _i64, _dp, C.c_double, _i64, _dp, _ip, _dp, _dp, _dp, _dp,
+                                      C.c_void_p] + _TAB + [_dp, C.c_int])
         L.bfo_grid_regrid.argtypes = [C.c_int, _i64, _dp, _dp, _dp]
         L.bfo_snapshot_offsets.restype = _i64
         L.bfo_snapshot_offsets.argtypes = ([C.c_int, _i64, _dp, C.c_double, _i64, _dp, _dp, C.c_double,
@@ -216,8 +216,47 @@ class _GridBase:
         self.mass_def = mass_def if mass_def is not None else _ccl().halos.massdef.MassDef(200, "critical")
         self.verbose, self.use_ellipticity, self.nthreads = verbose, use_ellipticity, nthreads
         self.npairs = None
-        if use_ellipticity:
-            raise NotImplementedError("oracle: ellipticity not restated yet")
+        if use_ellipticity:  # Map2DRunner.py:266-272
+            names = HaloNDCatalog.cat.dtype.names
+            assert "q_ell" in names, "The 'q_ell' column is missing, but you set use_ellipticity = True"
+            if not GriddedMap.is2D:
+                assert "c_ell" in names, "The 'c_ell' column is missing, but you set use_ellipticity = True"
+            assert "A_ell" in names, "The 'A_ell' column is missing, but you set use_ellipticity = True"
+
+    @staticmethod
+    def build_Rmat(A, q):
+        """Map2DRunner.py:275-344, 2-D branch, expression by expression (A, q keep the catalogue's float32)."""
+        A /= np.linalg.norm(A)
+        ref = np.array([1., 0.])
+        beta = np.arccos(np.dot(A, ref))
+        eta = -np.log(q)
+        if eta > 1e-4:
+            eta2g = np.tanh(0.5 * eta) / eta
+        else:
+            etasq = eta * eta
+            eta2g = 0.5 + etasq * ((-1 / 24) + etasq * (1 / 240))
+        g = eta2g * eta * np.exp(2j * beta)
+        g1, g2 = g.real, g.imag
+        det = np.sqrt(1 - np.abs(g) ** 2)
+        return np.array([[1 + g1, g2], [g2, 1 - g1]]) / det
+
+    def _rmat(self, baryonify):
+        """Per-halo shear matrices [n, 4] (row-major), or None.  3-D raises like the reference (:565 / :790)."""
+        if not self.use_ellipticity:
+            return None
+        if not self.GriddedMap.is2D:
+            if baryonify:
+                raise NotImplementedError("Currently not able to ellipticities with 3D maps.")
+            raise ValueError("use_ellipticity is not implemented for 3D maps")
+        cat = self.HaloNDCatalog.cat
+        out = np.empty((cat.size, 4))
+        for j in range(cat.size):
+            q_j = cat["q_ell"][j]  # :489-492 / :726-729
+            A_j = cat["A_ell"][j]
+            A_j = A_j / np.sqrt(np.sum(A_j ** 2))
+            assert q_j > 0, "The axis ratio in halo %d is not positive" % j
+            out[j] = self.build_Rmat(A_j, q_j).reshape(-1)
+        return out
 
     def _cosmo(self):
         ccl, c = _ccl(), self.cosmo  # Map2DRunner.py:456-460 (no w0)
@@ -248,8 +287,10 @@ class BaryonifyGrid(_GridBase):
         pos, dim = self._positions()
         T = displacement_table(self.model)
         off = np.zeros((G.map.size, dim))
+        rmat = self._rmat(True)
         self.npairs = _lib().bfo_grid_halos(dim, 0, G.Npix, _c(G.bins), float(G.res), n, pos, Nsize,
-                                            np.log(1 / a), _log_native(M), cut, shift, *T.args(), off,
+                                            np.log(1 / a), _log_native(M), cut, shift,
+                                            None if rmat is None else rmat.ctypes.data, *T.args(), off,
                                             self.nthreads)
         return off
 
@@ -282,8 +323,10 @@ class PaintProfilesGrid(_GridBase):
         pos, dim = self._positions()
         T = profile_table(self.model, "2D" if G.is2D else "3D")
         out = np.zeros(G.map.size)
+        rmat = self._rmat(False)
         self.npairs = _lib().bfo_grid_halos(dim, 1, G.Npix, _c(G.bins), float(G.res), n, pos, Nsize,
-                                            np.log(1 / a), _log_native(M), cut, np.zeros(n), *T.args(), out,
+                                            np.log(1 / a), _log_native(M), cut, np.zeros(n),
+                                            None if rmat is None else rmat.ctypes.data, *T.args(), out,
                                             self.nthreads)
         return out.reshape(G.map.shape)
 

@@ -44,6 +44,8 @@ def run(impl, kind, cfg, **kw):
     cls = {"shell_baryonify": "BaryonifyShell", "shell_paint": "PaintProfilesShell", "grid_baryonify": "BaryonifyGrid",
            "grid_paint": "PaintProfilesGrid", "snapshot": "BaryonifySnapshot"}[kind]
     model = cfg["paint_model"] if kind.endswith("paint") else cfg["model"]
+    if cfg.get("use_ellipticity"):
+        kw = dict(kw, use_ellipticity=True)
     r = getattr(impl, cls)(cfg["catalog"], cfg["field"], eps, model, verbose=False, **kw)
     out = r.process()
     if kind == "snapshot":

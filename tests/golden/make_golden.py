@@ -40,6 +40,8 @@ CASES = [
     ("grid3d_baryonify_24", "grid_baryonify", dict(npix=24, nhalo=40, dim=3, epsilon_max=8.0, L=100.0), {}),
     ("grid2d_paint_64", "grid_paint", dict(npix=64, nhalo=120, dim=2, epsilon_max=20.0), {}),
     ("grid3d_paint_24", "grid_paint", dict(npix=24, nhalo=40, dim=3, epsilon_max=8.0, L=100.0), {}),
+    ("grid2d_baryonify_ell_64", "grid_baryonify", dict(npix=64, nhalo=120, dim=2, epsilon_max=20.0, ellipticity=True), {}),
+    ("grid2d_paint_ell_64", "grid_paint", dict(npix=64, nhalo=120, dim=2, epsilon_max=20.0, ellipticity=True), {}),
     ("snapshot3d_16", "snapshot", dict(npart_side=16, nhalo=80, dim=3, epsilon_max=5.0, L=100.0), {}),
     ("snapshot2d_64", "snapshot", dict(npart_side=64, nhalo=60, dim=2, epsilon_max=5.0, L=300.0), {}),
 ]
@@ -87,11 +89,13 @@ def run_reference(bfg, kind, cfg):
     dim = 2 if getattr(cfg["field"], "is2D", False) else 3
     if kind == "grid_baryonify":
         r = bfg.BaryonifyGrid(rm.ref_nd_catalog(bfg, cfg["catalog"], dim), rm.ref_grid(bfg, cfg["field"]), eps,
-                              rm.ref_displacement_model(bfg, cfg["model"]), verbose=False)
+                              rm.ref_displacement_model(bfg, cfg["model"]), verbose=False,
+                              use_ellipticity=cfg.get("use_ellipticity", False))
         return {"out": r.process()}
     if kind == "grid_paint":
         r = bfg.PaintProfilesGrid(rm.ref_nd_catalog(bfg, cfg["catalog"], dim), rm.ref_grid(bfg, cfg["field"]), eps,
-                                  rm.ref_profile_model(bfg, cfg["paint_model"]), verbose=False)
+                                  rm.ref_profile_model(bfg, cfg["paint_model"]), verbose=False,
+                                  use_ellipticity=cfg.get("use_ellipticity", False))
         return {"out": r.process()}
     if kind == "snapshot":
         r = bfg.BaryonifySnapshot(rm.ref_nd_catalog(bfg, cfg["catalog"], dim), rm.ref_snapshot(bfg, cfg["field"]), eps,

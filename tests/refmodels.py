@@ -42,8 +42,9 @@ def ref_lightcone_catalog(bfg, cat):
 
 def ref_nd_catalog(bfg, cat, dim):
     c = cat.cat
+    extra = {k: c[k] for k in c.dtype.names if k not in ("M", "x", "y", "z")}  # q_ell, A_ell, ...
     return bfg.HaloNDCatalog(x=c["x"], y=c["y"], z=c["z"] if dim == 3 else None, M=c["M"],
-                             redshift=cat.redshift, cosmo=cat.cosmo)
+                             redshift=cat.redshift, cosmo=cat.cosmo, **extra)
 
 
 def ref_shell(bfg, shell):

@@ -171,21 +171,24 @@ def test_baryonify_shell_tiny_halo_fallback(gpu, variant):
     assert np.max(np.abs(off_got - off_ref)) < 1e-13
 
 
-@pytest.mark.parametrize("dim,npix,nhalo,eps", [(2, 256, 500, 20.0), (3, 64, 150, 8.0)])
-def test_grid_parity(gpu, dim, npix, nhalo, eps):
+@pytest.mark.parametrize("dim,npix,nhalo,eps,ell", [(2, 256, 500, 20.0, False), (3, 64, 150, 8.0, False),
+                                                     (2, 256, 500, 20.0, True)])
+def test_grid_parity(gpu, dim, npix, nhalo, eps, ell):
+    """ell: use_ellipticity = True with q_ell / A_ell columns (2-D only, Map2DRunner.py:525-530, :758-763)."""
     import baryonification_b200 as bf
     from baryonification_b200 import synthetic as syn
     from oracle import runners as orc
-    cfg = syn.config_grid(npix=npix, nhalo=nhalo, dim=dim, epsilon_max=eps, L=(500.0 / 0.7 if dim == 2 else 100.0))
-    got_r = bf.BaryonifyGrid(cfg["catalog"], cfg["field"], eps, cfg["model"], verbose=False)
-    ref_r = orc.BaryonifyGrid(cfg["catalog"], cfg["field"], eps, cfg["model"])
+    cfg = syn.config_grid(npix=npix, nhalo=nhalo, dim=dim, epsilon_max=eps, L=(500.0 / 0.7 if dim == 2 else 100.0),
+                          ellipticity=ell)
+    got_r = bf.BaryonifyGrid(cfg["catalog"], cfg["field"], eps, cfg["model"], ell, verbose=False)
+    ref_r = orc.BaryonifyGrid(cfg["catalog"], cfg["field"], eps, cfg["model"], ell)
     got, ref = got_r.process(), ref_r.process()
     assert got_r.npairs == ref_r.npairs and ref_r.npairs > 1000
     assert got.shape == ref.shape
     assert relmax(got, ref) < 1e-9
     assert abs(got.sum() - cfg["field"].map.sum()) / cfg["field"].map.sum() < MASS_RTOL
-    gp = bf.PaintProfilesGrid(cfg["catalog"], cfg["field"], eps, cfg["paint_model"], verbose=False)
-    rp = orc.PaintProfilesGrid(cfg["catalog"], cfg["field"], eps, cfg["paint_model"])
+    gp = bf.PaintProfilesGrid(cfg["catalog"], cfg["field"], eps, cfg["paint_model"], ell, verbose=False)
+    rp = orc.PaintProfilesGrid(cfg["catalog"], cfg["field"], eps, cfg["paint_model"], ell)
     g, r = gp.process(), rp.process()
     assert gp.npairs == rp.npairs
     assert np.array_equal(g != 0, r != 0)

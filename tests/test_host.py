@@ -139,3 +139,20 @@ def test_spline_eval_is_bit_identical_to_scipy_and_chunked_setup_to_serial(monke
     par = host.shell_scalars(*args)
     for k, v in serial.items():
         assert np.array_equal(v, par[k]) and par[k].flags.c_contiguous, k
+
+
+def test_shear_matrices_equal_per_halo_build_Rmat_and_3d_raises():
+    """host.shear_matrices (vectorised) == the reference's per-halo build_Rmat (Map2DRunner.py:275-344, restated in
+    oracle.runners) bit for bit; 3-D ellipticity raises the reference's exceptions (:565 / :790)."""
+    from oracle import runners as orc
+    cfg = syn.config_grid(npix=32, nhalo=1500, dim=2, ellipticity=True)
+    got = host.shear_matrices(cfg["catalog"].cat)
+    want = orc.BaryonifyGrid(cfg["catalog"], cfg["field"], 20.0, cfg["model"], use_ellipticity=True)._rmat(True)
+    assert np.array_equal(got, want)
+    assert np.array_equal(got[0], [1.0, 0.0, 0.0, 1.0])  # q = 1: identity
+    assert np.allclose(got[:, 0] * got[:, 3] - got[:, 1] * got[:, 2], 1.0, atol=1e-12)  # shear: unit determinant
+    cfg3 = syn.config_grid(npix=16, nhalo=10, dim=3, L=100.0, ellipticity=True)
+    with pytest.raises(NotImplementedError):
+        host.grid_rmat(cfg3["catalog"], cfg3["field"], True, True)
+    with pytest.raises(ValueError):
+        host.grid_rmat(cfg3["catalog"], cfg3["field"], True, False)

@@ -32,6 +32,8 @@ LIVE = [
     ("grid_paint", dict(npix=128, nhalo=300, dim=2, epsilon_max=20.0, seed=15)),
     ("grid_baryonify", dict(npix=32, nhalo=60, dim=3, epsilon_max=6.0, L=120.0, seed=16)),
     ("grid_paint", dict(npix=32, nhalo=60, dim=3, epsilon_max=6.0, L=120.0, seed=17)),
+    ("grid_baryonify", dict(npix=128, nhalo=300, dim=2, epsilon_max=20.0, seed=24, ellipticity=True)),
+    ("grid_paint", dict(npix=128, nhalo=300, dim=2, epsilon_max=20.0, seed=25, ellipticity=True)),
     ("snapshot", dict(npart_side=24, nhalo=150, dim=3, epsilon_max=5.0, L=100.0, seed=18)),
     ("snapshot", dict(npart_side=100, nhalo=100, dim=2, epsilon_max=5.0, L=300.0, seed=19)),
 ]
