@@ -32,6 +32,12 @@ sys.path.insert(0, ROOT)
 
 B_PAIR = 48.0      # algorithmic bytes per pair: RMW of 3 f64 offset components
 B_PIXEL = 104.0    # algorithmic bytes per pixel: map read 8 + offsets 24 + 4-neighbour RMW 64 + zero-init 8
+B_PARTICLE = 88.0  # snapshot: read (M,x,y,z) 32 + offsets 24 + write 32
+B_SNAP_PAIR = 72.0 # snapshot: 24 B particle xyz read + 48 B offsets RMW per pair
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE gather_kernel<1> launch at the default workload, N = 1, from the
+# ncu --set full capture summarised in profiles/ (the kernel writes every pixel once; it never re-reads accumulators)
+GATHER_TRAFFIC_BYTES = 7.07e9
+SNAP_TRAFFIC_BYTES = 11.66e9
 
 
 def parse():
@@ -40,6 +46,10 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="shell", choices=["shell", "snapshot"],
+                    help="shell = BaryonifyShell NSIDE 4096 / 1e6 halos (the metric's configuration, default); "
+                         "snapshot = BaryonifySnapshot 512^3 particles / 1e5 halos (north_star's second target)")
+    ap.add_argument("--npart-side", type=int, default=512)
     ap.add_argument("--nside", type=int, default=4096)
     ap.add_argument("--nhalo", type=int, default=1_000_000)
     ap.add_argument("--variant", default="gather", choices=["gather", "atomic"])
@@ -267,8 +277,8 @@ def run_ours(args, rank, local_rank, world):
     if not args.no_e2e and world == 1:
         runner = bf.BaryonifyShell(cfg["catalog"], cfg["field"], eps, cfg["model"], verbose=False, device=local_rank,
                                    variant=args.variant, regrid=args.regrid)
-        for _ in range(max(2, min(args.warmup, 3))):  # warm-up: page-in, pinned staging buffers, allocator
-            runner.process()
+        for _ in range(max(3, min(args.warmup, 4))):  # warm-up: page-in, allocator, and BOTH pinned result buffers
+            out = runner.process()                     # (the caller still holds result k while call k+1 runs)
         ts = []
         for _ in range(max(1, min(args.steps, 3))):
             t0 = time.perf_counter()
@@ -316,7 +326,10 @@ def run_ours(args, rank, local_rank, world):
                        "regrid": args.regrid, "regrid_ms": {args.regrid: ms_rg, other: ms_rg_other},
                        "regrid_variants_max_reldiff": alt_diff},
             "roofline": {"bound": "hbm", "kernel": "gather_kernel<1>" if args.variant == "gather" else "shell_atomic_kernel<1>",
-                         "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                         "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                         "traffic": (GATHER_TRAFFIC_BYTES if (world == 1 and args.variant == "gather" and nside == 4096
+                                                              and args.nhalo == 1_000_000) else None),
+                         "traffic_unit": "bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum, profiles/)",
                          "peak_source": peak_src, "algorithmic_bytes_per_pair": B_PAIR, "kernel_ms": ms_acc,
                          "note": "pairs are summed in registers: the kernel is fp64-issue bound, HBM traffic is one 24 B write per pixel"},
             "e2e": e2e, "gpu_launches": (8 if args.regrid == "atomic" else 10) * args.steps, "clocks": clocks}
@@ -333,6 +346,121 @@ def run_ours(args, rank, local_rank, world):
         dist.destroy_process_group()
 
 
+def run_snapshot(args, rank, local_rank, world):
+    """BaryonifySnapshot: `npart_side`^3 particles in a 500 Mpc/h box, 1e5 halos, epsilon_max 5.  N > 1 splits the
+    particle array by index (weak in nothing: the same snapshot is divided, strong scaling); the halo grid is
+    replicated; there is no collective on the data path."""
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    import baryonification_b200 as bf
+    from baryonification_b200 import _device as dv, _lib, sharding as sh, synthetic as syn
+    from oracle import ref_shim
+    ref_shim.install()
+    _lib.load(require_cuda=True)
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    nh = 100_000
+    cfg = syn.config_snapshot(npart_side=args.npart_side, nhalo=nh, dim=3)
+    cat = cfg["field"].cat
+    a0, b0 = sh.index_split(cat.size, world)[rank]
+    runner = bf.BaryonifySnapshot(cfg["catalog"], cfg["field"], cfg["epsilon_max"], cfg["model"], verbose=False,
+                                  device=local_rank)
+    rec = dv.to_dev(cat[a0:b0].view(np.float64).reshape(-1, 4), dev=dev)
+    out = torch.empty_like(rec)
+    cnt = dv.pair_counter(dev)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    kms = []
+
+    def step(timed):
+        st = runner._setup(dev)  # table upload, (z, M) collapse, halo binning into the periodic grid
+        cnt.zero_()
+        a, b = ev(), ev()
+        a.record()
+        _lib.call("bf_snap_displace_records", 3, rec.shape[0], dv.ptr(rec), st["L"], float(st["s"]["a"]),
+                  C.byref(st["desc"]), C.byref(st["table"].desc), st["ng"], dv.ptr(st["ws"]), dv.ptr(out), dv.ptr(cnt),
+                  dv.stream_ptr())
+        b.record()
+        if timed:
+            kms.append((a, b))
+        return st
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    for _ in range(args.warmup):
+        step(False)
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    barrier()
+    t_a, t_b = ev(), ev()
+    t_a.record()
+    for _ in range(args.steps):
+        step(True)
+    t_b.record()
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    ms = torch.tensor([t_a.elapsed_time(t_b) / args.steps, float(np.mean([a.elapsed_time(b) for a, b in kms]))],
+                      dtype=torch.float64, device=dev)
+    pairs = cnt.clone()
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(pairs)
+    ms_step, ms_k, npairs = float(ms[0]), float(ms[1]), int(pairs[0])
+    # e2e: process() with host records in, host records out (pinned staging inside)
+    e2e = None
+    if not args.no_e2e:
+        local = runner if world == 1 else sh.ShardedSnapshot(runner, device=local_rank)
+        call = (lambda: local.process()) if world == 1 else (lambda: local.process(gather=False))
+        for _ in range(3):  # warm-up incl. both pinned result buffers (result k is alive while call k+1 runs)
+            res = call()
+        ts = []
+        for _ in range(max(1, min(args.steps, 3))):
+            barrier()
+            t0 = time.perf_counter()
+            res = call()
+            barrier()
+            ts.append(time.perf_counter() - t0)
+        t_e2e = float(np.mean(ts))
+        e2e = {"value": cat.size / t_e2e, "unit": "particles/s", "h2d_bytes_per_step": int((b0 - a0) * 32),
+               "d2h_bytes_per_step": int(res.nbytes), "ms": t_e2e * 1e3}
+    if rank == 0:
+        peak, peak_src = peaks()
+        alg = (cat.size * B_PARTICLE + npairs * B_SNAP_PAIR) / world
+        ach = alg / (ms_k * 1e-3) / 1e9
+        out_j = {"metric": "particle updates/sec", "value": cat.size / (ms_step * 1e-3), "unit": "particles/s",
+                 "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                 "config": {"workload": f"BaryonifySnapshot {args.npart_side}^3 particles, L=500 Mpc/h, {nh} halos, "
+                                        "epsilon_max=5, table 10x10x500", "parallelism": f"particle-index x{world}",
+                            "pairs": npairs, "l2": "particle records (64 B/particle in+out) far exceed the 126 MB L2"},
+                 "roofline": {"bound": "hbm", "kernel": "snap_gather_kernel<3,true>", "achieved": ach, "peak": peak,
+                              "unit": "GB/s", "frac": ach / peak, "peak_source": peak_src, "kernel_ms": ms_k,
+                              "traffic": SNAP_TRAFFIC_BYTES if (world == 1 and args.npart_side == 512) else None,
+                              "algorithmic_bytes": {"per_particle": B_PARTICLE, "per_pair": B_SNAP_PAIR}},
+                 "e2e": e2e, "gpu_launches": 12 * args.steps, "clocks": clocks}
+        if not args.no_cpu:
+            from oracle import runners as orc
+            cores = os.cpu_count() or 1
+            m = 2_000_000  # bounded sample: the first 2e6 particles against the full halo catalogue
+            sub = syn.ParticleSnapshot(x=cat["x"][:m], y=cat["y"][:m], z=cat["z"][:m], M=1.0, L=cfg["field"].L,
+                                       redshift=cfg["field"].redshift, cosmo=cfg["field"].cosmo)
+            r = orc.BaryonifySnapshot(cfg["catalog"], sub, cfg["epsilon_max"], cfg["model"], nthreads=cores)
+            t0 = time.perf_counter()
+            r.process()
+            dt = time.perf_counter() - t0
+            out_j["cpu_baseline"] = {"value": m / dt, "unit": "particles/s", "cores": cores, "kind": "port",
+                                     "sample": f"first {m} particles x all {nh} halos, cell-list ball query + displacement "
+                                               f"(OpenMP x{cores}) + apply, {dt:.1f} s", "extrapolated": False}
+        print(json.dumps(out_j))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     args = parse()
     rank = int(os.environ.get("RANK", 0))
@@ -340,6 +468,8 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", 1))
     if args.impl == "reference":
         run_reference(args, rank, world)
+    elif args.workload == "snapshot":
+        run_snapshot(args, rank, local_rank, world)
     else:
         run_ours(args, rank, local_rank, world)
 
