@@ -89,21 +89,30 @@ def _world(group):
     return dist.get_rank(group), dist.get_world_size(group)
 
 
-def _touched_extent(acc, first, last):
-    """[lo, hi) of the non-zero entries of ``acc`` outside the own range [first, last) (lo = first / hi = last if none)."""
+def _touched_extent(acc, first, last, window=None):
+    """[lo, hi) of the non-zero entries of ``acc`` outside the own range [first, last) (lo = first / hi = last if none).
+    ``window``: look at that many entries next to the range first (displaced mass lands a few rings away) and scan
+    the whole array only if the window's far edge is itself non-zero."""
+    n = acc.numel()
     lo, hi = first, last
     if first > 0:
-        nz = torch.nonzero(acc[:first])
+        a = 0 if window is None else max(0, first - window)
+        nz = torch.nonzero(acc[a:first])
         if nz.numel():
-            lo = int(nz[0])
-    if last < acc.numel():
-        nz = torch.nonzero(acc[last:])
+            lo = a + int(nz[0])
+            if lo == a and a > 0:
+                return _touched_extent(acc, first, last, None)
+    if last < n:
+        b = n if window is None else min(n, last + window)
+        nz = torch.nonzero(acc[last:b])
         if nz.numel():
             hi = last + int(nz[-1]) + 1
+            if hi == b and b < n:
+                return _touched_extent(acc, first, last, None)
     return lo, hi
 
 
-def exchange_boundary(acc, ranges, group=None):
+def exchange_boundary(acc, ranges, group=None, window=None):
     """Boundary mass exchange of the re-binning stage.
 
     ``acc`` is this rank's full-length accumulator: its own deposits, mostly inside its own range
@@ -116,7 +125,7 @@ def exchange_boundary(acc, ranges, group=None):
     own = acc[first:last]
     if world == 1:
         return own
-    lo, hi = _touched_extent(acc, first, last)
+    lo, hi = _touched_extent(acc, first, last, window)
     ext = torch.tensor([lo, hi], dtype=torch.int64, device=acc.device)
     all_ext = [torch.empty_like(ext) for _ in range(world)]
     dist.all_gather(all_ext, ext, group=group)
@@ -221,7 +230,7 @@ class ShardedShell:
             orig = np.ascontiguousarray(r.LightconeShell.map, dtype=np.float64)
             orig_d = dv.to_dev(orig[first:last], dev=dev, pinned=True)
             new_full = eng.regrid(orig_d, acc, method=r.regrid)
-            own = exchange_boundary(new_full, ranges, self.group)
+            own = exchange_boundary(new_full, ranges, self.group, window=64 * 4 * nside)
             sums = torch.stack([own.sum(), orig_d.sum()])
             dist.all_reduce(sums, group=self.group)  # the reference's mass check, HealpixRunner.py:344-346
             return gather_slices(own, ranges, self.group), (float(sums[0]), float(sums[1]))

@@ -164,14 +164,14 @@ def run_reference(args, rank, world):
     v = float(np.mean(vals))
     sample = (f"{a.cpu_sample} halos of the seed-42 shuffle (offset loop, OpenMP x{cores}) + re-binning of the first "
               f"{cb['regrid_pixels']} pixels (serial, as the reference's numba loop); scaled linearly to the full job")
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": "halo-pixel updates/sec", "value": v, "unit": "pairs/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": float(np.mean(times) * 1e3),
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"BaryonifyShell NSIDE={args.nside}, {args.nhalo} halos, epsilon_max=20, table 10x10x500"},
         "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0}))
+        "gpu_launches": 0})
 
 
 def run_ours(args, rank, local_rank, world):
@@ -226,7 +226,7 @@ def run_ours(args, rank, local_rank, world):
         eng.regrid(orig_d, off, new_d, method=args.regrid)
         c.record()
         if world > 1:  # boundary mass exchange + gather of the finished band slices (the only collectives)
-            own = sh.exchange_boundary(new_d, ranges)
+            own = sh.exchange_boundary(new_d, ranges, window=64 * 4 * nside)
             sh.gather_slices(own, ranges, out=full_d)
         if timed:
             acc_ms.append((a, b))
@@ -341,7 +341,7 @@ def run_ours(args, rank, local_rank, world):
                                    "sample": f"{cb['halos']} halos of the seed-42 shuffle (offset loop {cb['t_loop']:.1f} s, OpenMP x{cores}) "
                                              f"+ re-binning of {cb['regrid_pixels']} pixels ({cb['t_regrid_sample']:.1f} s, serial); "
                                              f"scaled linearly: full job ~{t_full:.0f} s", "extrapolated": True}
-        print(json.dumps(res))
+        emit(res)
     if world > 1:
         dist.destroy_process_group()
 
@@ -456,12 +456,30 @@ def run_snapshot(args, rank, local_rank, world):
             out_j["cpu_baseline"] = {"value": m / dt, "unit": "particles/s", "cores": cores, "kind": "port",
                                      "sample": f"first {m} particles x all {nh} halos, cell-list ball query + displacement "
                                                f"(OpenMP x{cores}) + apply, {dt:.1f} s", "extrapolated": False}
-        print(json.dumps(out_j))
+        emit(out_j)
     if world > 1:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def emit(obj):
+    """The ONE JSON line goes to the real stdout; everything else any library prints (NCCL's version banner, ...)
+    was redirected to stderr in main()."""
+    line = (json.dumps(obj) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(line.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, line)
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     args = parse()
     rank = int(os.environ.get("RANK", 0))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))

@@ -95,7 +95,7 @@ def _baryonify_ranks(rank, world, nside, eps):
     dist.all_reduce(crossing)
     assert int(crossing) > 0  # some mass does cross a shard boundary, so the exchange is exercised
     acc = torch.from_numpy(local)
-    own = sh.exchange_boundary(acc, ranges)
+    own = sh.exchange_boundary(acc, ranges, window=(4 * nside if rank == 0 else None))  # tiny window: falls back
     assert own.shape[0] == last - first
     full = sh.gather_slices(own, ranges).numpy()
     # a pixel gets (own deposits) + (ghost deposits): two partial sums instead of one serial sum -> last-bit changes only
