@@ -43,15 +43,20 @@ class DefaultRunnerGrid:
 
     def _prepare(self, table_host, baryonify, dev):
         keys = vars(self.model).get("p_keys", [])
-        if len(keys) > 0:
-            raise NotImplementedError(f"property-keyed tables {keys} are not yet supported by the B200 runners")
+        if len(keys) > 0:  # Map2DRunner.py:469-474 / :707-712
+            txt = (f"You asked to use {keys} properties in Baryonification. You must pass a ParamTabulatedProfile"
+                   f"as the model. You have passed {type(self.model)} instead")
+            tab = getattr(self.model, "raw_input_2D", None)
+            assert (not baryonify) and tab is not None and np.ndim(tab) == 3 + len(keys), txt
         G = self.GriddedMap
         rmat = host.grid_rmat(self.HaloNDCatalog, G, self.use_ellipticity, baryonify)  # 3-D raises (:565 / :790)
         table = dv.DeviceTable(table_host, dev=dev)
         s = host.grid_scalars(self.HaloNDCatalog, G, self.mass_def, self.epsilon_max, self.model, baryonify)
         t = {k: dv.to_dev(s[k], dev=dev) for k in ("pos", "cut", "lnr_shift", "z_in", "M_in")}
         t["Nsize"] = dv.to_dev(s["Nsize"], dtype=np.int64, dev=dev)
-        rows = table.collapse(t["z_in"], t["M_in"])
+        extras = host.property_columns(self.HaloNDCatalog.cat, self.model)
+        t["extras"] = dv.to_dev(extras, dev=dev) if extras is not None else None
+        rows = table.collapse(t["z_in"], t["M_in"], t["extras"])
         t["Rmat"] = dv.to_dev(rmat, dev=dev) if rmat is not None else None
         desc = _lib.GridHalos(t["pos"].data_ptr(), t["Nsize"].data_ptr(), t["cut"].data_ptr(),
                               t["lnr_shift"].data_ptr(), rows.data_ptr(),

@@ -42,20 +42,24 @@ class DefaultRunner:
             raise NotImplementedError("You have set use_ellipticity = True, but this not yet implemented for HealpixRunner")
 
     # -- helpers -----------------------------------------------------------------------------
-    def _check_keys(self):
+    def _check_keys(self, baryonify=False):
+        """HealpixRunner.py:282-287 / :407-412: models with property keys must be ParamTabulatedProfile tables."""
         keys = vars(self.model).get("p_keys", []) if self.model is not None else []
-        if len(keys) > 0:  # HealpixRunner.py:282-287; property-keyed tables are not on the GPU path yet
-            raise NotImplementedError(f"You asked to use {keys} properties in Baryonification; "
-                                      "ParamTabulatedProfile tables are not yet supported by the B200 runners")
+        if len(keys) > 0:
+            txt = (f"You asked to use {keys} properties in Baryonification. You must pass a ParamTabulatedProfile"
+                   f"as the model. You have passed {type(self.model)} instead")
+            tab = getattr(self.model, "raw_input_2D", None)
+            assert (not baryonify) and tab is not None and np.ndim(tab) == 3 + len(keys), txt
 
     def _engine(self, dev, mode, bands=None):
         """Host set-up (vectorised) + H2D + (z, M) collapse + halo binning."""
-        self._check_keys()
-        t0 = time.perf_counter()
         baryonify = mode == engine.BARYONIFY
+        self._check_keys(baryonify)
+        t0 = time.perf_counter()
         htab = displacement_host_table(self.model) if baryonify else profile_host_table(self.model, "2D")
         s = host.shell_scalars(self.HaloLightConeCatalog, self.cosmo, self.mass_def, self.epsilon_max, self.model,
                                baryonify)
+        s["extras"] = host.property_columns(self.HaloLightConeCatalog.cat, self.model)
         self.timings["host_setup"] = time.perf_counter() - t0
         t0 = time.perf_counter()
         eng = engine.ShellEngine(self.LightconeShell.NSIDE, mode, htab, s, dev, variant=self.variant, bands=bands)

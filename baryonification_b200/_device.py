@@ -105,12 +105,31 @@ class DeviceTable:
         self.desc = _lib.Table(self.gz.data_ptr(), self.gM.data_ptr(), self.gr.data_ptr(), self.values.data_ptr(),
                                host.gz.size, host.gM.size, host.gr.size, float(host.gr[0]), float(host.gr[-1]))
         self.nr = host.gr.size
+        self.nd = None
+        if host.extra:  # extra property axes (p_keys): N-d collapse descriptor
+            self.gx = [to_dev(g, dev=dev) for g in host.extra]
+            grids = [self.gz, self.gM] + self.gx
+            nd = _lib.TableND()
+            nd.naxes = len(grids)
+            for a, g in enumerate(grids):
+                nd.grid[a] = g.data_ptr()
+                nd.n[a] = g.numel()
+            nd.values = self.values.data_ptr()
+            nd.nr = self.nr
+            self.nd = nd
 
-    def collapse(self, z_in, M_in):
-        """rows[j, :] for every halo (bf_table_collapse_zM)."""
+    def collapse(self, z_in, M_in, extras=None):
+        """rows[j, :] for every halo (bf_table_collapse_zM; bf_table_collapse_nd when the table has property axes,
+        ``extras`` = [nh, n_keys] per-halo property values)."""
         nh = z_in.numel()
         rows = empty((nh, self.nr), dev=z_in.device)
-        _lib.call("bf_table_collapse_zM", C.byref(self.desc), nh, ptr(z_in), ptr(M_in), ptr(rows), stream_ptr())
+        if self.nd is None:
+            _lib.call("bf_table_collapse_zM", C.byref(self.desc), nh, ptr(z_in), ptr(M_in), ptr(rows), stream_ptr())
+        else:
+            if extras is None or extras.shape != (nh, len(self.gx)):
+                raise _lib.BFError("this table has property axes: per-halo property values [nh, n_keys] are required")
+            coords = torch.cat([z_in.reshape(-1, 1), M_in.reshape(-1, 1), extras], dim=1).contiguous()
+            _lib.call("bf_table_collapse_nd", C.byref(self.nd), nh, ptr(coords), ptr(rows), stream_ptr())
         return rows
 
     def readout(self, row, r, lnr_shift=0.0, cut=0.0, mode=0):

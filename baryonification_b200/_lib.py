@@ -26,6 +26,14 @@ class Table(C.Structure):
                 ("nz", _i64), ("nM", _i64), ("nr", _i64), ("lnr_first", C.c_double), ("lnr_last", C.c_double)]
 
 
+MAX_AXES = 6
+
+
+class TableND(C.Structure):
+    _fields_ = [("naxes", C.c_int), ("grid", C.c_void_p * MAX_AXES), ("n", _i64 * MAX_AXES), ("values", C.c_void_p),
+                ("nr", _i64)]
+
+
 class ShellHalos(C.Structure):
     _fields_ = [("vec", C.c_void_p), ("lon", C.c_void_p), ("lat", C.c_void_p), ("radius", C.c_void_p),
                 ("D", C.c_void_p), ("a", C.c_void_p), ("cut", C.c_void_p), ("lnr_shift", C.c_void_p),
@@ -48,6 +56,7 @@ _SIGS = {
     "bf_version": (C.c_int, []),
     "bf_device_sm_count": (C.c_int, [_P(C.c_int)]),
     "bf_table_collapse_zM": (C.c_int, [_P(Table), _i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p]),
+    "bf_table_collapse_nd": (C.c_int, [_P(TableND), _i64, _dbl_p, _dbl_p, C.c_void_p]),
     "bf_table_readout": (C.c_int, [_P(Table), _dbl_p, _i64, _dbl_p, C.c_double, C.c_double, C.c_int, _dbl_p,
                                    C.c_void_p]),
     "bf_healpix_ang2pix": (C.c_int, [_i64, _i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p]),

@@ -53,6 +53,53 @@ extern "C" int bf_table_collapse_zM(const bf_table *t, int64_t nh, const double 
     return BF_OK;
 }
 
+// N-d version: axes (z, M, extras...), r last.  Corner c's bit (naxes-1-a) selects the upper node of axis a, so the
+// corners are visited in itertools.product order (first axis slowest), like scipy's _evaluate_linear.
+__global__ void __launch_bounds__(128) collapse_nd_kernel(bf_table_nd T, i64 nh, const double *__restrict__ coords,
+                                                          double *__restrict__ rows) {
+    for (i64 j = blockIdx.x; j < nh; j += gridDim.x) {
+        int cell[BF_MAX_AXES];
+        double t[BF_MAX_AXES];
+        bool oob = false;
+        for (int a = 0; a < T.naxes; ++a) {
+            cell[a] = axis_cell(T.grid[a], (int)T.n[a], coords[j * T.naxes + a], t[a]);
+            if (cell[a] < 0) oob = true;
+        }
+        double *out = rows + j * T.nr;
+        if (oob) {
+            for (int k = threadIdx.x; k < T.nr; k += blockDim.x) out[k] = nan("");
+            continue;
+        }
+        const int ncorner = 1 << T.naxes;
+        for (int k = threadIdx.x; k < T.nr; k += blockDim.x) {
+            double acc = 0.0;
+            for (int c = 0; c < ncorner; ++c) {
+                double w = 1.0;
+                i64 off = 0;
+                for (int a = 0; a < T.naxes; ++a) {
+                    int bit = (c >> (T.naxes - 1 - a)) & 1;
+                    w = w * (bit ? t[a] : 1.0 - t[a]);
+                    off = off * T.n[a] + (cell[a] + bit);
+                }
+                double term = T.values[off * T.nr + k] * w;
+                acc = (c == 0) ? term : acc + term;
+            }
+            out[k] = acc;
+        }
+    }
+}
+
+extern "C" int bf_table_collapse_nd(const bf_table_nd *t, int64_t nh, const double *coords, double *rows, void *stream) {
+    BF_REQUIRE(t && t->values && t->naxes >= 1 && t->naxes <= BF_MAX_AXES && t->nr >= 2, "bad N-d table");
+    for (int a = 0; a < t->naxes; ++a) BF_REQUIRE(t->grid[a] && t->n[a] >= 2, "N-d table axis needs >= 2 ascending points");
+    BF_REQUIRE(nh >= 0 && (nh == 0 || (coords && rows)), "null per-halo array");
+    if (nh == 0) return BF_OK;
+    int grid = (int)((nh < (i64)bf_sm_count() * 16) ? nh : (i64)bf_sm_count() * 16);
+    collapse_nd_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(*t, nh, coords, rows);
+    BF_LAUNCH_OK();
+    return BF_OK;
+}
+
 __global__ void readout_kernel(bf_raxis ax, const double *__restrict__ row, i64 n, const double *__restrict__ r,
                                double lnr_shift, double cut, int mode, double *__restrict__ out) {
     i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;

@@ -43,7 +43,8 @@ class ShellEngine:
         self.table = dv.DeviceTable(self.host_table, dev=dev)
         keys = ("vec", "lon", "lat", "radius", "D", "a", "cut", "lnr_shift", "z_in", "M_in")
         self.t = {k: dv.to_dev(s[k], dev=dev, pinned=pinned) for k in keys}
-        self.rows = self.table.collapse(self.t["z_in"], self.t["M_in"])
+        self.t["extras"] = dv.to_dev(s["extras"], dev=dev) if s.get("extras") is not None else None  # p_keys columns
+        self.rows = self.table.collapse(self.t["z_in"], self.t["M_in"], self.t["extras"])
         self.order = torch.argsort(self.t["radius"], descending=True) if self.variant == "atomic" else None
         t = self.t
         self.desc = _lib.ShellHalos(t["vec"].data_ptr(), t["lon"].data_ptr(), t["lat"].data_ptr(),
@@ -54,7 +55,7 @@ class ShellEngine:
         return self
 
     def recollapse(self):
-        self.rows = self.table.collapse(self.t["z_in"], self.t["M_in"])
+        self.rows = self.table.collapse(self.t["z_in"], self.t["M_in"], self.t["extras"])
         self.desc.rows = self.rows.data_ptr()
 
     # ---- stage 1: halo binning into sky cells (gather variant) ----------------------------------

@@ -96,6 +96,16 @@ def model_cut(model, M, a, need_cut=True):
     return np.asarray(cut, dtype=np.float64), np.asarray(shift, dtype=np.float64)
 
 
+def property_columns(cat, model):
+    """Per-halo values of the model's extra table axes, ``o_j = {key: cat[key][j] for key in p_keys}``
+    (HealpixRunner.py:425, Map2DRunner.py:720), as float64 [n, n_keys] -- ``kwargs[k] * empty`` (Tabulate.py:607)
+    widens the catalogue scalar (float32 in ND catalogues) to float64.  None when the model has no p_keys."""
+    keys = list(vars(model).get("p_keys", []) or []) if model is not None else []
+    if not keys:
+        return None
+    return np.ascontiguousarray(np.stack([np.asarray(cat[k]).astype(np.float64) for k in keys], axis=1))
+
+
 def log_native(M):
     """np.log(M_j) in the catalogue's dtype (BaryonCorrection.py:369, Tabulate.py:283), widened."""
     M = np.asarray(M)

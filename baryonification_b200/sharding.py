@@ -208,12 +208,13 @@ class ShardedShell:
         from . import _device as dv, engine, host
         from .tables import displacement_host_table, profile_host_table
         r = self.runner
-        r._check_keys()
+        r._check_keys(self.baryonify)
         dev = dv.device(self.device)
         nside = r.LightconeShell.NSIDE
         bands, ranges = self.plan()
         lo, hi = bands[self.rank]
         s = host.shell_scalars(r.HaloLightConeCatalog, r.cosmo, r.mass_def, r.epsilon_max, r.model, self.baryonify)
+        s["extras"] = host.property_columns(r.HaloLightConeCatalog.cat, r.model)
         keep = halos_touching_bands(s["vec"][:, 2], s["radius"], nside, lo, hi)
         s = _subset(s, keep)
         mode = engine.BARYONIFY if self.baryonify else engine.PAINT

@@ -8,7 +8,7 @@ from __future__ import annotations
 import numpy as np
 
 from . import _ccl
-from .tables import DisplacementTable, ProfileTable
+from .tables import DisplacementTable, ParamProfileTable, ProfileTable
 from .utils.io import (GriddedMap, HaloLightConeCatalog, HaloNDCatalog, LightconeShell,
                        ParticleSnapshot)
 
@@ -89,6 +89,28 @@ def profile_model(zmin, zmax, cosmo=COSMO, nz=10, nM=10, nR=500, zero_beyond=Non
     return cls(z, M, r, P3, P2, model_cosmology(cosmo))
 
 
+CDELTA_GRID = np.linspace(2.0, 12.0, 6)
+
+
+def param_profile_model(zmin, zmax, cosmo=COSMO, nz=10, nM=10, nR=500, zero_beyond=None):
+    """The same profiles tabulated over one extra halo property, ``cdelta`` (p_keys = ['cdelta'], like a
+    ParamTabulatedProfile built with other_params = {'cdelta': ...}, utils/Tabulate.py:524-561)."""
+    z, M, r = table_axes(zmin, zmax, nz=nz, nM=nM, nR=nR)
+    c = CDELTA_GRID
+    P3 = profile_values(z, M, r, zero_beyond)[..., None] * ((c / 5.0) ** 1.5 / (1 + (r[:, None] * c / 4.0) ** 0.5))[None, None]
+    P2 = 2.0 * r[None, None, :, None] * P3 * (1.0 / (1.0 + z))[:, None, None, None]
+    return ParamProfileTable(z, M, r, P3, P2, {"cdelta": c}, model_cosmology(cosmo))
+
+
+def cdelta_column(n, seed):
+    """Per-halo concentrations; a few lie outside the tabulated axis (their readout is NaN -> painted as 0)."""
+    rng = np.random.default_rng(seed + 555)
+    c = rng.uniform(CDELTA_GRID[0], CDELTA_GRID[-1], n)
+    c[::97] = CDELTA_GRID[-1] + 1.0
+    c[1::211] = CDELTA_GRID[2]  # exactly on a node
+    return c
+
+
 def lognormal_field(shape, seed):
     rng = np.random.default_rng(seed)
     return rng.lognormal(0.0, 1.0, shape) * 1e10
@@ -102,8 +124,11 @@ def grid_bins(npix, L):
 # --------------------------------------------------------------------------------------
 # the five BASELINE.json configurations (sizes overridable so tests can shrink them)
 # --------------------------------------------------------------------------------------
-def config_grid(npix=512, nhalo=2000, dim=2, L=500.0 / 0.7, seed=SEED0 + 1, epsilon_max=20.0, ellipticity=False):
+def config_grid(npix=512, nhalo=2000, dim=2, L=500.0 / 0.7, seed=SEED0 + 1, epsilon_max=20.0, ellipticity=False,
+                p_keys=False):
     halos = box_halos(nhalo, seed, L, dim=dim)
+    if p_keys:
+        halos["cdelta"] = cdelta_column(nhalo, seed)
     if ellipticity:  # q_ell axis ratios, A_ell major-axis directions (+ c_ell in 3-D), Map2DRunner.py:266-272
         rng = np.random.default_rng(seed + 77)
         halos["q_ell"] = rng.uniform(0.4, 1.0, nhalo)
@@ -116,19 +141,22 @@ def config_grid(npix=512, nhalo=2000, dim=2, L=500.0 / 0.7, seed=SEED0 + 1, epsi
     gmap = GriddedMap(map=field, redshift=halos["redshift"], bins=grid_bins(npix, L), cosmo=COSMO)
     z = halos["redshift"]
     model = displacement_model(z * 0.5, z * 2.0, epsilon_max)
-    pmodel = profile_model(z * 0.5, z * 2.0)
+    pmodel = param_profile_model(z * 0.5, z * 2.0) if p_keys else profile_model(z * 0.5, z * 2.0)
     return dict(catalog=cat, field=gmap, model=model, paint_model=pmodel, epsilon_max=epsilon_max,
                 use_ellipticity=bool(ellipticity))
 
 
-def config_shell(nside=1024, nhalo=100_000, seed=SEED0 + 2, epsilon_max=20.0, zero_map=False, zero_beyond=None):
+def config_shell(nside=1024, nhalo=100_000, seed=SEED0 + 2, epsilon_max=20.0, zero_map=False, zero_beyond=None,
+                 p_keys=False):
     halos = lightcone_halos(nhalo, seed)
+    if p_keys:
+        halos["cdelta"] = cdelta_column(nhalo, seed)
     npix = 12 * nside * nside
     field = np.zeros(npix) if zero_map else lognormal_field(npix, seed + 1000)
     cat = HaloLightConeCatalog(**halos)
     shell = LightconeShell(map=field, cosmo=COSMO)
     model = displacement_model(0.05, 1.2, epsilon_max)
-    pmodel = profile_model(0.05, 1.2, zero_beyond=zero_beyond)
+    pmodel = (param_profile_model if p_keys else profile_model)(0.05, 1.2, zero_beyond=zero_beyond)
     return dict(catalog=cat, field=shell, model=model, paint_model=pmodel, epsilon_max=epsilon_max)
 
 

@@ -63,21 +63,39 @@ class ProfileTable(_NoCpuPath):
     real = projected = _NoCpuPath._nope
 
 
+class ParamProfileTable(ProfileTable):
+    """Holder for profiles tabulated over extra halo properties (the reference's ``ParamTabulatedProfile``,
+    utils/Tabulate.py:524-561): ``raw_input_2D/3D`` are [Nz, NM, NR, Np1, ...], ``p_keys`` names the extra axes
+    and ``raw_input_<key>_range`` holds each axis; the per-halo values are catalogue columns of the same names."""
+
+    def __init__(self, z, M, r, prof3D, prof2D, other_params, cosmo=None, mass_def=None):
+        super().__init__(z, M, r, prof3D, prof2D, cosmo, mass_def)
+        self.p_keys = list(other_params.keys())
+        for k, v in other_params.items():
+            setattr(self, "raw_input_%s_range" % k, np.asarray(v, dtype=np.float64))
+
+
 class HostTable:
-    """Contiguous float64 view of one (z, M, r) table, ready for H2D."""
+    """Contiguous float64 view of one table, ready for H2D: axes (z, M[, extras...]) + the radial axis.
+    ``values`` is stored with r LAST ([Nz, NM, Np1, ..., NR]) so that the per-halo collapse reads rows."""
 
-    __slots__ = ("gz", "gM", "gr", "values", "is_log", "uniform_r")
+    __slots__ = ("gz", "gM", "gr", "values", "is_log", "extra", "keys")
 
-    def __init__(self, gz, gM, gr, values, is_log):
+    def __init__(self, gz, gM, gr, values, is_log, extra=(), keys=()):
         self.gz = np.ascontiguousarray(gz, dtype=np.float64)
         self.gM = np.ascontiguousarray(gM, dtype=np.float64)
         self.gr = np.ascontiguousarray(gr, dtype=np.float64)
-        self.values = np.ascontiguousarray(values, dtype=np.float64)
+        self.extra = [np.ascontiguousarray(g, dtype=np.float64) for g in extra]
+        self.keys = list(keys)
+        values = np.asarray(values, dtype=np.float64)
+        want = (self.gz.size, self.gM.size, self.gr.size) + tuple(g.size for g in self.extra)
+        if values.shape != want:
+            raise ValueError(f"table shape {values.shape} does not match its axes {want}")
+        if self.extra:  # reference layout [z, M, r, p...] -> [z, M, p..., r]
+            values = np.moveaxis(values, 2, -1)
+        self.values = np.ascontiguousarray(values)
         self.is_log = bool(is_log)
-        if self.values.shape != (self.gz.size, self.gM.size, self.gr.size):
-            raise ValueError(f"table shape {self.values.shape} does not match its axes "
-                             f"({self.gz.size}, {self.gM.size}, {self.gr.size})")
-        for g, nm in ((self.gz, "z"), (self.gM, "M"), (self.gr, "r")):
+        for g, nm in [(self.gz, "z"), (self.gM, "M"), (self.gr, "r")] + list(zip(self.extra, self.keys)):
             if g.size < 2 or not np.all(np.diff(g) > 0):
                 raise ValueError(f"table axis {nm} must be strictly ascending with >= 2 points")
 
@@ -92,11 +110,11 @@ def _require(model, names):
 
 
 def _no_pkeys(model):
+    """The reference's Baryonify runners assert that a model with property keys is a ParamTabulatedProfile
+    (HealpixRunner.py:282-287, Map2DRunner.py:469-474) -- which a displacement model never is."""
     keys = list(vars(model).get("p_keys", []) or [])
-    if keys:
-        raise NotImplementedError(
-            f"tables with extra property axes {keys} (ParamTabulatedProfile / other_params) are not yet "
-            "supported by the B200 runners")
+    assert not keys, (f"You asked to use {keys} properties in Baryonification. You must pass a ParamTabulatedProfile"
+                      f"as the model. You have passed {type(model)} instead")
 
 
 def displacement_host_table(model) -> HostTable:
@@ -117,8 +135,10 @@ def profile_host_table(model, which: str) -> HostTable:
     if not hasattr(model, name) and (hasattr(model, "_projected") or hasattr(model, "projected")) \
             and not hasattr(model, "interp2D") and hasattr(model, "setup_interpolator"):
         raise NameError("No Table created. Run setup_interpolator() method first")  # Tabulate.py:322
-    _require(model, [name, "raw_input_z_range", "raw_input_M_range", "raw_input_r_range"])
-    _no_pkeys(model)
+    keys = list(vars(model).get("p_keys", []) or [])
+    _require(model, [name, "raw_input_z_range", "raw_input_M_range", "raw_input_r_range"] +
+             ["raw_input_%s_range" % k for k in keys])
     with np.errstate(divide="ignore", invalid="ignore"):
         vals = np.log(np.asarray(getattr(model, name), dtype=np.float64))
-    return HostTable(model.raw_input_z_range, model.raw_input_M_range, model.raw_input_r_range, vals, is_log=True)
+    return HostTable(model.raw_input_z_range, model.raw_input_M_range, model.raw_input_r_range, vals, is_log=True,
+                     extra=[getattr(model, "raw_input_%s_range" % k) for k in keys], keys=keys)

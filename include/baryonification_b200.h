@@ -44,6 +44,21 @@ typedef struct {
 /* rows[j][:] = blend of the 4 (z,M) corners for halo j; rows of out-of-table halos are NaN. */
 int bf_table_collapse_zM(const bf_table *tab_host, int64_t nh, const double *z_in, const double *M_in,
                          double *rows /* [nh][nr] */, void *stream);
+/* Tables with extra property axes (`p_keys`: other_params of BaryonCorrection.py:205-221 and
+ * ParamTabulatedProfile, Tabulate.py:524-561; the per-halo values are catalogue columns, HealpixRunner.py:425).
+ * The host moves the r axis last: values is [n[0]][n[1]]...[n[naxes-1]][nr] with axes (z, M, extras...), C order.
+ * coords[j][a] is halo j's coordinate on axis a; rows[j][:] = N-linear blend of the 2^naxes corners (scipy RGI
+ * weights, multiplied in axis order), NaN when any coordinate is outside its axis. */
+#define BF_MAX_AXES 6
+typedef struct {
+    int naxes;
+    const double *grid[BF_MAX_AXES]; /* ascending axes */
+    int64_t n[BF_MAX_AXES];
+    const double *values;
+    int64_t nr;
+} bf_table_nd;
+int bf_table_collapse_nd(const bf_table_nd *tab_host, int64_t nh, const double *coords /* [nh][naxes] */,
+                         double *rows /* [nh][nr] */, void *stream);
 /* out[i] = readout of halo `row` at radius r[i]; mode 0: linear table with cut (r < cut else 0),
  * mode 1: exp(log table).  lnr_shift is subtracted from ln r (Rdelta_sampling). */
 int bf_table_readout(const bf_table *tab_host, const double *row, int64_t n, const double *r,

@@ -47,6 +47,7 @@ def _lib():
         L.bfo_snapshot_offsets.argtypes = ([C.c_int, _i64, _dp, C.c_double, _i64, _dp, _dp, C.c_double,
                                             _dp, _dp, _dp, _dp] + _TAB + [_dp, C.c_int])
         L.bfo_snapshot_apply.argtypes = [_i64, _dp, _dp, C.c_double, _dp]
+        L.bfo_set_extra_axes.argtypes = [C.c_int, _dp, _ip, _dp]
         _ready = True
     return L
 
@@ -61,7 +62,7 @@ def _c(a, dt=np.float64):
 class _Table:
     def __init__(self, gz, gM, gr, tab):
         self.gz, self.gM, self.gr, self.tab = _c(gz), _c(gM), _c(gr), _c(tab)
-        assert self.tab.shape == (self.gz.size, self.gM.size, self.gr.size)
+        assert self.tab.shape[:3] == (self.gz.size, self.gM.size, self.gr.size)  # (+ p_keys axes after r)
 
     def args(self):
         return [self.gz, self.gz.size, self.gM, self.gM.size, self.gr, self.gr.size, self.tab]
@@ -75,10 +76,34 @@ def displacement_table(model):
                   model.raw_input_d)
 
 
+class extra_axes:
+    """Context manager: registers the model's extra property axes (``p_keys``: Tabulate.py:524-561 /
+    BaryonCorrection.py:205-221) and the per-halo property values ``o_j = {key: cat[key][j]}``
+    (HealpixRunner.py:425, Map2DRunner.py:720) with the C oracle for the duration of one runner call."""
+
+    def __init__(self, model, cat):
+        keys = list(getattr(model, "p_keys", []) or [])
+        self.nx = len(keys)
+        if self.nx:
+            grids = [_c(getattr(model, "raw_input_%s_range" % k)) for k in keys]
+            self.grids = _c(np.concatenate(grids))
+            self.sizes = np.array([g.size for g in grids], dtype=np.int64)
+            # kwargs[k] * empty (Tabulate.py:607): the catalogue scalar (float32 for ND catalogues) widened to float64
+            self.xin = _c(np.stack([np.asarray(cat[k]).astype(np.float64) for k in keys], axis=1))
+
+    def __enter__(self):
+        if self.nx:
+            _lib().bfo_set_extra_axes(self.nx, self.grids, self.sizes, self.xin)
+        return self
+
+    def __exit__(self, *exc):
+        if self.nx:
+            _lib().bfo_set_extra_axes(0, self.grids, self.sizes, self.xin)
+        return False
+
+
 def profile_table(model, which):
-    """log(raw_input_2D|3D) as built at utils/Tabulate.py:229-238."""
-    if len(getattr(model, "p_keys", [])) > 0:
-        raise NotImplementedError("oracle: p_keys tables not restated yet")
+    """log(raw_input_2D|3D) as built at utils/Tabulate.py:229-238 (:553-561 with p_keys axes)."""
     raw = model.raw_input_2D if which == "2D" else model.raw_input_3D
     with np.errstate(divide="ignore", invalid="ignore"):
         return _Table(model.raw_input_z_range, model.raw_input_M_range, model.raw_input_r_range,
@@ -198,9 +223,10 @@ class PaintProfilesShell(_ShellBase):
         s = self._halo_scalars()
         T = profile_table(self.model, "2D")
         new_map = np.zeros(self.LightconeShell.map.size)
-        self.npairs = _lib().bfo_paint_shell(
-            self.LightconeShell.NSIDE, s["M"].size, s["vec"], s["radius"], s["D"], s["a"], s["z_in"],
-            s["M_in"], *T.args(), new_map, self.nthreads)
+        with extra_axes(self.model, self.HaloLightConeCatalog.cat):
+            self.npairs = _lib().bfo_paint_shell(
+                self.LightconeShell.NSIDE, s["M"].size, s["vec"], s["radius"], s["D"], s["a"], s["z_in"],
+                s["M_in"], *T.args(), new_map, self.nthreads)
         return new_map
 
 
@@ -324,10 +350,11 @@ class PaintProfilesGrid(_GridBase):
         T = profile_table(self.model, "2D" if G.is2D else "3D")
         out = np.zeros(G.map.size)
         rmat = self._rmat(False)
-        self.npairs = _lib().bfo_grid_halos(dim, 1, G.Npix, _c(G.bins), float(G.res), n, pos, Nsize,
-                                            np.log(1 / a), _log_native(M), cut, np.zeros(n),
-                                            None if rmat is None else rmat.ctypes.data, *T.args(), out,
-                                            self.nthreads)
+        with extra_axes(self.model, cat):
+            self.npairs = _lib().bfo_grid_halos(dim, 1, G.Npix, _c(G.bins), float(G.res), n, pos, Nsize,
+                                                np.log(1 / a), _log_native(M), cut, np.zeros(n),
+                                                None if rmat is None else rmat.ctypes.data, *T.args(), out,
+                                                self.nthreads)
         return out.reshape(G.map.shape)
 
 

@@ -23,11 +23,18 @@ def ref_displacement_model(bfg, table):
 
 
 def ref_profile_model(bfg, table):
-    """A reference ``TabulatedProfile`` as ``setup_interpolator`` leaves it (utils/Tabulate.py:229-238)."""
-    m = object.__new__(bfg.TabulatedProfile)
+    """A reference ``TabulatedProfile`` as ``setup_interpolator`` leaves it (utils/Tabulate.py:229-238), or a
+    ``ParamTabulatedProfile`` (:553-561) when the table has property axes."""
+    keys = list(getattr(table, "p_keys", []) or [])
+    m = object.__new__(bfg.utils.ParamTabulatedProfile if keys else bfg.TabulatedProfile)
     grid = (table.raw_input_z_range, table.raw_input_M_range, table.raw_input_r_range)
+    if keys:
+        m.p_keys = keys
+        for k in keys:
+            setattr(m, "raw_input_%s_range" % k, getattr(table, "raw_input_%s_range" % k))
+        grid = grid + tuple(getattr(table, "raw_input_%s_range" % k) for k in keys)
     m.raw_input_3D, m.raw_input_2D = table.raw_input_3D, table.raw_input_2D
-    m.raw_input_z_range, m.raw_input_M_range, m.raw_input_r_range = grid
+    m.raw_input_z_range, m.raw_input_M_range, m.raw_input_r_range = grid[:3]
     with np.errstate(divide="ignore", invalid="ignore"):
         m.interp3D = interpolate.RegularGridInterpolator(grid, np.log(table.raw_input_3D), bounds_error=False)
         m.interp2D = interpolate.RegularGridInterpolator(grid, np.log(table.raw_input_2D), bounds_error=False)
@@ -37,7 +44,8 @@ def ref_profile_model(bfg, table):
 
 def ref_lightcone_catalog(bfg, cat):
     c = cat.cat
-    return bfg.HaloLightConeCatalog(ra=c["ra"], dec=c["dec"], M=c["M"], z=c["z"], cosmo=cat.cosmo)
+    extra = {k: c[k] for k in c.dtype.names if k not in ("M", "z", "ra", "dec")}  # cdelta, ...
+    return bfg.HaloLightConeCatalog(ra=c["ra"], dec=c["dec"], M=c["M"], z=c["z"], cosmo=cat.cosmo, **extra)
 
 
 def ref_nd_catalog(bfg, cat, dim):

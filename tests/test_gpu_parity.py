@@ -347,3 +347,33 @@ def test_grid_regrid_sorted_matches_atomic_and_oracle(gpu, dim, npix):
     assert relmax(s1, a1) < 1e-12 and relmax(s1, ref) < 1e-9
     tot = cfg["field"].map.sum()
     assert abs(s1.sum() - tot) / tot < MASS_RTOL
+
+
+# ------------------------------------------------------------------ property-keyed tables (p_keys)
+def test_param_tabulated_profiles_parity(gpu):
+    """ParamTabulatedProfile-style tables [Nz, NM, NR, Ncdelta] with a per-halo `cdelta` column
+    (utils/Tabulate.py:524-621; HealpixRunner.py:407-441, Map2DRunner.py:707-801)."""
+    import baryonification_b200 as bf
+    from baryonification_b200 import synthetic as syn
+    from oracle import runners as orc
+    cfg = syn.config_shell(nside=128, nhalo=1500, zero_map=True, zero_beyond=50.0, p_keys=True)
+    for variant in ("gather", "atomic"):
+        g = bf.PaintProfilesShell(cfg["catalog"], cfg["field"], 20.0, cfg["paint_model"], verbose=False, variant=variant)
+        r = orc.PaintProfilesShell(cfg["catalog"], cfg["field"], 20.0, cfg["paint_model"])
+        got, ref = g.process(), r.process()
+        assert g.npairs == r.npairs
+        assert np.array_equal(got != 0, ref != 0)
+        assert relmax(got, ref) < 1e-11
+    for dim, npix, L in ((2, 128, 500.0 / 0.7), (3, 32, 100.0)):
+        cg = syn.config_grid(npix=npix, nhalo=200, dim=dim, epsilon_max=8.0, L=L, p_keys=True)
+        g = bf.PaintProfilesGrid(cg["catalog"], cg["field"], 8.0, cg["paint_model"], verbose=False)
+        r = orc.PaintProfilesGrid(cg["catalog"], cg["field"], 8.0, cg["paint_model"])
+        got, ref = g.process(), r.process()
+        assert g.npairs == r.npairs and np.array_equal(got != 0, ref != 0)
+        assert relmax(got, ref) < 1e-11
+    # the reference's Baryonify runners refuse property keys unless the model is a ParamTabulatedProfile
+    dm = cfg["model"]
+    dm.p_keys = ["cdelta"]
+    with pytest.raises(AssertionError, match="You asked to use"):
+        bf.BaryonifyShell(cfg["catalog"], cfg["field"], 20.0, dm, verbose=False).process()
+    dm.p_keys = []
