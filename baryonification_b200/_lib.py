@@ -93,6 +93,10 @@ _SIGS = {
                                    _P(Table), _i64, C.c_void_p, _dbl_p, _dbl_p, _dbl_p, _dbl_p, C.c_void_p]),
     "bf_snap_displace_records": (C.c_int, [C.c_int, _i64, C.c_void_p, C.c_double, C.c_double, _P(SnapHalos), _P(Table),
                                            _i64, C.c_void_p, C.c_void_p, _dbl_p, C.c_void_p]),
+    "bf_pk_ngp_deposit": (C.c_int, [_i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p, C.c_double, _i64, _dbl_p, C.c_void_p]),
+    "bf_pk_bin_ws_bytes": (C.c_size_t, [_i64, _i64]),
+    "bf_pk_bin": (C.c_int, [_i64, C.c_void_p, _P(_i64), C.c_double, C.c_double, C.c_double, _i64, _dbl_p, C.c_void_p,
+                            C.c_size_t, C.c_void_p]),
 }
 
 EXPORTED = tuple(_SIGS)

@@ -192,6 +192,20 @@ int bf_snap_displace_records(int dim, int64_t np, const void *cat, double L, dou
                              const bf_table *tab_host, int64_t ng, const void *ws, void *cat_out,
                              unsigned long long *npairs, void *stream);
 
+/* ---- Delta P(k) summary (examples/10_Reproduce_Schneider_deltaPk.ipynb, cells 1, 12, 15) ---- */
+/* NGP mass assignment of (folded) positions: grid[ix][iy][iz] += 1 with ix = int((x % Lfold) / (Lfold / ngrid))
+ * (`numba_histogram3d(Part % Lbox, ...)`).  Give either x, y, z or `records` ((M, x, y, z) float64, 16-byte
+ * aligned).  grid is [ngrid]^3 float64, += (zero it first); counts are whole numbers, so the result is exact. */
+int bf_pk_ngp_deposit(int64_t np, const double *x, const double *y, const double *z, const void *records, double Lfold,
+                      int64_t ngrid, double *grid, void *stream);
+/* Spherical average of |F|^2 over `nk` linear bins, F = rfftn(grid) as complex128 [ngrid][ngrid][ngrid/2+1];
+ * strides_host = element strides of the three axes (torch.fft returns a permuted dense view; NULL = C order).  val = 1 / (ngrid * d) of np.fft.fftfreq, k0 = kbins[0], dk = kbins[1] - kbins[0].
+ * out[0][b] = sum |F|^2, out[1][b] = sum k, out[2][b] = number of modes of bin b, each mirrored mode counted twice
+ * (equals np.bincount over the full cube).  Deterministic (no atomics). */
+size_t bf_pk_bin_ws_bytes(int64_t ngrid, int64_t nk);
+int bf_pk_bin(int64_t ngrid, const void *spectrum, const int64_t *strides_host, double val, double k0, double dk,
+              int64_t nk, double *out, void *ws, size_t ws_bytes, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -377,3 +377,47 @@ def test_param_tabulated_profiles_parity(gpu):
     with pytest.raises(AssertionError, match="You asked to use"):
         bf.BaryonifyShell(cfg["catalog"], cfg["field"], 20.0, dm, verbose=False).process()
     dm.p_keys = []
+
+
+# ------------------------------------------------------------------ Delta P(k)
+@pytest.mark.parametrize("ngrd,nk,factor", [(32, 12, 1), (48, 20, 2), (27, 9, 1), (64, 30, 8)])
+def test_delta_pk_matches_notebook_recipe(gpu, ngrd, nk, factor):
+    """NGP counts bit-exact, bin membership (mode counts, k centres) exact, P(k) to 1e-11 against the numpy
+    restatement of examples/10_Reproduce_Schneider_deltaPk.ipynb."""
+    from baryonification_b200.pk import PowerSpectrumGrid
+    from oracle import pk as opk
+    rng = np.random.default_rng(ngrd)
+    L = 200.0
+    pts = rng.uniform(0, L, (200_000, 3))
+    pts[:1000] += rng.normal(scale=3.0, size=(1000, 3))  # some particles outside [0, L): the fold wraps them
+    pts[0] = [0.0, L, L / factor]  # edges
+    ps = PowerSpectrumGrid(ngrd, L, nk)
+    grid = ps.density(pts, factor)
+    k, P, nm = ps.power(grid, factor)
+    ko, Po, kc, Map = opk.power(pts, ngrd, nk, L, factor)
+    assert np.array_equal(grid.cpu().numpy(), Map.astype(np.float64))
+    assert np.array_equal(nm, kc.astype(np.float64))
+    ok = kc > 0
+    assert np.allclose(k[ok], ko[ok], rtol=1e-13, atol=0)
+    assert np.allclose(P[ok], Po[ok], rtol=1e-11, atol=0)
+    k2, P2, _ = ps.power(grid, factor)
+    assert np.array_equal(P, P2) and np.array_equal(k, k2)  # deterministic reduction: bit-reproducible
+
+
+def test_delta_pk_suppression_of_a_baryonified_snapshot(gpu):
+    import baryonification_b200 as bf
+    from baryonification_b200 import synthetic as syn
+    from baryonification_b200.pk import PowerSpectrumGrid
+    from oracle import pk as opk
+    cfg = syn.config_snapshot(npart_side=64, nhalo=2000, dim=3, epsilon_max=5.0, L=200.0)
+    new = bf.BaryonifySnapshot(cfg["catalog"], cfg["field"], 5.0, cfg["model"], verbose=False).process()
+    ps = PowerSpectrumGrid(32, 200.0, 14)
+    res = ps.suppression(new, cfg["field"].cat, factors=(1, 4))
+    for f in (1, 4):
+        B = np.stack([new[k] for k in "xyz"], 1)
+        D = np.stack([cfg["field"].cat[k] for k in "xyz"], 1)
+        k, PB, kc, _ = opk.power(B, 32, 14, 200.0, f)
+        _, PD, _, _ = opk.power(D, 32, 14, 200.0, f)
+        ok = kc > 0
+        assert np.allclose(res[f"Factor{f}"]["S"][ok], (PB / PD)[ok], rtol=1e-10)
+        assert np.allclose(res[f"Factor{f}"]["k"][ok], k[ok], rtol=1e-13)
