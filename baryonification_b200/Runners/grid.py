@@ -68,12 +68,17 @@ class DefaultRunnerGrid:
 class BaryonifyGrid(DefaultRunnerGrid):
     def offsets_device(self, dev):
         G = self.GriddedMap
+        t0 = time.perf_counter()
         table, s, desc, bins, keep = self._prepare(displacement_host_table(self.model), True, dev)
         off = dv.zeros((G.map.size, s["dim"]), dev=dev)
         cnt = dv.pair_counter(dev)
+        torch.cuda.synchronize(dev)
+        self.timings["setup"] = time.perf_counter() - t0
+        t0 = time.perf_counter()
         _lib.call("bf_grid_baryonify_atomic", s["dim"], G.Npix, dv.ptr(bins), float(G.res), C.byref(desc),
                   C.byref(table.desc), dv.ptr(off), dv.ptr(cnt), dv.stream_ptr())
         self.npairs = int(cnt.item())
+        self.timings["accumulate"] = time.perf_counter() - t0
         del keep
         return off
 
@@ -81,10 +86,12 @@ class BaryonifyGrid(DefaultRunnerGrid):
         dev = dv.device(self.device)
         G = self.GriddedMap
         with torch.cuda.device(dev):
-            t0 = time.perf_counter()
-            off = self.offsets_device(dev)
+            t00 = time.perf_counter()
             orig = np.ascontiguousarray(G.map, dtype=np.float64).reshape(-1)
-            orig_d = dv.to_dev(orig, dev=dev, pinned=True)
+            up = dv.AsyncUpload(orig, dev)  # the map travels while the halos are set up and evaluated
+            off = self.offsets_device(dev)
+            t0 = time.perf_counter()
+            orig_d = up.result()
             new_d = dv.zeros(orig.size, dev=dev)
             dim = 2 if G.is2D else 3
             if self.regrid == "sorted":
@@ -93,12 +100,17 @@ class BaryonifyGrid(DefaultRunnerGrid):
                 ws = torch.empty(nb, dtype=torch.uint8, device=dev)
                 _lib.call("bf_grid_regrid_sorted", dim, G.Npix, dv.ptr(off), dv.ptr(orig_d), dv.ptr(new_d), dv.ptr(ws),
                           nb, dv.stream_ptr())
+                del ws
             else:
                 _lib.call("bf_grid_regrid", dim, G.Npix, dv.ptr(off), dv.ptr(orig_d), dv.ptr(new_d), dv.stream_ptr())
-            new_sum = float(new_d.sum().item())
-            new_map = new_d.cpu().numpy().reshape(G.map.shape)
-            self.timings["process"] = time.perf_counter() - t0
-        old_sum = np.sum(orig)  # Map2DRunner.py:611-613
+            new_sum_d, old_sum_d = new_d.sum(), orig_d.sum()
+            torch.cuda.synchronize(dev)
+            self.timings["regrid"] = time.perf_counter() - t0
+            t0 = time.perf_counter()
+            new_map = dv.to_host(new_d, True).reshape(G.map.shape)
+            new_sum, old_sum = float(new_sum_d.item()), float(old_sum_d.item())  # Map2DRunner.py:611-613
+            self.timings["d2h"] = time.perf_counter() - t0
+            self.timings["process"] = time.perf_counter() - t00
         assert np.isclose(new_sum, old_sum), \
             "ERROR in pixel regridding, sum(new_map) [%0.14e] != sum(oldmap) [%0.14e]" % (new_sum, old_sum)
         return new_map
@@ -117,6 +129,7 @@ class PaintProfilesGrid(DefaultRunnerGrid):
             _lib.call("bf_grid_paint_atomic", s["dim"], G.Npix, dv.ptr(bins), float(G.res), C.byref(desc),
                       C.byref(table.desc), dv.ptr(out), dv.ptr(cnt), dv.stream_ptr())
             self.npairs = int(cnt.item())
-            res = out.cpu().numpy().reshape(G.map.shape)
+            self.timings["accumulate"] = time.perf_counter() - t0
+            res = dv.to_host(out, True).reshape(G.map.shape)
             self.timings["process"] = time.perf_counter() - t0
         return res

@@ -1,0 +1,89 @@
+"""One pass over BASELINE.json's configurations on one B200: process() wall time (host buffers in/out), pair counts,
+pairs/s, and the CPU oracle (OpenMP) on the same or a bounded input.  Usage: measure_all.py [c1,c2,c3,c5a,c5b,pk]"""
+import json
+import os
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+from oracle import ref_shim
+
+ref_shim.install()
+import baryonification_b200 as bf
+from baryonification_b200 import synthetic as syn
+from oracle import runners as orc
+
+which = (sys.argv[1] if len(sys.argv) > 1 else "c1,c2,c3,c5a,pk").split(",")
+cores = os.cpu_count() or 1
+res = {}
+
+
+def timed(fn, n=3):
+    fn()
+    ts = []
+    for _ in range(n):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        out = fn()
+        torch.cuda.synchronize()
+        ts.append(time.perf_counter() - t0)
+    return out, min(ts)
+
+
+def report(name, d):
+    res[name] = d
+    print(name, json.dumps(d), flush=True)
+
+
+if "c1" in which:  # BaryonifyGrid 2-D 512^2 + 2k halos (+ PaintProfilesGrid), runs in full on the CPU too
+    cfg = syn.config_grid(npix=512, nhalo=2000, dim=2)
+    r = bf.BaryonifyGrid(cfg["catalog"], cfg["field"], 20.0, cfg["model"], verbose=False)
+    out, t = timed(r.process)
+    o = orc.BaryonifyGrid(cfg["catalog"], cfg["field"], 20.0, cfg["model"], nthreads=cores)
+    t0 = time.perf_counter(); ref = o.process(); tc = time.perf_counter() - t0
+    report("C1 BaryonifyGrid 2D 512^2, 2k halos", dict(pairs=r.npairs, gpu_process_ms=t * 1e3, gpu_pairs_per_s=r.npairs / t,
+           cpu_oracle_s=tc, cpu_cores=cores, relerr=float(np.max(np.abs(out - ref)) / np.max(np.abs(ref)))))
+    p = bf.PaintProfilesGrid(cfg["catalog"], cfg["field"], 20.0, cfg["paint_model"], verbose=False)
+    out, t = timed(p.process)
+    report("C1 PaintProfilesGrid 2D 512^2, 2k halos", dict(pairs=p.npairs, gpu_process_ms=t * 1e3, gpu_pairs_per_s=p.npairs / t))
+
+if "c2" in which:  # BaryonifyShell NSIDE 1024, 1e5 halos
+    cfg = syn.config_shell(nside=1024, nhalo=100_000)
+    r = bf.BaryonifyShell(cfg["catalog"], cfg["field"], 20.0, cfg["model"], verbose=False)
+    out, t = timed(r.process)
+    o = orc.BaryonifyShell(cfg["catalog"], cfg["field"], 20.0, cfg["model"], nthreads=cores)
+    t0 = time.perf_counter(); ref = o.process(); tc = time.perf_counter() - t0
+    report("C2 BaryonifyShell NSIDE 1024, 1e5 halos", dict(pairs=r.npairs, gpu_process_ms=t * 1e3, gpu_pairs_per_s=r.npairs / t,
+           stages_ms={k: round(v * 1e3, 2) for k, v in r.timings.items()}, cpu_oracle_s=tc, cpu_cores=cores,
+           relerr=float(np.max(np.abs(out - ref)) / np.max(np.abs(ref)))))
+
+if "c3" in which:  # PaintProfilesShell NSIDE 4096, 1e6 halos
+    cfg = syn.config_shell(nside=4096, nhalo=1_000_000, zero_map=True)
+    r = bf.PaintProfilesShell(cfg["catalog"], cfg["field"], 20.0, cfg["paint_model"], verbose=False)
+    out, t = timed(r.process)
+    report("C3 PaintProfilesShell NSIDE 4096, 1e6 halos", dict(pairs=r.npairs, gpu_process_ms=t * 1e3,
+           gpu_pairs_per_s=r.npairs / t, stages_ms={k: round(v * 1e3, 2) for k, v in r.timings.items()},
+           algorithmic_GBps_kernel=r.npairs * 16 / r.timings["accumulate"] / 1e9))
+    del out, r, cfg
+
+for tag, npix, nh in (("c5a", 512, 20_000), ("c5b", 1024, 100_000)):
+    if tag in which:  # BaryonifyGrid 3-D
+        cfg = syn.config_grid(npix=npix, nhalo=nh, dim=3)
+        r = bf.BaryonifyGrid(cfg["catalog"], cfg["field"], 20.0, cfg["model"], verbose=False,
+                             regrid=("sorted" if npix <= 512 else "atomic"))
+        out, t = timed(r.process, n=2)
+        report(f"C5 BaryonifyGrid 3D {npix}^3, {nh} halos", dict(pairs=r.npairs, gpu_process_ms=t * 1e3,
+               gpu_pairs_per_s=r.npairs / t, stages_ms={k: round(v * 1e3, 2) for k, v in r.timings.items()},
+               mass_relerr=float(abs(out.sum() / cfg["field"].map.sum() - 1))))
+        del out, r, cfg
+
+if "pk" in which:  # Delta P(k) of a baryonified 256^3 snapshot on a 256^3 mesh, folding factors 1 and 8
+    cfg = syn.config_snapshot(npart_side=256, nhalo=20_000, dim=3)
+    new = bf.BaryonifySnapshot(cfg["catalog"], cfg["field"], 5.0, cfg["model"], verbose=False).process()
+    ps = bf.PowerSpectrumGrid(256, cfg["field"].L, 180)
+    out, t = timed(lambda: ps.suppression(new, cfg["field"].cat, factors=(1, 8)), n=2)
+    S = out["Factor1"]["S"]
+    report("DeltaP(k) 256^3 particles, 256^3 mesh, Nk 180, factors 1+8", dict(gpu_ms=t * 1e3, S_min=float(np.nanmin(S)),
+           S_max=float(np.nanmax(S))))
