@@ -36,8 +36,8 @@ B_PARTICLE = 88.0  # snapshot: read (M,x,y,z) 32 + offsets 24 + write 32 (SURVEY
 B_SNAP_PAIR = 72.0 # snapshot: 24 B particle xyz read + 48 B offsets RMW per pair
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE gather_kernel<1> launch at the default workload, N = 1, from the
 # ncu --set full capture summarised in profiles/ (the kernel writes every pixel once; it never re-reads accumulators)
-GATHER_TRAFFIC_BYTES = 7.07e9
-SNAP_TRAFFIC_BYTES = 11.66e9
+GATHER_TRAFFIC_BYTES = 7.06e9
+SNAP_TRAFFIC_BYTES = 10.69e9
 
 
 def parse():
@@ -442,7 +442,7 @@ def run_snapshot(args, rank, local_rank, world):
                               "unit": "GB/s", "frac": ach / peak, "peak_source": peak_src, "kernel_ms": ms_k,
                               "traffic": SNAP_TRAFFIC_BYTES if (world == 1 and args.npart_side == 512) else None,
                               "algorithmic_bytes": {"per_particle": B_PARTICLE, "per_pair": B_SNAP_PAIR}},
-                 "e2e": e2e, "gpu_launches": 12 * args.steps, "clocks": clocks}
+                 "e2e": e2e, "gpu_launches": 8 * args.steps, "clocks": clocks}
         if not args.no_cpu:
             from oracle import runners as orc
             cores = os.cpu_count() or 1
