@@ -21,6 +21,77 @@ from ..tables import displacement_host_table
 __all__ = ["DefaultRunnerSnapshot", "BaryonifySnapshot"]
 
 
+class _RecordPipeline:
+    """Particle records: pageable numpy -> pinned staging -> HBM -> kernel -> pinned result, chunk by chunk.
+
+    PCIe is full duplex, so the upload of chunk i+1, the kernel on chunk i and the read-back of chunk i-1 overlap; a
+    helper thread does the pageable -> pinned copies (started in the constructor, i.e. during halo set-up).  The
+    result array is backed by page-locked memory from torch's caching host allocator."""
+
+    CHUNK = int(os.environ.get("BF_SNAP_CHUNK", 1 << 20))  # particles per chunk (32 MiB of records)
+
+    def __init__(self, rec, dev):
+        import threading
+        self.rec, self.dev = rec, dev
+        n = rec.shape[0]
+        self.bounds = [(i, min(i + self.CHUNK, n)) for i in range(0, n, self.CHUNK)]
+        self.h2d, self.d2h = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+        self.d_in = torch.empty((n, 4), dtype=torch.float64, device=dev)
+        self.ready = [torch.cuda.Event() for _ in self.bounds]
+        self.queued = [threading.Event() for _ in self.bounds]
+        self.err = None
+        self.th = threading.Thread(target=self._upload, daemon=True)
+        self.th.start()
+
+    def _upload(self):
+        try:
+            import warnings
+            with warnings.catch_warnings():  # a read-only input is only ever read here
+                warnings.simplefilter("ignore")
+                src = torch.from_numpy(self.rec)
+            with torch.cuda.device(self.dev):
+                stage = [torch.empty((min(self.CHUNK, src.shape[0]), 4), dtype=torch.float64, pin_memory=True)
+                         for _ in range(3)]
+                free = [None] * 3
+                for i, (a, b) in enumerate(self.bounds):
+                    k = i % 3
+                    if free[k] is not None:
+                        free[k].synchronize()  # the H2D copy that last used this staging buffer is done
+                    stage[k][: b - a].copy_(src[a:b])
+                    with torch.cuda.stream(self.h2d):
+                        self.d_in[a:b].copy_(stage[k][: b - a], non_blocking=True)
+                        self.ready[i].record(self.h2d)
+                        free[k] = self.ready[i]
+                    self.queued[i].set()
+        except BaseException as e:  # re-raised in run()
+            self.err = e
+            for q in self.queued:
+                q.set()
+
+    def run(self, kernel):
+        """kernel(rec_chunk, out_chunk, stream) per chunk on the current stream; returns the host result array."""
+        n = self.rec.shape[0]
+        cur = torch.cuda.current_stream(self.dev)
+        d_out = torch.empty((n, 4), dtype=torch.float64, device=self.dev)
+        out = torch.empty((n, 4), dtype=torch.float64, pin_memory=True)
+        done = torch.cuda.Event()
+        for i, (a, b) in enumerate(self.bounds):
+            self.queued[i].wait()
+            if self.err is not None:
+                raise self.err
+            cur.wait_event(self.ready[i])
+            kernel(self.d_in[a:b], d_out[a:b], cur)
+            done = torch.cuda.Event()
+            done.record(cur)
+            self.d2h.wait_event(done)
+            with torch.cuda.stream(self.d2h):
+                out[a:b].copy_(d_out[a:b], non_blocking=True)
+        self.th.join()
+        self.d2h.synchronize()
+        cur.synchronize()
+        return out.numpy()
+
+
 class DefaultRunnerSnapshot:
     def __init__(self, HaloNDCatalog, ParticleSnapshot, epsilon_max, model, mass_def=None, verbose=True,
                  KDTree_kwargs={}, *, device=None):
@@ -89,19 +160,18 @@ class BaryonifySnapshot(DefaultRunnerSnapshot):
             t0 = time.perf_counter()
             cat = S.cat
             fast = self._is_reference_layout(cat)
-            up = dv.AsyncUpload(cat.view(np.float64).reshape(-1, 4), dev) if fast else None  # travels during set-up
+            pipe = _RecordPipeline(cat.view(np.float64).reshape(-1, 4), dev) if fast else None  # travels during set-up
             st = self._setup(dev)
             dim, s = st["dim"], st["s"]
             cnt = dv.pair_counter(dev)
             self.timings["setup"] = time.perf_counter() - t0
             t1 = time.perf_counter()
             if fast:
-                rec = up.result()
-                rec_out = torch.empty_like(rec)
-                _lib.call("bf_snap_displace_records", dim, rec.shape[0], dv.ptr(rec), st["L"], float(s["a"]),
-                          C.byref(st["desc"]), C.byref(st["table"].desc), st["ng"], dv.ptr(st["ws"]), dv.ptr(rec_out),
-                          dv.ptr(cnt), dv.stream_ptr())
-                new_cat = dv.to_host(rec_out, True).reshape(-1).view(cat.dtype).reshape(cat.shape)
+                def displace(rec, rec_out, stream):
+                    _lib.call("bf_snap_displace_records", dim, rec.shape[0], dv.ptr(rec), st["L"], float(s["a"]),
+                              C.byref(st["desc"]), C.byref(st["table"].desc), st["ng"], dv.ptr(st["ws"]),
+                              dv.ptr(rec_out), dv.ptr(cnt), C.c_void_p(stream.cuda_stream))
+                new_cat = pipe.run(displace).reshape(-1).view(cat.dtype).reshape(cat.shape)
             else:  # any other record layout: field by field
                 names = ("x", "y", "z")[:dim]
                 xin = [dv.to_dev(cat[k], dev=dev, pinned=True) for k in names]

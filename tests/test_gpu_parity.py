@@ -243,6 +243,25 @@ def test_snapshot_dense_block_uses_several_queue_rounds(gpu):
         assert np.max(np.abs(got[k] - ref[k])) < 1e-9
 
 
+@pytest.mark.gpu
+def test_snapshot_chunked_transfer_pipeline_equals_one_shot(gpu, monkeypatch):
+    """process() streams the records through HBM chunk by chunk (upload / kernel / read-back overlapped); ragged last
+    chunk, more chunks than staging buffers, read-only input array."""
+    import baryonification_b200 as bf
+    from baryonification_b200 import synthetic as syn
+    from baryonification_b200.Runners import snapshot as snap
+    cfg = syn.config_snapshot(npart_side=20, nhalo=120, dim=3, epsilon_max=5.0, L=100.0)
+    want_r = bf.BaryonifySnapshot(cfg["catalog"], cfg["field"], 5.0, cfg["model"], verbose=False)
+    want = want_r.process()
+    monkeypatch.setattr(snap._RecordPipeline, "CHUNK", 999)  # 8000 particles -> 9 chunks, the last one short
+    cfg["field"].cat.flags.writeable = False
+    got_r = bf.BaryonifySnapshot(cfg["catalog"], cfg["field"], 5.0, cfg["model"], verbose=False)
+    got = got_r.process()
+    assert got_r.npairs == want_r.npairs
+    for k in want.dtype.names:
+        assert np.array_equal(got[k], want[k]), k
+
+
 # ------------------------------------------------------------------ committed reference fixtures
 import cases  # noqa: E402
 
