@@ -21,7 +21,7 @@ __all__ = ["DefaultRunnerGrid", "BaryonifyGrid", "PaintProfilesGrid"]
 
 class DefaultRunnerGrid:
     def __init__(self, HaloNDCatalog, GriddedMap, epsilon_max, model, use_ellipticity=False, mass_def=None,
-                 verbose=True, *, device=None, regrid="sorted"):
+                 verbose=True, *, device=None, regrid="gather"):
         self.HaloNDCatalog = HaloNDCatalog
         self.GriddedMap = GriddedMap
         self.cosmo = HaloNDCatalog.cosmology
@@ -31,7 +31,9 @@ class DefaultRunnerGrid:
         self.verbose = verbose
         self.use_ellipticity = use_ellipticity
         self.device = device
-        self.regrid = regrid  # re-binning: "sorted" (deterministic, default) | "atomic"
+        # re-binning: "gather" (deterministic, default; falls back to "sorted" for very wide displacement windows)
+        # | "sorted" (deterministic, 25 B of workspace per deposit) | "atomic"
+        self.regrid = regrid
         self.npairs = None
         self.timings = {}
         if use_ellipticity:  # Map2DRunner.py:266-272
@@ -94,8 +96,22 @@ class BaryonifyGrid(DefaultRunnerGrid):
             orig_d = up.result()
             new_d = dv.zeros(orig.size, dev=dev)
             dim = 2 if G.is2D else 3
-            if self.regrid == "sorted":
-                lib = _lib.load(require_cuda=True)
+            lib = _lib.load(require_cuda=True)
+            mode = self.regrid
+            if mode == "gather":
+                ws = torch.empty(lib.bf_grid_regrid_gather_ws_bytes(), dtype=torch.uint8, device=dev)
+                win = (C.c_int * 3)()
+                rc = lib.bf_grid_regrid_gather(dim, G.Npix, dv.ptr(off), dv.ptr(orig_d), dv.ptr(new_d), dv.ptr(ws),
+                                               ws.numel(), win, dv.stream_ptr())
+                self.regrid_window = tuple(win)
+                if rc == -3:  # BF_E_WINDOW: displacements span too many cells for the gather
+                    mode = "sorted"
+                else:
+                    _lib.check(rc, "bf_grid_regrid_gather")
+            self.regrid_used = mode
+            if mode == "gather":
+                pass
+            elif mode == "sorted":
                 nb = lib.bf_grid_regrid_sorted_ws_bytes(dim, G.Npix)
                 ws = torch.empty(nb, dtype=torch.uint8, device=dev)
                 _lib.call("bf_grid_regrid_sorted", dim, G.Npix, dv.ptr(off), dv.ptr(orig_d), dv.ptr(new_d), dv.ptr(ws),

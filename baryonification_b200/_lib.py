@@ -85,6 +85,9 @@ _SIGS = {
     "bf_grid_regrid": (C.c_int, [C.c_int, _i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p]),
     "bf_grid_regrid_sorted_ws_bytes": (C.c_size_t, [C.c_int, _i64]),
     "bf_grid_regrid_sorted": (C.c_int, [C.c_int, _i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "bf_grid_regrid_gather_ws_bytes": (C.c_size_t, []),
+    "bf_grid_regrid_gather": (C.c_int, [C.c_int, _i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p, C.c_size_t,
+                                        C.POINTER(C.c_int), C.c_void_p]),
     "bf_snap_grid_cells": (_i64, [C.c_int, C.c_double, C.c_double]),
     "bf_snap_ws_bytes": (C.c_size_t, [C.c_int, _i64, C.c_double, _i64, _i64]),
     "bf_snap_bin_halos": (C.c_int, [C.c_int, C.c_double, _i64, _P(SnapHalos), _i64, C.c_void_p, C.c_size_t, _P(_i64),

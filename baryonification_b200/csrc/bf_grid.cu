@@ -11,39 +11,9 @@
 //   * BaryonifyGrid does NOT zero non-finite values per halo: NaN accumulates into the cell and the cell's
 //     whole offset is zeroed before re-binning (:591, :601); PaintProfilesGrid masks per halo (:803-807).
 #include "bf_common.cuh"
+#include "bf_grid_common.cuh"
 
 #define GR_THREADS 256
-
-__device__ __forceinline__ double cut_coord(i64 i, i64 N, double res) {  // np.linspace(-N/2, N/2, N)[i]*res
-    double start = -(double)N / 2.0, stop = (double)N / 2.0;
-    double step = (stop - start) / (double)(N - 1);
-    double y = (i == N - 1) ? stop : ((double)i * step + start);
-    return y * res;
-}
-
-__device__ __forceinline__ i64 wrap_once(i64 i, i64 N) {  // pick_indices (:394-423)
-    if (i < 0) i += N;
-    if (i >= N) i -= N;
-    return i;
-}
-
-// np.argmin(np.abs(bins - x)): first index of the minimum.  bins are ascending, so a bisection lands
-// next to it and the exact |.| comparison over a +-2 window reproduces the first-minimum rule.
-__device__ __forceinline__ i64 argmin_abs(const double *__restrict__ bins, i64 n, double x) {
-    i64 lo = 0, hi = n - 1;
-    while (hi - lo > 1) {
-        i64 mid = (lo + hi) >> 1;
-        if (bins[mid] <= x) lo = mid; else hi = mid;
-    }
-    i64 b0 = (lo - 2 > 0) ? lo - 2 : 0, b1 = (hi + 2 < n - 1) ? hi + 2 : n - 1;
-    i64 best = b0;
-    double bv = fabs(bins[b0] - x);
-    for (i64 i = b0 + 1; i <= b1; ++i) {
-        double v = fabs(bins[i] - x);
-        if (v < bv) { bv = v; best = i; }
-    }
-    return best;
-}
 
 template <int DIM, int MODE>  // MODE 0 = baryonify, 1 = paint
 __global__ void __launch_bounds__(GR_THREADS) grid_atomic_kernel(i64 npix, const double *__restrict__ bins,

@@ -26,6 +26,7 @@ extern "C" {
 #define BF_OK 0
 #define BF_E_INVALID (-1)   /* bad argument */
 #define BF_E_WORKSPACE (-2) /* workspace too small */
+#define BF_E_WINDOW (-3)    /* bf_grid_regrid_gather: displacement window too wide, use bf_grid_regrid_sorted */
 
 const char *bf_last_error(void);
 int bf_version(void);
@@ -162,6 +163,18 @@ int bf_grid_regrid(int dim, int64_t npix, const double *offsets, const double *o
 size_t bf_grid_regrid_sorted_ws_bytes(int dim, int64_t npix);
 int bf_grid_regrid_sorted(int dim, int64_t npix, const double *offsets, const double *orig, double *new_map, void *ws,
                           size_t ws_bytes, void *stream);
+
+/* deterministic destination-gather variant (same bits as the sorted one, no per-deposit workspace): a first pass
+ * measures the range of floor(displaced position) - cell per axis; every cell then sums the deposits of the sources
+ * inside that window in ascending source order.  ws = bf_grid_regrid_gather_ws_bytes() device bytes;
+ * window_host[3] (may be NULL) receives the window length per axis.  BF_E_WINDOW when a cell would have to scan more
+ * than BF_GRID_GATHER_MAX_WINDOW_{2D,3D} sources (fall back to bf_grid_regrid_sorted).  new_map is +=.
+ * Synchronises `stream` once. */
+#define BF_GRID_GATHER_MAX_WINDOW_2D 121
+#define BF_GRID_GATHER_MAX_WINDOW_3D 343
+size_t bf_grid_regrid_gather_ws_bytes(void);
+int bf_grid_regrid_gather(int dim, int64_t npix, const double *offsets, const double *orig, double *new_map, void *ws,
+                          size_t ws_bytes, int *window_host, void *stream);
 
 /* ---- Snapshot runner (SnapshotRunner.py) ---- */
 typedef struct {

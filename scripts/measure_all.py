@@ -72,7 +72,7 @@ for tag, npix, nh in (("c5a", 512, 20_000), ("c5b", 1024, 100_000)):
     if tag in which:  # BaryonifyGrid 3-D
         cfg = syn.config_grid(npix=npix, nhalo=nh, dim=3)
         r = bf.BaryonifyGrid(cfg["catalog"], cfg["field"], 20.0, cfg["model"], verbose=False,
-                             regrid=("sorted" if npix <= 512 else "atomic"))
+                             regrid="gather")
         out, t = timed(r.process, n=2)
         report(f"C5 BaryonifyGrid 3D {npix}^3, {nh} halos", dict(pairs=r.npairs, gpu_process_ms=t * 1e3,
                gpu_pairs_per_s=r.npairs / t, stages_ms={k: round(v * 1e3, 2) for k, v in r.timings.items()},

@@ -368,6 +368,67 @@ def test_grid_regrid_sorted_matches_atomic_and_oracle(gpu, dim, npix):
     assert abs(s1.sum() - tot) / tot < MASS_RTOL
 
 
+def _grid_regrid(kind, dim, npix, off, orig):
+    """C-ABI call of one re-binning variant on host arrays -> (status, new map, window)."""
+    import ctypes as C
+    import torch
+    from baryonification_b200 import _device as dv, _lib
+    lib = _lib.load(require_cuda=True)
+    off_d, orig_d = dv.to_dev(off), dv.to_dev(orig)
+    new_d = dv.zeros(orig.size)
+    win = (C.c_int * 3)()
+    if kind == "gather":
+        ws = torch.empty(lib.bf_grid_regrid_gather_ws_bytes(), dtype=torch.uint8, device=off_d.device)
+        rc = lib.bf_grid_regrid_gather(dim, npix, dv.ptr(off_d), dv.ptr(orig_d), dv.ptr(new_d), dv.ptr(ws), ws.numel(),
+                                       win, dv.stream_ptr())
+    else:
+        nb = lib.bf_grid_regrid_sorted_ws_bytes(dim, npix)
+        ws = torch.empty(nb, dtype=torch.uint8, device=off_d.device)
+        rc = lib.bf_grid_regrid_sorted(dim, npix, dv.ptr(off_d), dv.ptr(orig_d), dv.ptr(new_d), dv.ptr(ws), nb,
+                                       dv.stream_ptr())
+    torch.cuda.synchronize()
+    return rc, new_d.cpu().numpy(), tuple(win)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dim,npix,amp", [(2, 5, 0.9), (2, 37, 0.4), (2, 64, 2.7), (2, 100, 4.6), (3, 5, 0.6), (3, 19, 0.9),
+                                          (3, 32, 1.7), (3, 21, 2.4), (2, 33, 0.0)])
+def test_grid_regrid_gather_is_bit_identical_to_the_sorted_serial_order_sum(gpu, dim, npix, amp):
+    """Destination gather == counting sort (both = the reference's serial summation order), for displacement windows of
+    2..7 cells per axis, grids that are not a multiple of the tile, periodic wrap of the window, non-finite offsets and
+    exact-integer displacements (zero-weight deposits)."""
+    rng = np.random.default_rng(100 * dim + npix)
+    ncell = npix ** dim
+    off = rng.uniform(-amp, amp, (ncell, dim))
+    off[rng.integers(0, ncell, 7)] = np.nan
+    off[rng.integers(0, ncell, 7), 0] = np.inf
+    off[rng.integers(0, ncell, 9)] = np.round(off[rng.integers(0, ncell, 9)])
+    orig = rng.lognormal(0.0, 1.0, ncell)
+    orig[rng.integers(0, ncell, 5)] = 0.0
+    rc_s, want, _ = _grid_regrid("sorted", dim, npix, off, orig)
+    rc_g, got, win = _grid_regrid("gather", dim, npix, off, orig)
+    assert rc_s == 0 and rc_g == 0
+    assert all(2 <= w <= 2 * int(np.ceil(amp)) + 2 for w in win[:dim])
+    assert np.array_equal(got, want)
+    assert abs(got.sum() - orig.sum()) / orig.sum() < 1e-13
+
+
+@pytest.mark.gpu
+def test_grid_regrid_gather_reports_a_too_wide_window_and_the_runner_falls_back(gpu):
+    import baryonification_b200 as bf
+    from baryonification_b200 import synthetic as syn
+    rng = np.random.default_rng(5)
+    off = rng.uniform(-9.0, 9.0, (40 * 40, 2))
+    rc, _, win = _grid_regrid("gather", 2, 40, off, np.ones(1600))
+    assert rc == -3 and win[0] * win[1] > 121  # BF_E_WINDOW
+    cfg = syn.config_grid(npix=64, nhalo=120, dim=2, epsilon_max=20.0)
+    g = bf.BaryonifyGrid(cfg["catalog"], cfg["field"], 20.0, cfg["model"], verbose=False)
+    a = g.process()
+    assert g.regrid_used == "gather" and max(g.regrid_window) <= 4
+    s = bf.BaryonifyGrid(cfg["catalog"], cfg["field"], 20.0, cfg["model"], verbose=False, regrid="sorted").process()
+    assert np.array_equal(a, s)
+
+
 # ------------------------------------------------------------------ property-keyed tables (p_keys)
 def test_param_tabulated_profiles_parity(gpu):
     """ParamTabulatedProfile-style tables [Nz, NM, NR, Ncdelta] with a per-halo `cdelta` column
