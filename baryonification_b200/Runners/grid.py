@@ -21,7 +21,7 @@ __all__ = ["DefaultRunnerGrid", "BaryonifyGrid", "PaintProfilesGrid"]
 
 class DefaultRunnerGrid:
     def __init__(self, HaloNDCatalog, GriddedMap, epsilon_max, model, use_ellipticity=False, mass_def=None,
-                 verbose=True, *, device=None, regrid="gather"):
+                 verbose=True, *, device=None, regrid="gather", variant="gather"):
         self.HaloNDCatalog = HaloNDCatalog
         self.GriddedMap = GriddedMap
         self.cosmo = HaloNDCatalog.cosmology
@@ -34,6 +34,8 @@ class DefaultRunnerGrid:
         # re-binning: "gather" (deterministic, default; falls back to "sorted" for very wide displacement windows)
         # | "sorted" (deterministic, 25 B of workspace per deposit) | "atomic"
         self.regrid = regrid
+        # pair loop: "gather" (cell-owner, deterministic catalogue-order sums, default) | "atomic" (halo-centric)
+        self.variant = variant
         self.npairs = None
         self.timings = {}
         if use_ellipticity:  # Map2DRunner.py:266-272
@@ -67,6 +69,35 @@ class DefaultRunnerGrid:
         return table, s, desc, bins, (t, rows)
 
 
+    def _accumulate(self, mode, s, desc, bins, table, out, cnt, dev):
+        """The per-halo loop (Map2DRunner.py:476-580 / :714-810) into ``out``: cell-owner gather, or atomics."""
+        G = self.GriddedMap
+        lib = _lib.load(require_cuda=True)
+        dim, nh = s["dim"], s["cut"].size
+        self.variant_used = self.variant
+        if self.variant == "gather" and nh > 0 and int(np.max(s["Nsize"])) > G.Npix:
+            self.variant_used = "atomic"  # a cut-out wider than the grid: numpy's duplicate-dropping += semantics
+        if self.variant_used == "gather" and nh > 0:
+            max_entries, n = 0, C.c_int64()
+            for _ in range(2):  # counting pass first (exact size), then the real one
+                nb = lib.bf_grid_bin_ws_bytes(dim, G.Npix, nh, max_entries)
+                ws = torch.empty(nb, dtype=torch.uint8, device=dev)
+                rc = lib.bf_grid_bin_halos(dim, G.Npix, dv.ptr(bins), C.byref(desc), table.nr, max_entries, dv.ptr(ws),
+                                           nb, C.byref(n), dv.stream_ptr())
+                if rc == -2 and n.value > max_entries:
+                    max_entries = n.value
+                    continue
+                _lib.check(rc, "bf_grid_bin_halos")
+                break
+            self.nentries = n.value
+            _lib.call("bf_grid_gather", dim, mode, G.Npix, float(G.res), C.byref(desc), C.byref(table.desc), max_entries,
+                      dv.ptr(ws), dv.ptr(out), dv.ptr(cnt), dv.stream_ptr())
+        else:
+            _lib.call("bf_grid_paint_atomic" if mode else "bf_grid_baryonify_atomic", dim, G.Npix, dv.ptr(bins),
+                      float(G.res), C.byref(desc), C.byref(table.desc), dv.ptr(out), dv.ptr(cnt), dv.stream_ptr())
+        self.npairs = int(cnt.item())
+
+
 class BaryonifyGrid(DefaultRunnerGrid):
     def offsets_device(self, dev):
         G = self.GriddedMap
@@ -77,9 +108,7 @@ class BaryonifyGrid(DefaultRunnerGrid):
         torch.cuda.synchronize(dev)
         self.timings["setup"] = time.perf_counter() - t0
         t0 = time.perf_counter()
-        _lib.call("bf_grid_baryonify_atomic", s["dim"], G.Npix, dv.ptr(bins), float(G.res), C.byref(desc),
-                  C.byref(table.desc), dv.ptr(off), dv.ptr(cnt), dv.stream_ptr())
-        self.npairs = int(cnt.item())
+        self._accumulate(0, s, desc, bins, table, off, cnt, dev)
         self.timings["accumulate"] = time.perf_counter() - t0
         del keep
         return off
@@ -142,9 +171,7 @@ class PaintProfilesGrid(DefaultRunnerGrid):
                                                         False, dev)
             out = dv.zeros(G.map.size, dev=dev)
             cnt = dv.pair_counter(dev)
-            _lib.call("bf_grid_paint_atomic", s["dim"], G.Npix, dv.ptr(bins), float(G.res), C.byref(desc),
-                      C.byref(table.desc), dv.ptr(out), dv.ptr(cnt), dv.stream_ptr())
-            self.npairs = int(cnt.item())
+            self._accumulate(1, s, desc, bins, table, out, cnt, dev)
             self.timings["accumulate"] = time.perf_counter() - t0
             res = dv.to_host(out, True).reshape(G.map.shape)
             self.timings["process"] = time.perf_counter() - t0

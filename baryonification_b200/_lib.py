@@ -82,6 +82,11 @@ _SIGS = {
                                            _dbl_p, C.c_void_p]),
     "bf_grid_paint_atomic": (C.c_int, [C.c_int, _i64, _dbl_p, C.c_double, _P(GridHalos), _P(Table), _dbl_p,
                                        _dbl_p, C.c_void_p]),
+    "bf_grid_bin_ws_bytes": (C.c_size_t, [C.c_int, _i64, _i64, _i64]),
+    "bf_grid_bin_halos": (C.c_int, [C.c_int, _i64, _dbl_p, _P(GridHalos), _i64, _i64, C.c_void_p, C.c_size_t,
+                                    _P(_i64), C.c_void_p]),
+    "bf_grid_gather": (C.c_int, [C.c_int, C.c_int, _i64, C.c_double, _P(GridHalos), _P(Table), _i64, C.c_void_p,
+                                 _dbl_p, _dbl_p, C.c_void_p]),
     "bf_grid_regrid": (C.c_int, [C.c_int, _i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p]),
     "bf_grid_regrid_sorted_ws_bytes": (C.c_size_t, [C.c_int, _i64]),
     "bf_grid_regrid_sorted": (C.c_int, [C.c_int, _i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p, C.c_size_t, C.c_void_p]),

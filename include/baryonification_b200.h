@@ -156,6 +156,20 @@ int bf_grid_baryonify_atomic(int dim, int64_t npix, const double *bins, double r
 /* PaintProfilesGrid per-halo loop (:714-810): out[cell] += P masked by finite & r < cut */
 int bf_grid_paint_atomic(int dim, int64_t npix, const double *bins, double res, const bf_grid_halos *h_host,
                          const bf_table *tab_host, double *out, unsigned long long *npairs, void *stream);
+/* Deterministic cell-owner variant of the two loops above.  bf_grid_bin_halos intersects every halo's cut-out box
+ * (pick_indices :394-423) with tiles of 8^3 (3-D) / 16 x 32 (2-D) cells and leaves, per tile, its halos in catalogue
+ * order; bf_grid_gather runs one CTA per tile, one thread per cell, and sums the cell's pairs in registers in that
+ * order (the reference's serial order): no atomics, bit-reproducible, out is += once per cell.
+ * Protocol as bf_shell_bin_halos: *nentries_host = exact number of (tile, halo) entries, BF_E_WORKSPACE when it exceeds
+ * max_entries (call again with a workspace of bf_grid_bin_ws_bytes for it).  BF_E_WINDOW when a cut-out is wider than
+ * the grid (Nsize > npix: the reference's fancy-index += then drops duplicates; use the halo-centric kernels).
+ * nr = row length of h_host->rows (= the table's nr).  mode 0 = BaryonifyGrid, 1 = PaintProfilesGrid.  The same
+ * max_entries must be given to bf_grid_gather.  bf_grid_bin_halos synchronises `stream` once. */
+size_t bf_grid_bin_ws_bytes(int dim, int64_t npix, int64_t nh, int64_t max_entries);
+int bf_grid_bin_halos(int dim, int64_t npix, const double *bins, const bf_grid_halos *h_host, int64_t nr,
+                      int64_t max_entries, void *ws, size_t ws_bytes, int64_t *nentries_host, void *stream);
+int bf_grid_gather(int dim, int mode, int64_t npix, double res, const bf_grid_halos *h_host, const bf_table *tab_host,
+                   int64_t max_entries, const void *ws, double *out, unsigned long long *npairs, void *stream);
 /* BaryonifyGrid tail (:583-607 + regrid_pixels_2D/3D :14-163): CIC-equivalent periodic deposit. */
 int bf_grid_regrid(int dim, int64_t npix, const double *offsets, const double *orig, double *new_map, void *stream);
 

@@ -33,8 +33,12 @@ def ev(fn, n=5):
     return min(ts)
 
 
-off = r.offsets_device(dev)
-print("pairs", r.npairs, "accumulate (host clock, incl. set-up sync) ms", r.timings["accumulate"] * 1e3)
+for variant in ("atomic", "gather"):
+    r.variant = variant
+    for _ in range(2):
+        off = r.offsets_device(dev)
+    print(variant, "pairs", r.npairs, "accumulate (host clock: bin + pair kernel) ms %.2f" % (r.timings["accumulate"] * 1e3),
+          "entries", getattr(r, "nentries", None))
 orig = dv.to_dev(np.ascontiguousarray(cfg["field"].map).reshape(-1))
 new = dv.zeros(orig.numel())
 ncell = orig.numel()

@@ -368,6 +368,50 @@ def test_grid_regrid_sorted_matches_atomic_and_oracle(gpu, dim, npix):
     assert abs(s1.sum() - tot) / tot < MASS_RTOL
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("dim,npix,nhalo,eps,ell", [(2, 64, 120, 20.0, False), (2, 75, 200, 30.0, True), (2, 512, 2000, 20.0, False),
+                                                    (3, 24, 40, 8.0, False), (3, 37, 120, 12.0, False), (3, 64, 300, 20.0, False)])
+def test_grid_cell_owner_gather_equals_halo_centric_atomics(gpu, dim, npix, nhalo, eps, ell):
+    """The two pair loops visit the same (halo, cell) set (exact pair count); values agree to rounding (different
+    summation order, table-based ln); grids that are not a multiple of the tile; cut-outs wrapping the box."""
+    import baryonification_b200 as bf
+    from baryonification_b200 import synthetic as syn
+    L = 500.0 / 0.7 if dim == 2 else 100.0
+    cfg = syn.config_grid(npix=npix, nhalo=nhalo, dim=dim, epsilon_max=eps, L=L, ellipticity=ell)
+    kw = dict(verbose=False, use_ellipticity=cfg.get("use_ellipticity", False))
+    for cls, model in (("BaryonifyGrid", cfg["model"]), ("PaintProfilesGrid", cfg["paint_model"])):
+        g = getattr(bf, cls)(cfg["catalog"], cfg["field"], eps, model, variant="gather", **kw)
+        a = getattr(bf, cls)(cfg["catalog"], cfg["field"], eps, model, variant="atomic", **kw)
+        got, want = g.process(), a.process()
+        assert g.variant_used == "gather" and a.variant_used == "atomic"
+        assert g.npairs == a.npairs and g.npairs > 500
+        assert relmax(got, want) < 1e-11
+        if cls == "PaintProfilesGrid":
+            assert np.array_equal(got != 0, want != 0)
+        again = getattr(bf, cls)(cfg["catalog"], cfg["field"], eps, model, variant="gather", **kw).process()
+        assert np.array_equal(got, again)  # register sums in catalogue order: bit-reproducible
+
+
+@pytest.mark.gpu
+def test_grid_bin_refuses_a_cut_out_wider_than_the_grid(gpu):
+    """Nsize > npix: numpy's fancy-index += drops the duplicate cells, which only the halo-centric path mimics; the
+    runners never get there (Map2DRunner.py:489 / :733 clip the cut-out to half the box), the ABI says so."""
+    import ctypes as C
+    import torch
+    from baryonification_b200 import _device as dv, _lib
+    lib = _lib.load(require_cuda=True)
+    t = {k: dv.to_dev(np.asarray(v, dtype=np.float64)) for k, v in dict(pos=[[3.0, 4.0]], cut=[1.0], shift=[0.0],
+                                                                         rows=np.zeros((1, 8)), bins=np.arange(16.0)).items()}
+    ns = dv.to_dev(np.array([40]), dtype=np.int64)
+    desc = _lib.GridHalos(t["pos"].data_ptr(), ns.data_ptr(), t["cut"].data_ptr(), t["shift"].data_ptr(),
+                          t["rows"].data_ptr(), None, 1)
+    nb = lib.bf_grid_bin_ws_bytes(2, 16, 1, 64)
+    ws = torch.empty(nb, dtype=torch.uint8, device=t["pos"].device)
+    n = C.c_int64()
+    rc = lib.bf_grid_bin_halos(2, 16, dv.ptr(t["bins"]), C.byref(desc), 8, 64, dv.ptr(ws), nb, C.byref(n), dv.stream_ptr())
+    assert rc == -3 and b"wider than the grid" in lib.bf_last_error()
+
+
 def _grid_regrid(kind, dim, npix, off, orig):
     """C-ABI call of one re-binning variant on host arrays -> (status, new map, window)."""
     import ctypes as C
