@@ -49,12 +49,15 @@ struct gg_ws {
     gh_rec *recs;
     long long *cnt, *offs;  // [nh + 1]
     int *tstart, *tend;     // [ntiles]
+    double *axis;           // ln r grid [nr], 1 / (g[k+1] - g[k]) [nr], ln table [2 * BF_LOGTAB]: filled by bf_grid_gather
     unsigned long long *keys, *keys_alt;
     void *cub_tmp;
     size_t cub_bytes, total;
 };
 
 __host__ __device__ inline int tiles_per_axis(int npix, int T) { return (npix + T - 1) / T; }
+
+constexpr int GG_MAX_NR = 8192;  // longest radial axis staged in shared memory
 
 static gg_ws gg_layout(void *base, int dim, i64 npix, i64 nh, i64 max_entries) {
     gg_ws w;
@@ -70,6 +73,7 @@ static gg_ws gg_layout(void *base, int dim, i64 npix, i64 nh, i64 max_entries) {
     w.offs = (long long *)take(sizeof(long long) * (size_t)(nh + 1));
     w.tstart = (int *)take(sizeof(int) * nt);
     w.tend = (int *)take(sizeof(int) * nt);
+    w.axis = (double *)take(sizeof(double) * (2 * GG_MAX_NR + 2 * BF_LOGTAB));
     w.keys = (unsigned long long *)take(sizeof(unsigned long long) * (size_t)max_entries);
     w.keys_alt = (unsigned long long *)take(sizeof(unsigned long long) * (size_t)max_entries);
     size_t c1 = 0, c2 = 0;
@@ -165,9 +169,19 @@ __global__ void __launch_bounds__(256) gg_bounds_kernel(long long n, const unsig
     if (i == n - 1 || (unsigned)(keys[i + 1] >> 32) != t) tend[t] = (int)(i + 1);
 }
 
+// ln r grid, reciprocal cell widths and the ln table, once per call (every CTA then only copies them)
+__global__ void __launch_bounds__(256) gg_axis_kernel(bf_raxis ax, double *__restrict__ axis) {
+    const int t = threadIdx.x, nr = ax.nr;
+    for (int k = t; k < nr; k += 256) axis[k] = ax.g[k];
+    for (int k = t; k < nr - 1; k += 256) axis[nr + k] = 1.0 / (ax.g[k + 1] - ax.g[k]);
+    if (t == 0) axis[2 * nr - 1] = 0.0;
+    bf_logtab_init(reinterpret_cast<double2 *>(axis + 2 * nr), t, 256);
+}
+
 struct gg_args {
     int npix;
-    double res;
+    double res, inv_res;
+    const double *axis;
     bf_raxis ax;
     const gh_rec *recs;
     const gg_hdr *hdr;
@@ -190,10 +204,11 @@ __global__ void __launch_bounds__(GG_THREADS, 2) grid_gather_kernel(gg_args A) {
     double *g_s = reinterpret_cast<double *>(logtab + BF_LOGTAB);
     double *ig_s = g_s + A.ax.nr;
     const int t = threadIdx.x, npix = A.npix, nr = A.ax.nr;
-    for (int k = t; k < nr; k += GG_THREADS) g_s[k] = A.ax.g[k];
-    bf_logtab_init(logtab, t, GG_THREADS);
-    __syncthreads();
-    for (int k = t; k < nr - 1; k += GG_THREADS) ig_s[k] = 1.0 / (g_s[k + 1] - g_s[k]);
+    for (int k = t; k < nr; k += GG_THREADS) {
+        g_s[k] = __ldg(A.axis + k);
+        ig_s[k] = __ldg(A.axis + nr + k);
+    }
+    for (int k = t; k < 2 * BF_LOGTAB; k += GG_THREADS) reinterpret_cast<double *>(logtab)[k] = __ldg(A.axis + 2 * nr + k);
     bf_raxis ax = A.ax;
     ax.g = g_s;
     // this thread's cell
@@ -263,12 +278,15 @@ __global__ void __launch_bounds__(GG_THREADS, 2) grid_gather_kernel(gg_args A) {
                 const double tt = (x - gk) * ig_s[k];
                 v = __ldg(H.row + k) * (1.0 - tt) + __ldg(H.row + k + 1) * tt;
             }
-            const double rt = sqrt(rt2);
-            const bool inside = rt < H.cut;
+            // r < cut (BaryonCorrection.py:381, Map2DRunner.py:804) decided on the squares; only a radius within
+            // rounding of the cut pays the square root the reference compares with
+            const double c2 = H.cut * H.cut;
+            bool inside = rt2 < c2;
+            if (fabs(rt2 - c2) <= 1e-12 * c2) inside = sqrt(rt2) < H.cut;
             if (MODE == 0) {
                 v = inside ? v : 0.0;  // BaryonCorrection.py:381-382
-                const double r = (DIM == 2 && A.Rmat) ? sqrt(r2) : rt;  // the unit vector keeps the round radius
-                const double q = (v / res) / r;  // :534 / :577: offset = d / res along the unit vector
+                // :534 / :577: offset = d / res along the unit vector (round radius also for sheared halos)
+                const double q = (v * A.inv_res) * rsqrt(r2);
                 acc[0] += q * gx;
                 acc[1] += q * gy;
                 if (DIM == 3) acc[2] += q * gz;
@@ -373,19 +391,21 @@ extern "C" int bf_grid_bin_halos(int dim, int64_t npix, const double *bins, cons
 }
 
 extern "C" int bf_grid_gather(int dim, int mode, int64_t npix, double res, const bf_grid_halos *G, const bf_table *T,
-                              int64_t max_entries, const void *ws, double *out, unsigned long long *npairs, void *stream) {
+                              int64_t max_entries, void *ws, double *out, unsigned long long *npairs, void *stream) {
     BF_REQUIRE(dim == 2 || dim == 3, "dim must be 2 or 3");
     BF_REQUIRE(mode == 0 || mode == 1, "mode: 0 baryonify, 1 paint");
     BF_REQUIRE(npix >= 5 && out && res > 0 && ws && G, "npix/out/res/ws");
     BF_REQUIRE(bf_check_table(T), "bad table");
     BF_REQUIRE(dim == 2 || G->Rmat == nullptr, "ellipticity (Rmat) is only defined for 2-D grids");
     if (G->nh == 0) return BF_OK;
-    gg_ws w = gg_layout(const_cast<void *>(ws), dim, npix, G->nh, max_entries);
+    gg_ws w = gg_layout(ws, dim, npix, G->nh, max_entries);
     gg_args A;
     A.npix = (int)npix;
     A.res = res;
+    A.inv_res = 1.0 / res;
     A.ax = bf_make_raxis(T);
-    BF_REQUIRE(gather_smem(A.ax.nr) <= 200 * 1024, "radial axis too long for the shared-memory staging");
+    BF_REQUIRE(A.ax.nr <= GG_MAX_NR, "radial axis too long for the shared-memory staging");
+    A.axis = w.axis;
     A.recs = w.recs; A.hdr = w.hdr; A.tstart = w.tstart; A.tend = w.tend;
     A.Rmat = G->Rmat; A.out = out; A.npairs = npairs;
     const int ta = tiles_per_axis((int)npix, dim == 2 ? tile_shape<2>::A : tile_shape<3>::A),
@@ -393,6 +413,8 @@ extern "C" int bf_grid_gather(int dim, int mode, int64_t npix, double res, const
               tc = dim == 3 ? tiles_per_axis((int)npix, tile_shape<3>::C) : 1;
     const unsigned nt = (unsigned)((size_t)ta * tb * tc);
     cudaStream_t s = (cudaStream_t)stream;
+    gg_axis_kernel<<<1, 256, 0, s>>>(A.ax, w.axis);
+    BF_LAUNCH_OK();
     if (dim == 2) return mode == 0 ? launch<2, 0>(A, nt, s) : launch<2, 1>(A, nt, s);
     return mode == 0 ? launch<3, 0>(A, nt, s) : launch<3, 1>(A, nt, s);
 }

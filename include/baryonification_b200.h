@@ -169,7 +169,7 @@ size_t bf_grid_bin_ws_bytes(int dim, int64_t npix, int64_t nh, int64_t max_entri
 int bf_grid_bin_halos(int dim, int64_t npix, const double *bins, const bf_grid_halos *h_host, int64_t nr,
                       int64_t max_entries, void *ws, size_t ws_bytes, int64_t *nentries_host, void *stream);
 int bf_grid_gather(int dim, int mode, int64_t npix, double res, const bf_grid_halos *h_host, const bf_table *tab_host,
-                   int64_t max_entries, const void *ws, double *out, unsigned long long *npairs, void *stream);
+                   int64_t max_entries, void *ws, double *out, unsigned long long *npairs, void *stream);
 /* BaryonifyGrid tail (:583-607 + regrid_pixels_2D/3D :14-163): CIC-equivalent periodic deposit. */
 int bf_grid_regrid(int dim, int64_t npix, const double *offsets, const double *orig, double *new_map, void *stream);
 
