@@ -156,3 +156,21 @@ def test_shear_matrices_equal_per_halo_build_Rmat_and_3d_raises():
         host.grid_rmat(cfg3["catalog"], cfg3["field"], True, True)
     with pytest.raises(ValueError):
         host.grid_rmat(cfg3["catalog"], cfg3["field"], True, False)
+
+
+def test_runners_are_picklable_like_the_reference_ones():
+    """utils/Parallelize.py:105-107 ships Runner objects to loky workers: no live CUDA handle may sit on ``self``."""
+    import pickle
+    import baryonification_b200 as bf
+    from baryonification_b200 import synthetic as syn
+    sh, gr, sn = syn.config_shell(nside=8, nhalo=10), syn.config_grid(npix=16, nhalo=5, dim=2), \
+        syn.config_snapshot(npart_side=4, nhalo=5, dim=3, L=50.0)
+    runners = [bf.BaryonifyShell(sh["catalog"], sh["field"], 20.0, sh["model"], verbose=False),
+               bf.PaintProfilesShell(sh["catalog"], sh["field"], 20.0, sh["paint_model"], verbose=False),
+               bf.BaryonifyGrid(gr["catalog"], gr["field"], 20.0, gr["model"], verbose=False),
+               bf.PaintProfilesGrid(gr["catalog"], gr["field"], 20.0, gr["paint_model"], verbose=False),
+               bf.BaryonifySnapshot(sn["catalog"], sn["field"], 5.0, sn["model"], verbose=False)]
+    for r in runners:
+        r2 = pickle.loads(pickle.dumps(r))
+        assert type(r2) is type(r) and r2.epsilon_max == r.epsilon_max
+        assert np.array_equal(r2.model.raw_input_r_range, r.model.raw_input_r_range)
