@@ -423,6 +423,14 @@ __global__ void __launch_bounds__(SN_THREADS, SN_MINBLOCKS) snap_gather_kernel(s
                 tab[u] = __ldg(A.cell_tab + c);
             }
         }
+        // cells reached by exactly one halo (most non-empty cells): decide membership here, with all lanes' loads in
+        // flight together, so that only particles that do move (or sit in a multi-halo cell) are parked
+#pragma unroll
+        for (int u = 0; u < 2; ++u)
+            if (tab[u] < 0) {
+                double dx[3];
+                if (!snap_member<DIM>(P[u], ldg_rec(A.hrec + (-tab[u] - 1)), A.G.L, dx)) tab[u] = 0;
+            }
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
             const i64 p = chunk0 + (t0 + u) * 32 + lane;
