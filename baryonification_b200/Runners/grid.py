@@ -36,6 +36,7 @@ class DefaultRunnerGrid:
         self.regrid = regrid
         # pair loop: "gather" (cell-owner, deterministic catalogue-order sums, default) | "atomic" (halo-centric)
         self.variant = variant
+        self.rows = None  # (a_first, a_last): slab of the first grid axis owned by this rank (sharding.ShardedGrid)
         self.npairs = None
         self.timings = {}
         if use_ellipticity:  # Map2DRunner.py:266-272
@@ -68,7 +69,6 @@ class DefaultRunnerGrid:
         bins = dv.to_dev(G.bins, dev=dev)
         return table, s, desc, bins, (t, rows)
 
-
     def _accumulate(self, mode, s, desc, bins, table, out, cnt, dev):
         """The per-halo loop (Map2DRunner.py:476-580 / :714-810) into ``out``: cell-owner gather, or atomics."""
         G = self.GriddedMap
@@ -90,9 +90,12 @@ class DefaultRunnerGrid:
                 _lib.check(rc, "bf_grid_bin_halos")
                 break
             self.nentries = n.value
-            _lib.call("bf_grid_gather", dim, mode, G.Npix, float(G.res), C.byref(desc), C.byref(table.desc), max_entries,
-                      dv.ptr(ws), dv.ptr(out), dv.ptr(cnt), dv.stream_ptr())
-        else:
+            a0, a1 = self.rows if self.rows is not None else (0, G.Npix)
+            _lib.call("bf_grid_gather_rows", dim, mode, G.Npix, float(G.res), C.byref(desc), C.byref(table.desc),
+                      max_entries, dv.ptr(ws), dv.ptr(out), a0, a1, dv.ptr(cnt), dv.stream_ptr())
+        elif nh > 0:
+            if self.rows is not None:
+                raise _lib.BFError("slab-sharded grids need the cell-owner gather (variant='gather')")
             _lib.call("bf_grid_paint_atomic" if mode else "bf_grid_baryonify_atomic", dim, G.Npix, dv.ptr(bins),
                       float(G.res), C.byref(desc), C.byref(table.desc), dv.ptr(out), dv.ptr(cnt), dv.stream_ptr())
         self.npairs = int(cnt.item())
@@ -162,16 +165,22 @@ class BaryonifyGrid(DefaultRunnerGrid):
 
 
 class PaintProfilesGrid(DefaultRunnerGrid):
+    def paint_device(self, dev):
+        """The painted map as a device tensor [Npix^D] (rows outside ``self.rows`` stay zero)."""
+        G = self.GriddedMap
+        table, s, desc, bins, keep = self._prepare(profile_host_table(self.model, "2D" if G.is2D else "3D"), False, dev)
+        out = dv.zeros(G.map.size, dev=dev)
+        cnt = dv.pair_counter(dev)
+        self._accumulate(1, s, desc, bins, table, out, cnt, dev)
+        del keep
+        return out
+
     def process(self):
         dev = dv.device(self.device)
         G = self.GriddedMap
         with torch.cuda.device(dev):
             t0 = time.perf_counter()
-            table, s, desc, bins, keep = self._prepare(profile_host_table(self.model, "2D" if G.is2D else "3D"),
-                                                        False, dev)
-            out = dv.zeros(G.map.size, dev=dev)
-            cnt = dv.pair_counter(dev)
-            self._accumulate(1, s, desc, bins, table, out, cnt, dev)
+            out = self.paint_device(dev)
             self.timings["accumulate"] = time.perf_counter() - t0
             res = dv.to_host(out, True).reshape(G.map.shape)
             self.timings["process"] = time.perf_counter() - t0

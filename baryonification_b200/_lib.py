@@ -87,6 +87,12 @@ _SIGS = {
                                     _P(_i64), C.c_void_p]),
     "bf_grid_gather": (C.c_int, [C.c_int, C.c_int, _i64, C.c_double, _P(GridHalos), _P(Table), _i64, C.c_void_p,
                                  _dbl_p, _dbl_p, C.c_void_p]),
+    "bf_grid_gather_rows": (C.c_int, [C.c_int, C.c_int, _i64, C.c_double, _P(GridHalos), _P(Table), _i64, C.c_void_p,
+                                      _dbl_p, _i64, _i64, _dbl_p, C.c_void_p]),
+    "bf_grid_regrid_window": (C.c_int, [C.c_int, _i64, _dbl_p, _i64, _i64, C.c_void_p, C.c_size_t, C.POINTER(C.c_int),
+                                        C.c_void_p]),
+    "bf_grid_regrid_gather_rows": (C.c_int, [C.c_int, _i64, _dbl_p, _dbl_p, _dbl_p, C.POINTER(C.c_int), _i64, _i64,
+                                             C.POINTER(C.c_int), C.c_void_p]),
     "bf_grid_regrid": (C.c_int, [C.c_int, _i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p]),
     "bf_grid_regrid_sorted_ws_bytes": (C.c_size_t, [C.c_int, _i64]),
     "bf_grid_regrid_sorted": (C.c_int, [C.c_int, _i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p, C.c_size_t, C.c_void_p]),

@@ -180,6 +180,8 @@ __global__ void __launch_bounds__(256) gg_axis_kernel(bf_raxis ax, double *__res
 
 struct gg_args {
     int npix;
+    int a_first, a_last;  // rows (first grid axis) this call owns; tile_first = a_first / tile edge
+    int tile_first;
     double res, inv_res;
     const double *axis;
     bf_raxis ax;
@@ -196,7 +198,7 @@ __global__ void __launch_bounds__(GG_THREADS, 2) grid_gather_kernel(gg_args A) {
     using TS = tile_shape<DIM>;
     static_assert(TS::A * TS::B * TS::C == GG_THREADS, "one cell per thread");
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int tile = blockIdx.x;
+    const int tile = blockIdx.x + A.tile_first;
     const int s0 = A.tstart[tile], s1 = A.tend[tile];
     if (s0 >= s1) return;  // no halo reaches this tile
     gh_rec *chunk = reinterpret_cast<gh_rec *>(smem_raw);
@@ -220,7 +222,7 @@ __global__ void __launch_bounds__(GG_THREADS, 2) grid_gather_kernel(gg_args A) {
     if (DIM == 3) { lc = t % TS::C; lb = (t / TS::C) % TS::B; la = t / (TS::C * TS::B); }
     else { lb = t % TS::B; la = t / TS::B; }
     const int ca = tta * TS::A + la, cb = ttb * TS::B + lb, cc = ttc * TS::C + lc;
-    const bool active = ca < npix && cb < npix && (DIM == 2 || cc < npix);
+    const bool active = ca >= A.a_first && ca < A.a_last && cb < npix && (DIM == 2 || cc < npix);
     const unsigned long long *keys = A.hdr->sorted_keys;
     const double res = A.res;
     double acc[3] = {0.0, 0.0, 0.0};
@@ -392,7 +394,15 @@ extern "C" int bf_grid_bin_halos(int dim, int64_t npix, const double *bins, cons
 
 extern "C" int bf_grid_gather(int dim, int mode, int64_t npix, double res, const bf_grid_halos *G, const bf_table *T,
                               int64_t max_entries, void *ws, double *out, unsigned long long *npairs, void *stream) {
+    return bf_grid_gather_rows(dim, mode, npix, res, G, T, max_entries, ws, out, 0, npix, npairs, stream);
+}
+
+extern "C" int bf_grid_gather_rows(int dim, int mode, int64_t npix, double res, const bf_grid_halos *G,
+                                   const bf_table *T, int64_t max_entries, void *ws, double *out, int64_t a_first,
+                                   int64_t a_last, unsigned long long *npairs, void *stream) {
     BF_REQUIRE(dim == 2 || dim == 3, "dim must be 2 or 3");
+    BF_REQUIRE(a_first >= 0 && a_first <= a_last && a_last <= npix, "0 <= a_first <= a_last <= npix");
+    if (a_first == a_last) return BF_OK;
     BF_REQUIRE(mode == 0 || mode == 1, "mode: 0 baryonify, 1 paint");
     BF_REQUIRE(npix >= 5 && out && res > 0 && ws && G, "npix/out/res/ws");
     BF_REQUIRE(bf_check_table(T), "bad table");
@@ -411,7 +421,12 @@ extern "C" int bf_grid_gather(int dim, int mode, int64_t npix, double res, const
     const int ta = tiles_per_axis((int)npix, dim == 2 ? tile_shape<2>::A : tile_shape<3>::A),
               tb = tiles_per_axis((int)npix, dim == 2 ? tile_shape<2>::B : tile_shape<3>::B),
               tc = dim == 3 ? tiles_per_axis((int)npix, tile_shape<3>::C) : 1;
-    const unsigned nt = (unsigned)((size_t)ta * tb * tc);
+    const int TA = dim == 2 ? tile_shape<2>::A : tile_shape<3>::A;
+    const int t_first = (int)(a_first / TA), t_last = (int)((a_last + TA - 1) / TA);
+    (void)ta;
+    A.a_first = (int)a_first; A.a_last = (int)a_last;
+    A.tile_first = t_first * tb * tc;
+    const unsigned nt = (unsigned)((size_t)(t_last - t_first) * tb * tc);
     cudaStream_t s = (cudaStream_t)stream;
     gg_axis_kernel<<<1, 256, 0, s>>>(A.ax, w.axis);
     BF_LAUNCH_OK();

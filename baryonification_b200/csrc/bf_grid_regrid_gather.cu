@@ -56,10 +56,11 @@ __global__ void window_init_kernel(int *mm) {
 
 // mm[0..2] = min, mm[3..5] = max over all cells of (floor(position) - cell coordinate), min-image, per grid axis
 template <int DIM>
-__global__ void __launch_bounds__(256) window_kernel(int N, const double *__restrict__ off, int *__restrict__ mm) {
-    const i64 ncell = (DIM == 2) ? (i64)N * N : (i64)N * N * N;
+__global__ void __launch_bounds__(256) window_kernel(int N, const double *__restrict__ off, i64 cell_first,
+                                                     i64 cell_last, int *__restrict__ mm) {
     int lo[3] = {INT_MAX, INT_MAX, INT_MAX}, hi[3] = {INT_MIN, INT_MIN, INT_MIN};
-    for (i64 cell = (i64)blockIdx.x * blockDim.x + threadIdx.x; cell < ncell; cell += (i64)gridDim.x * blockDim.x) {
+    for (i64 cell = cell_first + (i64)blockIdx.x * blockDim.x + threadIdx.x; cell < cell_last;
+         cell += (i64)gridDim.x * blockDim.x) {
         int a, b, c = 0;
         if (DIM == 2) { a = (int)(cell / N); b = (int)(cell - (i64)a * N); }
         else { a = (int)(cell / ((i64)N * N)); i64 rem = cell - (i64)a * N * N; b = (int)(rem / N); c = (int)(rem - (i64)b * N); }
@@ -97,6 +98,7 @@ struct gg_args {
     double *out;
     int hi[3];  // source coordinate of window slot k for destination d: d - hi - 1 + k
     int w[3];   // window length per axis (1 for the unused third axis of a 2-D grid)
+    int a_first, a_last;  // destination rows (first grid axis) written by this call
 };
 
 // shared-memory staging, structure of arrays over the E = EA*EB*EC sources around the tile:
@@ -111,7 +113,7 @@ __global__ void __launch_bounds__(TA * TB * TC) grid_gather_regrid_kernel(gg_arg
     const int E = EA * EB * EC;
     double *pos_s = stage_s, *mass_s = stage_s + DIM * E;
     int *idx_s = (int *)(stage_s + (DIM + 1) * E);
-    const int oa = ((DIM == 3) ? blockIdx.z : blockIdx.y) * TA, ob = ((DIM == 3) ? blockIdx.y : blockIdx.x) * TB,
+    const int oa = A.a_first + ((DIM == 3) ? blockIdx.z : blockIdx.y) * TA, ob = ((DIM == 3) ? blockIdx.y : blockIdx.x) * TB,
               oc = (DIM == 3) ? blockIdx.x * TC : 0;
     const int tid = threadIdx.x;
     // ---- stage the sources around the tile
@@ -141,7 +143,7 @@ __global__ void __launch_bounds__(TA * TB * TC) grid_gather_regrid_kernel(gg_arg
     if (DIM == 3) { tc = tid % TC; tb = (tid / TC) % TB; ta = tid / (TC * TB); }
     else { tb = tid % TB; ta = tid / TB; }
     const int da = oa + ta, db = ob + tb, dc = oc + tc;
-    if (da >= N || db >= N || (DIM == 3 && dc >= N)) return;
+    if (da >= A.a_last || db >= N || (DIM == 3 && dc >= N)) return;
     // ascending source coordinate along an axis: the window is a run of w consecutive coordinates mod N; when it
     // crosses N its wrapped tail (coordinates 0, 1, ...) comes first
     const int wa = A.w[0], wb = A.w[1], wc = A.w[2];
@@ -199,8 +201,9 @@ int launch_gather(const gg_args &A, cudaStream_t s) {
     auto kern = grid_gather_regrid_kernel<DIM, TA, TB, TC>;
     BF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     dim3 grid;
-    if (DIM == 3) grid = dim3((A.N + TC - 1) / TC, (A.N + TB - 1) / TB, (A.N + TA - 1) / TA);
-    else grid = dim3((A.N + TB - 1) / TB, (A.N + TA - 1) / TA, 1);
+    const int rows = A.a_last - A.a_first;
+    if (DIM == 3) grid = dim3((A.N + TC - 1) / TC, (A.N + TB - 1) / TB, (rows + TA - 1) / TA);
+    else grid = dim3((A.N + TB - 1) / TB, (rows + TA - 1) / TA, 1);
     kern<<<grid, TA * TB * TC, smem, s>>>(A);
     BF_LAUNCH_OK();
     return BF_OK;
@@ -210,35 +213,51 @@ int launch_gather(const gg_args &A, cudaStream_t s) {
 
 extern "C" size_t bf_grid_regrid_gather_ws_bytes(void) { return 8 * sizeof(int); }
 
-extern "C" int bf_grid_regrid_gather(int dim, int64_t npix, const double *offsets, const double *orig, double *new_map,
-                                     void *ws, size_t ws_bytes, int *window_host, void *stream) {
+extern "C" int bf_grid_regrid_window(int dim, int64_t npix, const double *offsets, int64_t a_first, int64_t a_last,
+                                     void *ws, size_t ws_bytes, int *lohi_host, void *stream) {
     BF_REQUIRE(dim == 2 || dim == 3, "dim must be 2 or 3");
-    BF_REQUIRE(npix >= 5 && npix < (1 << 30) && offsets && orig && new_map, "5 <= npix < 2^30 and non-null arrays");
+    BF_REQUIRE(npix >= 5 && npix < (1 << 30) && offsets && lohi_host, "5 <= npix < 2^30 and non-null arrays");
+    BF_REQUIRE(a_first >= 0 && a_first <= a_last && a_last <= npix, "0 <= a_first <= a_last <= npix");
     if (!ws || ws_bytes < 8 * sizeof(int)) {
-        bf_set_error("bf_grid_regrid_gather: workspace %zu < %zu bytes", ws_bytes, 8 * sizeof(int));
+        bf_set_error("bf_grid_regrid_window: workspace %zu < %zu bytes", ws_bytes, 8 * sizeof(int));
         return BF_E_WORKSPACE;
     }
     cudaStream_t s = (cudaStream_t)stream;
-    int *mm = (int *)ws, h[6];
+    int *mm = (int *)ws;
     const int N = (int)npix;
-    const i64 ncell = (dim == 2) ? (i64)N * N : (i64)N * N * N;
+    const i64 rowlen = (dim == 2) ? (i64)N : (i64)N * N, c0 = a_first * rowlen, c1 = a_last * rowlen;
     window_init_kernel<<<1, 32, 0, s>>>(mm);
     BF_LAUNCH_OK();
-    unsigned blocks = (unsigned)std::min<i64>((ncell + 255) / 256, 148 * 16);
-    if (dim == 2) window_kernel<2><<<blocks, 256, 0, s>>>(N, offsets, mm);
-    else window_kernel<3><<<blocks, 256, 0, s>>>(N, offsets, mm);
-    BF_LAUNCH_OK();
-    BF_CUDA_OK(cudaMemcpyAsync(h, mm, sizeof(h), cudaMemcpyDeviceToHost, s));
+    if (c1 > c0) {
+        unsigned blocks = (unsigned)std::min<i64>((c1 - c0 + 255) / 256, 148 * 16);
+        if (dim == 2) window_kernel<2><<<blocks, 256, 0, s>>>(N, offsets, c0, c1, mm);
+        else window_kernel<3><<<blocks, 256, 0, s>>>(N, offsets, c0, c1, mm);
+        BF_LAUNCH_OK();
+    }
+    BF_CUDA_OK(cudaMemcpyAsync(lohi_host, mm, 6 * sizeof(int), cudaMemcpyDeviceToHost, s));
     BF_CUDA_OK(cudaStreamSynchronize(s));
+    for (int m = dim; m < 3; ++m) lohi_host[m] = lohi_host[3 + m] = 0;
+    return BF_OK;
+}
+
+extern "C" int bf_grid_regrid_gather_rows(int dim, int64_t npix, const double *offsets, const double *orig,
+                                          double *new_map, const int *lohi_host, int64_t a_first, int64_t a_last,
+                                          int *window_host, void *stream) {
+    BF_REQUIRE(dim == 2 || dim == 3, "dim must be 2 or 3");
+    BF_REQUIRE(npix >= 5 && npix < (1 << 30) && offsets && orig && new_map && lohi_host,
+               "5 <= npix < 2^30 and non-null arrays");
+    BF_REQUIRE(a_first >= 0 && a_first <= a_last && a_last <= npix, "0 <= a_first <= a_last <= npix");
+    const int N = (int)npix;
     gg_args A;
     A.N = N; A.off = offsets; A.orig = orig; A.out = new_map;
+    A.a_first = (int)a_first; A.a_last = (int)a_last;
     i64 vol = 1;
     for (int m = 0; m < 3; ++m) {
-        if (m < dim) { A.hi[m] = h[3 + m]; A.w[m] = h[3 + m] - h[m] + 2; }
+        if (m < dim) { A.hi[m] = lohi_host[3 + m]; A.w[m] = lohi_host[3 + m] - lohi_host[m] + 2; }
         else { A.hi[m] = 0; A.w[m] = 1; }
         if (window_host) window_host[m] = A.w[m];
-        if (A.w[m] > N) {
-            bf_set_error("bf_grid_regrid_gather: displacement window %d exceeds the grid", A.w[m]);
+        if (A.w[m] > N || A.w[m] < 2 - (m >= dim)) {
+            bf_set_error("bf_grid_regrid_gather: displacement window %d does not fit the grid", A.w[m]);
             return BF_E_WINDOW;
         }
         vol *= A.w[m];
@@ -248,5 +267,15 @@ extern "C" int bf_grid_regrid_gather(int dim, int64_t npix, const double *offset
                      (long long)vol);
         return BF_E_WINDOW;
     }
+    if (a_first == a_last) return BF_OK;
+    cudaStream_t s = (cudaStream_t)stream;
     return (dim == 2) ? launch_gather<2, 16, 32, 1>(A, s) : launch_gather<3, 4, 8, 16>(A, s);
+}
+
+extern "C" int bf_grid_regrid_gather(int dim, int64_t npix, const double *offsets, const double *orig, double *new_map,
+                                     void *ws, size_t ws_bytes, int *window_host, void *stream) {
+    int lohi[6];
+    int rc = bf_grid_regrid_window(dim, npix, offsets, 0, npix, ws, ws_bytes, lohi, stream);
+    if (rc != BF_OK) return rc;
+    return bf_grid_regrid_gather_rows(dim, npix, offsets, orig, new_map, lohi, 0, npix, window_host, stream);
 }

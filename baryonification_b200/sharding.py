@@ -177,6 +177,69 @@ def gather_slices(own, ranges, group=None, out=None):
 
 
 # ----------------------------------------------------------------------------------------------------------
+# periodic grids: slabs of the first grid axis
+# ----------------------------------------------------------------------------------------------------------
+def halos_touching_rows(x, bins, Nsize, a_first, a_last):
+    """Mask of the halos whose cut-out box (Map2DRunner.py:494-512: ``Nsize`` cells around ``argmin|bins - x|``,
+    periodic) can reach rows ``a_first <= a < a_last`` of the first grid axis.  One extra row either side stands in
+    for the exact argmin, so the mask is a superset; the kernel's membership test is the exact one."""
+    n = bins.size
+    res = bins[1] - bins[0]
+    cen = np.clip(np.rint((np.asarray(x, dtype=np.float64) - bins[0]) / res), 0, n - 1).astype(np.int64)
+    W = np.asarray(Nsize, dtype=np.int64)
+    lo, length = cen - W // 2 - 1, W + 2
+    keep = length >= n
+    for shift in (-n, 0, n):
+        keep |= (lo + shift < a_last) & (lo + shift + length > a_first)
+    return keep & (W >= 2)
+
+
+def ghost_rows(rows, rank, below, above, n):
+    """Global row indices (periodic) that ``rank`` needs beyond its own slab: ``below`` rows before it and ``above``
+    rows after it, without the rows it owns itself."""
+    a0, a1 = rows[rank]
+    need = [(a0 - k) % n for k in range(min(below, n), 0, -1)] + [(a1 + k) % n for k in range(min(above, n))]
+    seen, out = set(), []
+    for g in need:
+        if not (a0 <= g < a1) and g not in seen:
+            seen.add(g)
+            out.append(g)
+    return out
+
+
+def exchange_rows(buf, rows, below, above, group=None):
+    """Fill the ghost rows of ``buf`` ([n_rows, ...] with GLOBAL row indexing; every rank holds valid data in its
+    own slab ``rows[rank]``) from their owners.  Point-to-point only, one message per (owner, needer) pair."""
+    rank, world = _world(group)
+    n = buf.shape[0]
+    if world == 1:
+        return buf
+    owner = np.empty(n, dtype=np.int64)
+    for r, (a, b) in enumerate(rows):
+        owner[a:b] = r
+    ops, recvs = [], []
+    for needer in range(world):
+        need = ghost_rows(rows, needer, below, above, n)
+        for src in range(world):
+            idx = [g for g in need if owner[g] == src]
+            if not idx or src == needer:
+                continue
+            if rank == src:
+                payload = buf[torch.as_tensor(idx, device=buf.device)].contiguous()
+                ops.append(dist.P2POp(dist.isend, payload, needer, group=group))
+            elif rank == needer:
+                box = torch.empty((len(idx),) + tuple(buf.shape[1:]), dtype=buf.dtype, device=buf.device)
+                ops.append(dist.P2POp(dist.irecv, box, src, group=group))
+                recvs.append((idx, box))
+    if ops:
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+    for idx, box in recvs:
+        buf[torch.as_tensor(idx, device=buf.device)] = box
+    return buf
+
+
+# ----------------------------------------------------------------------------------------------------------
 # sharded runners (call from every rank of an initialised process group with the SAME host inputs)
 # ----------------------------------------------------------------------------------------------------------
 def _subset(scalars, keep):
@@ -274,3 +337,103 @@ class ShardedSnapshot:
         parts = [None] * self.world
         dist.all_gather_object(parts, out, group=self.group)
         return np.concatenate(parts)
+
+
+class ShardedGrid:
+    """Slab-sharded BaryonifyGrid / PaintProfilesGrid: every rank owns a run of rows of the first grid axis.
+
+    Pair loop: the rank evaluates only the cells of its slab (cell-owner gather, ``bf_grid_gather_rows``) against the
+    halos whose cut-out can reach it -- catalogue order is kept inside the subset, so a cell's sum is bit-identical to
+    the single-GPU one, and there is no collective.  Re-binning (BaryonifyGrid): the destination gather needs the
+    offsets and masses of a few source rows either side of the slab; those INPUT ghost rows are exchanged point to
+    point (``exchange_rows``) after the displacement window has been agreed on with a MIN / MAX all-reduce of six
+    integers, and every rank then writes its own destination rows -- again the single-GPU bits.  Arrays keep global
+    indexing (full-size allocations, slab-sized work).  ``process()`` returns the full map on every rank."""
+
+    def __init__(self, runner, group=None, device=None):
+        from .Runners import grid as _grid
+        self.runner, self.group, self.device = runner, group, device
+        self.baryonify = isinstance(runner, _grid.BaryonifyGrid)
+        self.rank, self.world = _world(group)
+        self.npairs = None
+
+    def _local_runner(self, a0, a1):
+        import copy
+        from . import host
+        r = self.runner
+        G = r.GriddedMap
+        s = host.grid_scalars(r.HaloNDCatalog, G, r.mass_def, r.epsilon_max, r.model, self.baryonify)
+        keep = halos_touching_rows(s["pos"][:, 0], np.asarray(G.bins, dtype=np.float64), s["Nsize"], a0, a1)
+        cat = copy.copy(r.HaloNDCatalog)
+        cat.cat = r.HaloNDCatalog.cat[keep]
+        local = copy.copy(r)
+        local.HaloNDCatalog, local.rows, local.device, local.timings = cat, (a0, a1), self.device, {}
+        return local
+
+    def process(self, gather=True):
+        import ctypes as C
+        from . import _device as dv, _lib
+        r = self.runner
+        G = r.GriddedMap
+        n, dim = G.Npix, (2 if G.is2D else 3)
+        rowlen = n ** (dim - 1)
+        rows = index_split(n, self.world)
+        a0, a1 = rows[self.rank]
+        local = self._local_runner(a0, a1)
+        dev = dv.device(self.device)
+        with torch.cuda.device(dev):
+            if not self.baryonify:
+                out = local.paint_device(dev).view(n, rowlen)
+            else:
+                lib = _lib.load(require_cuda=True)
+                off = local.offsets_device(dev).view(n, rowlen * dim)
+                ws = torch.empty(lib.bf_grid_regrid_gather_ws_bytes(), dtype=torch.uint8, device=dev)
+                lohi = (C.c_int * 6)()
+                _lib.call("bf_grid_regrid_window", dim, n, dv.ptr(off), a0, a1, dv.ptr(ws), ws.numel(), lohi,
+                          dv.stream_ptr())
+                lo_t = torch.tensor(list(lohi)[:3], dtype=torch.int64, device=dev)
+                hi_t = torch.tensor(list(lohi)[3:], dtype=torch.int64, device=dev)
+                dist.all_reduce(lo_t, op=dist.ReduceOp.MIN, group=self.group)
+                dist.all_reduce(hi_t, op=dist.ReduceOp.MAX, group=self.group)
+                lohi = (C.c_int * 6)(*[int(v) for v in lo_t.tolist() + hi_t.tolist()])
+                below, above = max(0, lohi[3] + 1), max(0, -lohi[0])  # source rows a0 - hi - 1 ... a1 - 1 - lo
+                exchange_rows(off, rows, below, above, self.group)
+                orig_h = np.ascontiguousarray(G.map, dtype=np.float64).reshape(n, rowlen)
+                orig = dv.zeros((n, rowlen), dev=dev)
+                mine = list(range(a0, a1)) + ghost_rows(rows, self.rank, below, above, n)
+                for g0, g1 in _runs(sorted(mine)):
+                    orig[g0:g1] = dv.to_dev(orig_h[g0:g1], dev=dev)
+                out = dv.zeros((n, rowlen), dev=dev)
+                win = (C.c_int * 3)()
+                _lib.call("bf_grid_regrid_gather_rows", dim, n, dv.ptr(off), dv.ptr(orig), dv.ptr(out), lohi, a0, a1,
+                          win, dv.stream_ptr())
+                self.regrid_window = tuple(win)
+            pairs = torch.tensor([local.npairs], dtype=torch.int64, device=dev)
+            dist.all_reduce(pairs, group=self.group)
+            self.npairs = int(pairs.item())
+            own = out[a0:a1]
+            if not gather:
+                return own.cpu().numpy()
+            full = gather_slices(own.contiguous(), rows, self.group)
+            res = dv.to_host(full.reshape(-1), True).reshape(G.map.shape)
+        if self.baryonify:  # Map2DRunner.py:611-613
+            new_sum, old_sum = float(res.sum()), float(np.sum(G.map))
+            assert np.isclose(new_sum, old_sum), \
+                "ERROR in pixel regridding, sum(new_map) [%0.14e] != sum(oldmap) [%0.14e]" % (new_sum, old_sum)
+        return res
+
+
+def _runs(sorted_rows):
+    """Consecutive runs [g0, g1) of a sorted list of row indices."""
+    out, start, prev = [], None, None
+    for g in sorted_rows:
+        if start is None:
+            start = prev = g
+        elif g == prev + 1:
+            prev = g
+        else:
+            out.append((start, prev + 1))
+            start = prev = g
+    if start is not None:
+        out.append((start, prev + 1))
+    return out

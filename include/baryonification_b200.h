@@ -170,6 +170,11 @@ int bf_grid_bin_halos(int dim, int64_t npix, const double *bins, const bf_grid_h
                       int64_t max_entries, void *ws, size_t ws_bytes, int64_t *nentries_host, void *stream);
 int bf_grid_gather(int dim, int mode, int64_t npix, double res, const bf_grid_halos *h_host, const bf_table *tab_host,
                    int64_t max_entries, void *ws, double *out, unsigned long long *npairs, void *stream);
+/* Slab form for one rank of a multi-GPU run: only the cells of rows a_first <= a < a_last (first grid axis) are
+ * evaluated and written; `out` is still the full [npix^dim] array (global indexing).  *npairs counts this slab. */
+int bf_grid_gather_rows(int dim, int mode, int64_t npix, double res, const bf_grid_halos *h_host,
+                        const bf_table *tab_host, int64_t max_entries, void *ws, double *out, int64_t a_first,
+                        int64_t a_last, unsigned long long *npairs, void *stream);
 /* BaryonifyGrid tail (:583-607 + regrid_pixels_2D/3D :14-163): CIC-equivalent periodic deposit. */
 int bf_grid_regrid(int dim, int64_t npix, const double *offsets, const double *orig, double *new_map, void *stream);
 
@@ -189,6 +194,15 @@ int bf_grid_regrid_sorted(int dim, int64_t npix, const double *offsets, const do
 size_t bf_grid_regrid_gather_ws_bytes(void);
 int bf_grid_regrid_gather(int dim, int64_t npix, const double *offsets, const double *orig, double *new_map, void *ws,
                           size_t ws_bytes, int *window_host, void *stream);
+/* The two halves of bf_grid_regrid_gather for slab-sharded runs (global indexing, full-size arrays):
+ * bf_grid_regrid_window measures lohi_host[0..2] = min, [3..5] = max of floor(displaced position) - cell over the
+ * source rows a_first <= a < a_last (ranks combine theirs with MIN / MAX); bf_grid_regrid_gather_rows writes the
+ * destination rows a_first <= a < a_last, reading sources from rows a_first - hi_a - 1 ... a_last - 1 - lo_a
+ * (periodic), which the caller must have filled (own rows + ghost rows of the neighbouring slabs). */
+int bf_grid_regrid_window(int dim, int64_t npix, const double *offsets, int64_t a_first, int64_t a_last, void *ws,
+                          size_t ws_bytes, int *lohi_host, void *stream);
+int bf_grid_regrid_gather_rows(int dim, int64_t npix, const double *offsets, const double *orig, double *new_map,
+                               const int *lohi_host, int64_t a_first, int64_t a_last, int *window_host, void *stream);
 
 /* ---- Snapshot runner (SnapshotRunner.py) ---- */
 typedef struct {

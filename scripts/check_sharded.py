@@ -45,6 +45,23 @@ exact = all(np.array_equal(got[k], want[k]) for k in want.dtype.names)
 if rank == 0:
     print(f"BaryonifySnapshot: world {world} pairs {ss.npairs} (single {single.npairs}) bit-identical {exact}", flush=True)
 ok &= exact and ss.npairs == single.npairs
+for dim, npix, nhalo in ((2, 1000, 5000), (3, 200, 3000)):
+    gcfg = syn.config_grid(npix=npix, nhalo=nhalo, dim=dim, epsilon_max=20.0)
+    for name, cls, model in (("BaryonifyGrid", bf.BaryonifyGrid, gcfg["model"]), ("PaintProfilesGrid", bf.PaintProfilesGrid, gcfg["paint_model"])):
+        single = cls(gcfg["catalog"], gcfg["field"], 20.0, model, verbose=False, device=local)
+        want = single.process()
+        sg = sh.ShardedGrid(cls(gcfg["catalog"], gcfg["field"], 20.0, model, verbose=False), device=local)
+        sg.process()
+        torch.cuda.synchronize(); dist.barrier()
+        t0 = time.perf_counter()
+        got = sg.process()
+        dt = time.perf_counter() - t0
+        t0 = time.perf_counter(); single.process(); d1 = time.perf_counter() - t0
+        exact = np.array_equal(got, want)
+        if rank == 0:
+            print(f"{name} {dim}-D {npix}: world {world} pairs {sg.npairs} (single {single.npairs}) bit-identical {exact} "
+                  f"sharded process() {dt*1e3:.1f} ms (single {d1*1e3:.1f} ms)", flush=True)
+        ok &= exact and sg.npairs == single.npairs
 dist.barrier()
 dist.destroy_process_group()
 if rank == 0:

@@ -473,6 +473,55 @@ def test_grid_regrid_gather_reports_a_too_wide_window_and_the_runner_falls_back(
     assert np.array_equal(a, s)
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("dim,npix", [(2, 75), (3, 37)])
+def test_grid_row_slabs_reassemble_the_single_call_result(gpu, dim, npix):
+    """The slab entry points of the N > 1 path (bf_grid_gather_rows, bf_grid_regrid_window + _gather_rows), run slab
+    after slab on one GPU with uneven, tile-unaligned slabs: same bits as the whole-grid calls."""
+    import ctypes as C
+    import torch
+    import baryonification_b200 as bf
+    from baryonification_b200 import _device as dv, _lib, sharding as sh, synthetic as syn
+    lib = _lib.load(require_cuda=True)
+    cfg = syn.config_grid(npix=npix, nhalo=150, dim=dim, epsilon_max=12.0, L=(500.0 / 0.7 if dim == 2 else 100.0))
+    whole = bf.BaryonifyGrid(cfg["catalog"], cfg["field"], 12.0, cfg["model"], verbose=False)
+    dev = dv.device(None)
+    off_whole = whole.offsets_device(dev)
+    slabs = [(0, 5), (5, 6), (6, npix - 9), (npix - 9, npix)]
+    off = torch.zeros_like(off_whole)
+    pairs = 0
+    for a0, a1 in slabs:
+        part = bf.BaryonifyGrid(cfg["catalog"], cfg["field"], 12.0, cfg["model"], verbose=False)
+        part.rows = (a0, a1)
+        o = part.offsets_device(dev)
+        rl = npix ** (dim - 1) * dim
+        off.view(npix, rl)[a0:a1] = o.view(npix, rl)[a0:a1]
+        assert torch.count_nonzero(o.view(npix, rl)[:a0]) == 0 and torch.count_nonzero(o.view(npix, rl)[a1:]) == 0
+        pairs += part.npairs
+    assert pairs == whole.npairs and torch.equal(off, off_whole)
+    off = off * 30.0  # exaggerate so that mass crosses slab boundaries
+    orig = dv.to_dev(np.ascontiguousarray(cfg["field"].map).reshape(-1))
+    ws = torch.empty(64, dtype=torch.uint8, device=dev)
+    want = dv.zeros(orig.numel())
+    win = (C.c_int * 3)()
+    _lib.check(lib.bf_grid_regrid_gather(dim, npix, dv.ptr(off), dv.ptr(orig), dv.ptr(want), dv.ptr(ws), 64, win,
+                                         dv.stream_ptr()), "whole")
+    lo, hi = [10 ** 9] * 3, [-10 ** 9] * 3
+    for a0, a1 in slabs:
+        lohi = (C.c_int * 6)()
+        _lib.call("bf_grid_regrid_window", dim, npix, dv.ptr(off), a0, a1, dv.ptr(ws), 64, lohi, dv.stream_ptr())
+        lo = [min(a, b) for a, b in zip(lo, list(lohi)[:3])]
+        hi = [max(a, b) for a, b in zip(hi, list(lohi)[3:])]
+    lohi = (C.c_int * 6)(*(lo[:dim] + [0] * (3 - dim) + hi[:dim] + [0] * (3 - dim)))
+    got = dv.zeros(orig.numel())
+    for a0, a1 in slabs:
+        w2 = (C.c_int * 3)()
+        _lib.call("bf_grid_regrid_gather_rows", dim, npix, dv.ptr(off), dv.ptr(orig), dv.ptr(got), lohi, a0, a1, w2,
+                  dv.stream_ptr())
+        assert tuple(w2) == tuple(win)
+    assert max(win) >= 3 and torch.equal(got, want)
+
+
 # ------------------------------------------------------------------ property-keyed tables (p_keys)
 def test_param_tabulated_profiles_parity(gpu):
     """ParamTabulatedProfile-style tables [Nz, NM, NR, Ncdelta] with a per-halo `cdelta` column

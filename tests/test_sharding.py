@@ -151,3 +151,68 @@ def _snapshot_ranks(rank, world):
 
 def test_snapshot_index_sharding_is_exact():
     _run(_snapshot_ranks, 2)
+
+
+# ------------------------------------------------------------------ periodic grids: row slabs
+def test_halo_row_mask_is_a_superset_of_the_exact_cut_out_rows():
+    from baryonification_b200 import host
+    from baryonification_b200._ccl import default_mass_def
+    cfg = syn.config_grid(npix=64, nhalo=300, dim=3, epsilon_max=12.0, L=100.0)
+    G = cfg["field"]
+    s = host.grid_scalars(cfg["catalog"], G, default_mass_def(), 12.0, cfg["model"], True)
+    bins = np.asarray(G.bins, dtype=np.float64)
+    cen = np.array([np.argmin(np.abs(bins - x)) for x in s["pos"][:, 0]])  # Map2DRunner.py:505
+    for a0, a1 in sh.index_split(64, 5):
+        keep = sh.halos_touching_rows(s["pos"][:, 0], bins, s["Nsize"], a0, a1)
+        for j in np.flatnonzero(~keep):
+            w = s["Nsize"][j] // 2
+            rows_j = np.arange(cen[j] - w, cen[j] + w) % 64  # pick_indices (:394-423)
+            assert not np.any((rows_j >= a0) & (rows_j < a1)), j
+        assert keep.sum() < 300  # and it prunes
+
+
+def test_ghost_rows():
+    rows = sh.index_split(10, 3)  # (0,3) (3,6) (6,10)
+    assert sh.ghost_rows(rows, 0, 2, 1, 10) == [8, 9, 3]
+    assert sh.ghost_rows(rows, 2, 1, 2, 10) == [5, 0, 1]
+    assert sh.ghost_rows([(0, 10)], 0, 3, 3, 10) == []          # one rank owns everything
+    assert sorted(sh.ghost_rows(rows, 1, 20, 20, 10)) == [0, 1, 2, 6, 7, 8, 9]  # window wider than the box
+    assert sh._runs([0, 1, 2, 5, 7, 8]) == [(0, 3), (5, 6), (7, 9)]
+
+
+def _ghost_exchange_ranks(rank, world, n, below, above):
+    rng = np.random.default_rng(3)
+    truth = rng.normal(size=(n, 7, 2))
+    rows = sh.index_split(n, world)
+    a0, a1 = rows[rank]
+    buf = torch.full((n, 7, 2), float("nan"), dtype=torch.float64)
+    buf[a0:a1] = torch.from_numpy(truth[a0:a1])
+    sh.exchange_rows(buf, rows, below, above)
+    have = sorted(list(range(a0, a1)) + sh.ghost_rows(rows, rank, below, above, n))
+    got = buf.numpy()
+    assert np.array_equal(got[have], truth[have])
+    rest = np.setdiff1d(np.arange(n), have)
+    assert np.all(np.isnan(got[rest]))
+
+
+@pytest.mark.parametrize("world,n,below,above", [(2, 16, 2, 1), (3, 11, 1, 3), (3, 7, 4, 4)])
+def test_ghost_row_exchange_fills_exactly_the_needed_rows(world, n, below, above):
+    _run(_ghost_exchange_ranks, world, n, below, above)
+
+
+def test_ghost_width_from_the_displacement_window_covers_every_deposit():
+    """Rows outside [a0 - hi - 1, a1 - 1 - lo] never deposit into rows [a0, a1): the formula ShardedGrid uses."""
+    rng = np.random.default_rng(8)
+    n = 40
+    off = rng.uniform(-2.3, 1.4, n * n)          # offsets along the first grid axis, one per cell
+    a = np.repeat(np.arange(n), n)
+    pos = (off + a) % n
+    base = np.floor(pos).astype(int) % n
+    d = (base - a + n // 2) % n - n // 2         # min-image floor(position) - cell, as the window kernel measures it
+    lo, hi = d.min(), d.max()
+    below, above = max(0, hi + 1), max(0, -lo)
+    for a0, a1 in sh.index_split(n, 3):
+        dest_hit = ((base >= a0) & (base < a1)) | (((base + 1) % n >= a0) & ((base + 1) % n < a1))
+        allowed = np.zeros(n, dtype=bool)
+        allowed[[g % n for g in range(a0 - below, a1 + above)]] = True
+        assert np.all(allowed[a[dest_hit]])
