@@ -31,6 +31,22 @@ class PowerSpectrumGrid:
         val = 1.0 / (self.Ngrd * d)  # np.fft.fftfreq(n, d): results * val
         return L, float(val), float(kbins[0]), float(kbins[1] - kbins[0])
 
+    def upload(self, particles, dev=None):
+        """Host particles -> a device form ``density`` accepts, so that several folding factors read one upload:
+        the (M, x, y, z) record tensor when the array has the reference's 32-byte layout, else (x, y, z) columns."""
+        from .Runners.snapshot import BaryonifySnapshot
+        dev = dev or dv.device(self.device)
+        if isinstance(particles, (torch.Tensor, tuple)):
+            return particles
+        if getattr(particles, "dtype", None) is not None and particles.dtype.names:
+            if BaryonifySnapshot._is_reference_layout(particles):
+                return dv.AsyncUpload(particles.view(np.float64).reshape(-1, 4), dev).result()
+            cols = [particles[k] for k in "xyz"]
+        else:
+            p = np.asarray(particles)
+            cols = [p[:, 0], p[:, 1], p[:, 2]]
+        return tuple(dv.to_dev(c, dev=dev, pinned=True) for c in cols)
+
     def density(self, particles, factor=1, dev=None):
         """NGP counts [Ngrd]^3 (float64, device) of ``particles`` folded into a box of L / factor.
         ``particles``: structured array with x, y, z (the runners' output), an [n, 3] array, or a device tensor
@@ -39,18 +55,14 @@ class PowerSpectrumGrid:
         L, _, _, _ = self._setup(factor)
         grid = dv.zeros((self.Ngrd,) * 3, dev=dev)
         with torch.cuda.device(dev):
+            particles = self.upload(particles, dev)
             if isinstance(particles, torch.Tensor):
                 rec = particles.contiguous()
                 assert rec.dim() == 2 and rec.shape[1] == 4 and rec.dtype == torch.float64
                 _lib.call("bf_pk_ngp_deposit", rec.shape[0], None, None, None, dv.ptr(rec), L, self.Ngrd, dv.ptr(grid),
                           dv.stream_ptr())
             else:
-                if getattr(particles, "dtype", None) is not None and particles.dtype.names:
-                    cols = [particles[k] for k in "xyz"]
-                else:
-                    p = np.asarray(particles)
-                    cols = [p[:, 0], p[:, 1], p[:, 2]]
-                x, y, z = (dv.to_dev(c, dev=dev, pinned=True) for c in cols)
+                x, y, z = particles
                 _lib.call("bf_pk_ngp_deposit", x.numel(), dv.ptr(x), dv.ptr(y), dv.ptr(z), None, L, self.Ngrd,
                           dv.ptr(grid), dv.stream_ptr())
         return grid
@@ -75,6 +87,7 @@ class PowerSpectrumGrid:
     def suppression(self, part_baryon, part_dmo, factors=(1, 8)):
         """{factor: {'k': k_cen * factor, 'S': P_baryon / P_dmo}} as the notebook's RES_* dictionaries."""
         res = {}
+        part_baryon, part_dmo = self.upload(part_baryon), self.upload(part_dmo)  # once, for every factor
         for f in factors:
             k, PB, _ = self.power(self.density(part_baryon, f), f)
             _, PD, _ = self.power(self.density(part_dmo, f), f)

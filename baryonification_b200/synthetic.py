@@ -125,7 +125,7 @@ def grid_bins(npix, L):
 # the five BASELINE.json configurations (sizes overridable so tests can shrink them)
 # --------------------------------------------------------------------------------------
 def config_grid(npix=512, nhalo=2000, dim=2, L=500.0 / 0.7, seed=SEED0 + 1, epsilon_max=20.0, ellipticity=False,
-                p_keys=False):
+                p_keys=False, rdelta=False):
     halos = box_halos(nhalo, seed, L, dim=dim)
     if p_keys:
         halos["cdelta"] = cdelta_column(nhalo, seed)
@@ -140,14 +140,14 @@ def config_grid(npix=512, nhalo=2000, dim=2, L=500.0 / 0.7, seed=SEED0 + 1, epsi
     cat = HaloNDCatalog(**halos)
     gmap = GriddedMap(map=field, redshift=halos["redshift"], bins=grid_bins(npix, L), cosmo=COSMO)
     z = halos["redshift"]
-    model = displacement_model(z * 0.5, z * 2.0, epsilon_max)
+    model = displacement_model(z * 0.5, z * 2.0, epsilon_max, Rdelta_sampling=rdelta)
     pmodel = param_profile_model(z * 0.5, z * 2.0) if p_keys else profile_model(z * 0.5, z * 2.0)
     return dict(catalog=cat, field=gmap, model=model, paint_model=pmodel, epsilon_max=epsilon_max,
                 use_ellipticity=bool(ellipticity))
 
 
 def config_shell(nside=1024, nhalo=100_000, seed=SEED0 + 2, epsilon_max=20.0, zero_map=False, zero_beyond=None,
-                 p_keys=False):
+                 p_keys=False, rdelta=False):
     halos = lightcone_halos(nhalo, seed)
     if p_keys:
         halos["cdelta"] = cdelta_column(nhalo, seed)
@@ -155,12 +155,12 @@ def config_shell(nside=1024, nhalo=100_000, seed=SEED0 + 2, epsilon_max=20.0, ze
     field = np.zeros(npix) if zero_map else lognormal_field(npix, seed + 1000)
     cat = HaloLightConeCatalog(**halos)
     shell = LightconeShell(map=field, cosmo=COSMO)
-    model = displacement_model(0.05, 1.2, epsilon_max)
+    model = displacement_model(0.05, 1.2, epsilon_max, Rdelta_sampling=rdelta)
     pmodel = (param_profile_model if p_keys else profile_model)(0.05, 1.2, zero_beyond=zero_beyond)
     return dict(catalog=cat, field=shell, model=model, paint_model=pmodel, epsilon_max=epsilon_max)
 
 
-def config_snapshot(npart_side=512, nhalo=100_000, dim=3, L=500.0 / 0.7, seed=SEED0 + 4, epsilon_max=5.0):
+def config_snapshot(npart_side=512, nhalo=100_000, dim=3, L=500.0 / 0.7, seed=SEED0 + 4, epsilon_max=5.0, rdelta=False):
     halos = box_halos(nhalo, seed, L, dim=dim)
     rng = np.random.default_rng(seed + 1000)
     n = npart_side ** dim
@@ -169,5 +169,5 @@ def config_snapshot(npart_side=512, nhalo=100_000, dim=3, L=500.0 / 0.7, seed=SE
                             redshift=halos["redshift"], cosmo=COSMO)
     cat = HaloNDCatalog(**halos)
     z = halos["redshift"]
-    model = displacement_model(z * 0.5, z * 2.0, epsilon_max)
+    model = displacement_model(z * 0.5, z * 2.0, epsilon_max, Rdelta_sampling=rdelta)
     return dict(catalog=cat, field=snap, model=model, epsilon_max=epsilon_max)

@@ -44,6 +44,9 @@ CASES = [
     ("grid2d_paint_ell_64", "grid_paint", dict(npix=64, nhalo=120, dim=2, epsilon_max=20.0, ellipticity=True), {}),
     ("shell_paint_pkeys_ns32", "shell_paint", dict(nside=32, nhalo=300, epsilon_max=20.0, zero_map=True, p_keys=True), {}),
     ("grid2d_paint_pkeys_64", "grid_paint", dict(npix=64, nhalo=120, dim=2, epsilon_max=20.0, p_keys=True), {}),
+    ("shell_baryonify_rdelta_ns32", "shell_baryonify", dict(nside=32, nhalo=300, epsilon_max=20.0, rdelta=True), {}),
+    ("grid3d_baryonify_rdelta_24", "grid_baryonify", dict(npix=24, nhalo=40, dim=3, epsilon_max=8.0, L=100.0, rdelta=True), {}),
+    ("snapshot3d_rdelta_16", "snapshot", dict(npart_side=16, nhalo=80, dim=3, epsilon_max=5.0, L=100.0, rdelta=True), {}),
     ("snapshot3d_16", "snapshot", dict(npart_side=16, nhalo=80, dim=3, epsilon_max=5.0, L=100.0), {}),
     ("snapshot2d_64", "snapshot", dict(npart_side=64, nhalo=60, dim=2, epsilon_max=5.0, L=300.0), {}),
 ]

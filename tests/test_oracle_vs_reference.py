@@ -37,6 +37,9 @@ LIVE = [
     ("shell_paint", dict(nside=64, nhalo=400, epsilon_max=20.0, zero_map=True, zero_beyond=50.0, seed=26, p_keys=True)),
     ("grid_paint", dict(npix=96, nhalo=250, dim=2, epsilon_max=20.0, seed=27, p_keys=True)),
     ("grid_paint", dict(npix=24, nhalo=60, dim=3, epsilon_max=6.0, L=120.0, seed=28, p_keys=True)),
+    ("shell_baryonify", dict(nside=64, nhalo=300, epsilon_max=20.0, seed=31, rdelta=True)),  # Rdelta_sampling tables
+    ("grid_baryonify", dict(npix=96, nhalo=200, dim=2, epsilon_max=20.0, seed=32, rdelta=True)),
+    ("snapshot", dict(npart_side=20, nhalo=120, dim=3, epsilon_max=5.0, L=100.0, seed=33, rdelta=True)),
     ("snapshot", dict(npart_side=24, nhalo=150, dim=3, epsilon_max=5.0, L=100.0, seed=18)),
     ("snapshot", dict(npart_side=100, nhalo=100, dim=2, epsilon_max=5.0, L=300.0, seed=19)),
 ]
