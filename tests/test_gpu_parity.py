@@ -262,6 +262,62 @@ def test_snapshot_chunked_transfer_pipeline_equals_one_shot(gpu, monkeypatch):
         assert np.array_equal(got[k], want[k]), k
 
 
+# ------------------------------------------------------------------ empty / degenerate inputs
+def _empty(cat):
+    import copy
+    c = copy.copy(cat)
+    c.cat = cat.cat[:0]
+    return c
+
+
+@pytest.mark.gpu
+def test_empty_halo_catalogue_for_every_runner(gpu):
+    """The reference's loops simply do not run: Paint -> zeros, BaryonifyGrid / Snapshot -> the input, BaryonifyShell ->
+    the input re-binned with zero offsets (interpolation weights of a pixel centre are 1 only to rounding)."""
+    import baryonification_b200 as bf
+    from baryonification_b200 import synthetic as syn
+    from oracle import runners as orc
+    sh = syn.config_shell(nside=16, nhalo=10)
+    shz = syn.config_shell(nside=16, nhalo=10, zero_map=True)
+    for variant in ("gather", "atomic"):
+        got = bf.BaryonifyShell(_empty(sh["catalog"]), sh["field"], 20.0, sh["model"], verbose=False, variant=variant).process()
+        want = orc.BaryonifyShell(_empty(sh["catalog"]), sh["field"], 20.0, sh["model"]).process()
+        assert relmax(got, want) < 1e-13
+        p = bf.PaintProfilesShell(_empty(shz["catalog"]), shz["field"], 20.0, shz["paint_model"], verbose=False, variant=variant)
+        assert not p.process().any() and p.npairs == 0
+    for dim in (2, 3):
+        g = syn.config_grid(npix=16, nhalo=5, dim=dim, L=50.0)
+        for variant in ("gather", "atomic"):
+            b = bf.BaryonifyGrid(_empty(g["catalog"]), g["field"], 20.0, g["model"], verbose=False, variant=variant)
+            assert np.array_equal(b.process(), g["field"].map) and b.npairs == 0
+            assert not bf.PaintProfilesGrid(_empty(g["catalog"]), g["field"], 20.0, g["paint_model"], verbose=False,
+                                            variant=variant).process().any()
+        s = syn.config_snapshot(npart_side=6, nhalo=5, dim=dim, L=50.0)
+        r = bf.BaryonifySnapshot(_empty(s["catalog"]), s["field"], 5.0, s["model"], verbose=False)
+        out = r.process()
+        assert r.npairs == 0 and all(np.array_equal(out[k], s["field"].cat[k]) for k in out.dtype.names)
+
+
+@pytest.mark.gpu
+def test_empty_particle_set_and_halos_outside_the_table(gpu):
+    import copy
+    import baryonification_b200 as bf
+    from baryonification_b200 import synthetic as syn
+    from oracle import runners as orc
+    s = syn.config_snapshot(npart_side=8, nhalo=20, dim=3, L=50.0)
+    none = copy.copy(s["field"])
+    none.cat = s["field"].cat[:0]
+    out = bf.BaryonifySnapshot(s["catalog"], none, 5.0, s["model"], verbose=False).process()
+    assert out.shape == (0,) and out.dtype == s["field"].cat.dtype
+    # masses far above the tabulated range: scipy's fill_value NaN -> the reference adds nothing for those halos
+    g = syn.config_grid(npix=48, nhalo=40, dim=2, epsilon_max=20.0)
+    g["catalog"].cat["M"][::2] *= 1e4
+    for cls, model in ((bf.BaryonifyGrid, g["model"]), (bf.PaintProfilesGrid, g["paint_model"])):
+        got = cls(g["catalog"], g["field"], 20.0, model, verbose=False).process()
+        want = getattr(orc, cls.__name__)(g["catalog"], g["field"], 20.0, model).process()
+        assert relmax(got, want) < 1e-11
+
+
 # ------------------------------------------------------------------ committed reference fixtures
 import cases  # noqa: E402
 
