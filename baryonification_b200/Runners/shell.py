@@ -61,6 +61,9 @@ class DefaultRunner:
                                baryonify)
         s["extras"] = host.property_columns(self.HaloLightConeCatalog.cat, self.model)
         self.timings["host_setup"] = time.perf_counter() - t0
+        after = getattr(self, "_after_host", None)
+        if after is not None:  # e.g. start the map upload now: the host cores are free while the GPU works
+            after()
         t0 = time.perf_counter()
         eng = engine.ShellEngine(self.LightconeShell.NSIDE, mode, htab, s, dev, variant=self.variant, bands=bands)
         eng.upload().bin()
@@ -89,10 +92,16 @@ class BaryonifyShell(DefaultRunner):
         dev = dv.device(self.device)
         with torch.cuda.device(dev):
             orig = np.ascontiguousarray(self.LightconeShell.map, dtype=np.float64)
-            up = dv.AsyncUpload(orig, dev)  # the 8 B/pixel map travels while halos are set up, binned and evaluated
-            off = self.offsets_device(dev)
+            # the 8 B/pixel map travels (pageable -> pinned -> HBM) while halos are binned and evaluated on the GPU; it
+            # starts after the host set-up, which wants all host cores for itself
+            box = {}
+            self._after_host = lambda: box.setdefault("up", dv.AsyncUpload(orig, dev))
+            try:
+                off = self.offsets_device(dev)
+            finally:
+                self._after_host = None
             t0 = time.perf_counter()
-            orig_d = up.result()
+            orig_d = (box.get("up") or dv.AsyncUpload(orig, dev)).result()
             new_d = self._eng.regrid(orig_d, off, method=self.regrid)
             self._eng = None
             new_sum_d, old_sum_d = new_d.sum(), orig_d.sum()  # the reference's two np.sum's, on the device
