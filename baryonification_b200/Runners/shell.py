@@ -36,6 +36,12 @@ class DefaultRunner:
         self.variant = variant          # pair stage: "gather" (deterministic, default) | "atomic"
         self.regrid = regrid            # re-binning: "sorted" (deterministic, default) | "atomic"
         self.pinned_output = pinned_output
+        # opt-in (pipeline_chunks > 1): catalogues of at least `pipeline_min_halos` are cut into runs of consecutive halos
+        # and the host set-up of run k+1 overlaps the GPU stages of run k (sums continue on the device in catalogue
+        # order).  Off by default: on the 16-vCPU hosts of this pool the host threads, the pinned-memory copies and the
+        # launching thread compete for the same cores and the end-to-end time does not improve (scripts/e2e_shell_pipeline.py)
+        self.pipeline_chunks, self.pipeline_min_halos = 1, 400_000
+        self.pipeline_upload_after = 0  # index of the halo run after whose host set-up the map upload starts
         self.npairs = None
         self.timings = {}
         if use_ellipticity:  # HealpixRunner.py:164-165
@@ -70,6 +76,74 @@ class DefaultRunner:
         self._tick("upload_bin", t0, dev)
         return eng
 
+    def _pairs(self, dev, mode):
+        """Host set-up + binning + pair stage -> (engine, device accumulator); sets ``npairs``."""
+        nh = len(self.HaloLightConeCatalog.cat)
+        if self.variant != "gather" or self.pipeline_chunks < 2 or nh < self.pipeline_min_halos:
+            eng = self._engine(dev, mode)
+            t0 = time.perf_counter()
+            out = eng.accumulate()
+            self.npairs = eng.pair_count()
+            self._tick("accumulate", t0, dev)
+            return eng, out
+        return self._pairs_pipelined(dev, mode, nh)
+
+    def _pairs_pipelined(self, dev, mode, nh):
+        import copy
+        import queue
+        import threading
+        baryonify = mode == engine.BARYONIFY
+        self._check_keys(baryonify)
+        t00 = time.perf_counter()
+        htab = displacement_host_table(self.model) if baryonify else profile_host_table(self.model, "2D")
+        K = self.pipeline_chunks
+        bounds = [(nh * k // K, nh * (k + 1) // K) for k in range(K)]
+        q = queue.Queue()
+        state = {"out": None, "eng": None, "pairs": 0, "err": None}
+
+        def gpu_side():
+            try:
+                with torch.cuda.device(dev):
+                    k = 0
+                    while True:
+                        s = q.get()
+                        if s is None:
+                            return
+                        eng = engine.ShellEngine(self.LightconeShell.NSIDE, mode, htab, s, dev, variant="gather")
+                        eng.upload().bin()
+                        state["out"] = eng.accumulate(state["out"], add=k > 0)
+                        state["pairs"] += eng.pair_count()  # also keeps the chunk's buffers alive until it is done
+                        state["eng"] = eng
+                        k += 1
+            except BaseException as e:  # re-raised by the caller
+                state["err"] = e
+
+        th = threading.Thread(target=gpu_side, daemon=True)
+        th.start()
+        t_host = 0.0
+        try:
+            for i, (a, b) in enumerate(bounds):
+                t0 = time.perf_counter()
+                part = copy.copy(self.HaloLightConeCatalog)
+                part.cat = self.HaloLightConeCatalog.cat[a:b]
+                s = host.shell_scalars(part, self.cosmo, self.mass_def, self.epsilon_max, self.model, baryonify)
+                s["extras"] = host.property_columns(part.cat, self.model)
+                t_host += time.perf_counter() - t0
+                q.put(s)
+                if i == self.pipeline_upload_after:
+                    after = getattr(self, "_after_host", None)
+                    if after is not None:  # the map upload (host memcpy into pinned memory) joins here
+                        after()
+        finally:
+            q.put(None)
+            th.join()
+        if state["err"] is not None:
+            raise state["err"]
+        self.npairs = state["pairs"]
+        self.timings["host_setup"] = t_host
+        self.timings["pairs_pipelined"] = time.perf_counter() - t00
+        return state["eng"], state["out"]
+
     def _tick(self, name, t0, dev):
         torch.cuda.synchronize(dev)
         self.timings[name] = time.perf_counter() - t0
@@ -80,12 +154,7 @@ class BaryonifyShell(DefaultRunner):
     """Baryonify a HEALPix *mass* map (RING) with a tabulated displacement model."""
 
     def offsets_device(self, dev):
-        eng = self._engine(dev, engine.BARYONIFY)
-        t0 = time.perf_counter()
-        off = eng.accumulate()
-        self.npairs = eng.pair_count()
-        self._tick("accumulate", t0, dev)
-        self._eng = eng
+        self._eng, off = self._pairs(dev, engine.BARYONIFY)
         return off
 
     def process(self):
@@ -119,11 +188,7 @@ class PaintProfilesShell(DefaultRunner):
 
     def process_device(self, dev):
         assert self.model is not None, "You must provide a model"
-        eng = self._engine(dev, engine.PAINT)
-        t0 = time.perf_counter()
-        out = eng.accumulate()
-        self.npairs = eng.pair_count()
-        self._tick("accumulate", t0, dev)
+        _, out = self._pairs(dev, engine.PAINT)
         return out
 
     def process(self):

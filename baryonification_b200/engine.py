@@ -84,8 +84,9 @@ class ShellEngine:
         raise _lib.BFError("bf_shell_bin_halos: workspace retry failed")
 
     # ---- stage 2: pair evaluation ----------------------------------------------------------------
-    def accumulate(self, out=None):
-        """Returns the device accumulator of the engine's pixel range: map [n] or pix_offsets [n, 3]."""
+    def accumulate(self, out=None, add=False):
+        """Returns the device accumulator of the engine's pixel range: map [n] or pix_offsets [n, 3].  ``add``: sum on
+        top of what ``out`` holds (gather variant; halo chunks of one catalogue evaluated one after the other)."""
         n = self.pix_last - self.pix_first
         shape = (n,) if self.mode == PAINT else (n, 3)
         self.cnt.zero_()
@@ -93,9 +94,11 @@ class ShellEngine:
             if out is None:
                 out = dv.empty(shape, dev=self.dev)
             _lib.call("bf_shell_gather", self.nside, self.mode, C.byref(self.desc), C.byref(self.table.desc),
-                      self.bands[0], self.bands[1], dv.ptr(self.ws), dv.ptr(out), self.pix_first, 0, dv.ptr(self.cnt),
-                      dv.stream_ptr())
+                      self.bands[0], self.bands[1], dv.ptr(self.ws), dv.ptr(out), self.pix_first, 1 if add else 0,
+                      dv.ptr(self.cnt), dv.stream_ptr())
         else:
+            if add:
+                raise _lib.BFError("chunked accumulation is a feature of the gather variant")
             if self.bands != (0, self.lib.bf_shell_num_bands(self.nside)):
                 raise _lib.BFError("the atomic variant does not shard by ring band")
             if out is None:

@@ -262,6 +262,31 @@ def test_snapshot_chunked_transfer_pipeline_equals_one_shot(gpu, monkeypatch):
         assert np.array_equal(got[k], want[k]), k
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("cls", ["BaryonifyShell", "PaintProfilesShell"])
+def test_shell_halo_chunk_pipeline_equals_one_pass(gpu, cls):
+    """Large catalogues are evaluated in runs of consecutive halos (host set-up of run k+1 under the kernels of run k);
+    same pair set, sums continue on the device in catalogue order (only the grouping of partial sums changes)."""
+    import baryonification_b200 as bf
+    from baryonification_b200 import synthetic as syn
+    cfg = syn.config_shell(nside=128, nhalo=3001, zero_map=(cls == "PaintProfilesShell"))
+    model = cfg["paint_model"] if cls == "PaintProfilesShell" else cfg["model"]
+    one = getattr(bf, cls)(cfg["catalog"], cfg["field"], 20.0, model, verbose=False)
+    want = one.process()
+    piped = getattr(bf, cls)(cfg["catalog"], cfg["field"], 20.0, model, verbose=False)
+    piped.pipeline_min_halos, piped.pipeline_chunks, piped.pipeline_upload_after = 1000, 3, 2
+    got = piped.process()
+    assert "pairs_pipelined" in piped.timings and "pairs_pipelined" not in one.timings
+    assert piped.npairs == one.npairs
+    assert relmax(got, want) < 1e-13
+    if cls == "PaintProfilesShell":
+        assert np.array_equal(got != 0, want != 0)
+    again = getattr(bf, cls)(cfg["catalog"], cfg["field"], 20.0, model, verbose=False)
+    again.pipeline_min_halos, again.pipeline_chunks = 1000, 3
+    if cls == "PaintProfilesShell":
+        assert np.array_equal(again.process(), got)  # still deterministic
+
+
 # ------------------------------------------------------------------ empty / degenerate inputs
 def _empty(cat):
     import copy
