@@ -119,8 +119,8 @@ class BaryonifySnapshot(DefaultRunnerSnapshot):
         want = {"M": 0, "x": 8, "y": 16, "z": 24}
         return all(k in d.fields and d.fields[k][1] == o and d.fields[k][0] == np.dtype("=f8") for k, o in want.items())
 
-    def _setup(self, dev):
-        """Table, per-halo arrays, (z, M) collapse and halo binning into the periodic grid."""
+    def _upload(self, dev):
+        """Host part of the set-up: per-halo scalars (vectorised numpy) and their H2D copies, table upload."""
         S = self.ParticleSnapshot
         if len(vars(self.model).get("p_keys", [])) > 0:
             raise NotImplementedError("property-keyed tables are not yet supported by the B200 runners")
@@ -129,29 +129,41 @@ class BaryonifySnapshot(DefaultRunnerSnapshot):
         s = host.snapshot_scalars(self.HaloNDCatalog, S, self.mass_def, self.epsilon_max, self.model)
         dim, nh = s["dim"], s["Rq"].size
         t = {k: dv.to_dev(s[k], dev=dev) for k in ("pos", "Rq", "cut", "lnr_shift", "z_in", "M_in")}
-        rows = table.collapse(t["z_in"], t["M_in"])
-        desc = _lib.SnapHalos(t["pos"].data_ptr(), t["Rq"].data_ptr(), t["cut"].data_ptr(),
-                              t["lnr_shift"].data_ptr(), rows.data_ptr(), nh)
         L = float(S.L)
         ng = lib.bf_snap_grid_cells(dim, L, float(s["Rq"].mean()) if nh else 0.0)
         if os.environ.get("BF_SNAP_NG"):  # tuning experiments only
             ng = int(os.environ["BF_SNAP_NG"])
-        max_entries, ws = 0, None
+        return dict(table=table, s=s, t=t, ng=ng, dim=dim, L=L, nh=nh, ws=None, max_entries=0)
+
+    def _bin(self, st, dev):
+        """Device part of the set-up: (z, M) collapse and halo binning into the periodic grid.  The workspace of an
+        earlier call on the same ``st`` is reused (the counting pass only runs when it does not fit)."""
+        lib = _lib.load(require_cuda=True)
+        t, dim, nh, L, ng = st["t"], st["dim"], st["nh"], st["L"], st["ng"]
+        st["rows"] = rows = st["table"].collapse(t["z_in"], t["M_in"])
+        st["desc"] = desc = _lib.SnapHalos(t["pos"].data_ptr(), t["Rq"].data_ptr(), t["cut"].data_ptr(),
+                                           t["lnr_shift"].data_ptr(), rows.data_ptr(), nh)
         for _ in range(2):  # counting pass first (exact size), then the real one
-            need = lib.bf_snap_ws_bytes(dim, nh, L, ng, max_entries)
-            ws = torch.empty(max(need, 256), dtype=torch.uint8, device=dev)
+            need = max(lib.bf_snap_ws_bytes(dim, nh, L, ng, st["max_entries"]), 256)
+            if st["ws"] is None or st["ws"].numel() < need:
+                st["ws"] = None
+                st["ws"] = torch.empty(need, dtype=torch.uint8, device=dev)
             n = C.c_int64()
-            rc = lib.bf_snap_bin_halos(dim, L, ng, C.byref(desc), max_entries, dv.ptr(ws), ws.numel(), C.byref(n),
-                                       dv.stream_ptr())
-            if rc == -2 and n.value > max_entries:
-                max_entries = n.value
+            rc = lib.bf_snap_bin_halos(dim, L, ng, C.byref(desc), st["max_entries"], dv.ptr(st["ws"]), st["ws"].numel(),
+                                       C.byref(n), dv.stream_ptr())
+            if rc == -2 and n.value > st["max_entries"]:
+                st["max_entries"] = n.value
                 continue
             _lib.check(rc, "bf_snap_bin_halos")
             break
         else:
             raise _lib.BFError("bf_snap_bin_halos: workspace retry failed")
         self.nentries = n.value
-        return dict(table=table, s=s, t=t, rows=rows, desc=desc, ng=ng, ws=ws, dim=dim, L=L)
+        return st
+
+    def _setup(self, dev):
+        """Table, per-halo arrays, (z, M) collapse and halo binning into the periodic grid."""
+        return self._bin(self._upload(dev), dev)
 
     def process(self):
         dev = dv.device(self.device)

@@ -374,8 +374,10 @@ def run_snapshot(args, rank, local_rank, world):
     ev = lambda: torch.cuda.Event(enable_timing=True)
     kms = []
 
+    st = runner._upload(dev)  # per-halo scalars and the table are resident in HBM before the timed region, like the shell's
+
     def step(timed):
-        st = runner._setup(dev)  # table upload, (z, M) collapse, halo binning into the periodic grid
+        runner._bin(st, dev)  # (z, M) collapse + halo binning into the periodic grid
         cnt.zero_()
         a, b = ev(), ev()
         a.record()
