@@ -73,6 +73,7 @@ struct pk_args {
     int nk;
     i64 nmodes, per_block;
     int mem_n[3], mem_ax[3];  // memory order (slowest first): extent and LOGICAL axis (0 = i, 1 = j, 2 = l) of each level
+    int off[3];               // global index of the piece's first element along each LOGICAL axis (slab-decomposed FFT)
     double *partial;          // [nblocks][3][nk]  (power, k, count)
 };
 
@@ -95,7 +96,7 @@ __global__ void __launch_bounds__(PK_THREADS) pk_bin_kernel(pk_args A) {
             idx[A.mem_ax[2]] = c2;
             idx[A.mem_ax[1]] = (int)(r01 % A.mem_n[1]);
             idx[A.mem_ax[0]] = (int)(r01 / A.mem_n[1]);
-            const int i = idx[0], j = idx[1], l = idx[2];
+            const int i = idx[0] + A.off[0], j = idx[1] + A.off[1], l = idx[2] + A.off[2];
             const double kx = (double)((i < (A.N + 1) / 2) ? i : i - A.N) * A.val;
             const double ky = (double)((j < (A.N + 1) / 2) ? j : j - A.N) * A.val;
             const double kz = (double)((l < (A.N + 1) / 2) ? l : l - A.N) * A.val;  // l = N/2 -> -N/2 (same square)
@@ -149,19 +150,32 @@ static int pk_blocks(i64 nmodes) {
     return (int)((nb < want) ? (nb < 1 ? 1 : nb) : want);
 }
 
+static size_t pk_ws_bytes(i64 nmodes, i64 nk) { return sizeof(double) * 3 * (size_t)nk * (size_t)pk_blocks(nmodes) + 256; }
+
 extern "C" size_t bf_pk_bin_ws_bytes(int64_t ngrid, int64_t nk) {
     if (ngrid < 2 || nk < 1) return 0;
-    i64 nmodes = ngrid * ngrid * (ngrid / 2 + 1);
-    return sizeof(double) * 3 * (size_t)nk * (size_t)pk_blocks(nmodes) + 256;
+    return pk_ws_bytes(ngrid * ngrid * (ngrid / 2 + 1), nk);
 }
 
-extern "C" int bf_pk_bin(int64_t ngrid, const void *spectrum, const int64_t *strides_host, double val, double k0,
-                         double dk, int64_t nk, double *out /* [3][nk]: sum |F|^2, sum k, count */, void *ws,
-                         size_t ws_bytes, void *stream) {
-    BF_REQUIRE(ngrid >= 2 && ngrid <= 4096 && spectrum && out, "ngrid / spectrum / out");
+extern "C" size_t bf_pk_bin_part_ws_bytes(const int64_t *ext_host, int64_t nk) {
+    if (!ext_host || nk < 1 || ext_host[0] < 0 || ext_host[1] < 0 || ext_host[2] < 0) return 0;
+    return pk_ws_bytes(ext_host[0] * ext_host[1] * ext_host[2], nk);
+}
+
+// A rectangular PIECE of the half-complex spectrum: logical extents ext[3] (axes i, j, l), first global index off[3].
+// The slab-decomposed transform leaves every rank with all i, a range of j and all l; the per-rank [3][nk] sums are
+// then added across ranks (sharding.ShardedPowerSpectrum).  The whole spectrum is the piece with off = 0.
+extern "C" int bf_pk_bin_part(int64_t ngrid, const void *spectrum, const int64_t *strides_host, const int64_t *ext_host,
+                              const int64_t *off_host, double val, double k0, double dk, int64_t nk,
+                              double *out /* [3][nk]: sum |F|^2, sum k, count */, void *ws, size_t ws_bytes,
+                              void *stream) {
+    BF_REQUIRE(ngrid >= 2 && ngrid <= 4096 && out && ext_host && off_host, "ngrid / out / ext / off");
     BF_REQUIRE(nk >= 1 && nk <= 768 && dk > 0, "nk must be in [1, 768], dk > 0");
-    BF_REQUIRE((((uintptr_t)spectrum) & 15) == 0, "spectrum must be 16-byte aligned complex128");
-    size_t need = bf_pk_bin_ws_bytes(ngrid, nk);
+    const i64 nhalf = ngrid / 2 + 1;
+    i64 ext[3] = {ext_host[0], ext_host[1], ext_host[2]}, full[3] = {ngrid, ngrid, nhalf};
+    for (int a = 0; a < 3; ++a)
+        BF_REQUIRE(ext[a] >= 0 && off_host[a] >= 0 && off_host[a] + ext[a] <= full[a], "piece outside the spectrum");
+    size_t need = bf_pk_bin_part_ws_bytes(ext_host, nk);
     if (!ws || ws_bytes < need) {
         bf_set_error("bf_pk_bin: workspace %zu < %zu bytes", ws_bytes, need);
         return BF_E_WORKSPACE;
@@ -169,30 +183,48 @@ extern "C" int bf_pk_bin(int64_t ngrid, const void *spectrum, const int64_t *str
     pk_args A;
     A.F = (const double2 *)spectrum;
     A.N = (int)ngrid;
-    A.nh = (int)(ngrid / 2 + 1);
+    A.nh = (int)nhalf;
     A.val = val; A.k0 = k0; A.dk = dk;
     A.nk = (int)nk;
-    A.nmodes = ngrid * ngrid * (i64)A.nh;
+    A.nmodes = ext[0] * ext[1] * ext[2];
+    cudaStream_t s = (cudaStream_t)stream;
+    if (A.nmodes == 0) {
+        BF_CUDA_OK(cudaMemsetAsync(out, 0, sizeof(double) * 3 * (size_t)nk, s));
+        return BF_OK;
+    }
+    BF_REQUIRE(spectrum && (((uintptr_t)spectrum) & 15) == 0, "spectrum must be 16-byte aligned complex128");
     {   // memory order of the three logical axes from their element strides (NULL = C order); must be dense
-        i64 ext[3] = {ngrid, ngrid, (i64)A.nh}, st[3] = {ngrid * (i64)A.nh, (i64)A.nh, 1};
+        i64 st[3] = {ext[1] * ext[2], ext[2], 1};
         if (strides_host) { st[0] = strides_host[0]; st[1] = strides_host[1]; st[2] = strides_host[2]; }
         int ord[3] = {0, 1, 2};
         for (int a = 0; a < 3; ++a)
             for (int b = a + 1; b < 3; ++b)
-                if (st[ord[b]] > st[ord[a]]) { int t = ord[a]; ord[a] = ord[b]; ord[b] = t; }
-        BF_REQUIRE(st[ord[2]] == 1 && st[ord[1]] == ext[ord[2]] && st[ord[0]] == ext[ord[2]] * ext[ord[1]],
-                   "spectrum must be a dense permutation of [ngrid][ngrid][ngrid/2+1]");
+                if (st[ord[b]] > st[ord[a]] || (st[ord[b]] == st[ord[a]] && ext[ord[b]] > ext[ord[a]])) {
+                    int t = ord[a]; ord[a] = ord[b]; ord[b] = t;
+                }
+        // (an axis of extent 1 may carry any stride: it never moves)
+        bool dense = (ext[ord[2]] == 1 || st[ord[2]] == 1) && (ext[ord[1]] == 1 || st[ord[1]] == ext[ord[2]]) &&
+                     (ext[ord[0]] == 1 || st[ord[0]] == ext[ord[2]] * ext[ord[1]]);
+        BF_REQUIRE(dense, "spectrum must be a dense permutation of its logical extents");
         for (int d = 0; d < 3; ++d) { A.mem_ax[d] = ord[d]; A.mem_n[d] = (int)ext[ord[d]]; }
     }
+    for (int a = 0; a < 3; ++a) A.off[a] = (int)off_host[a];
     int nb = pk_blocks(A.nmodes);
     A.per_block = ((A.nmodes + nb - 1) / nb + 31) / 32 * 32;
     A.partial = (double *)ws;
     size_t smem = sizeof(double) * PK_WARPS * 3 * (size_t)nk;
-    cudaStream_t s = (cudaStream_t)stream;
     BF_CUDA_OK(cudaFuncSetAttribute(pk_bin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     pk_bin_kernel<<<nb, PK_THREADS, smem, s>>>(A);
     BF_LAUNCH_OK();
     pk_finish_kernel<<<(unsigned)((3 * nk + 127) / 128), 128, 0, s>>>(nb, (int)nk, A.partial, out);
     BF_LAUNCH_OK();
     return BF_OK;
+}
+
+extern "C" int bf_pk_bin(int64_t ngrid, const void *spectrum, const int64_t *strides_host, double val, double k0,
+                         double dk, int64_t nk, double *out /* [3][nk]: sum |F|^2, sum k, count */, void *ws,
+                         size_t ws_bytes, void *stream) {
+    BF_REQUIRE(ngrid >= 2 && ngrid <= 4096 && spectrum && out, "ngrid / spectrum / out");
+    const int64_t ext[3] = {ngrid, ngrid, ngrid / 2 + 1}, off[3] = {0, 0, 0};
+    return bf_pk_bin_part(ngrid, spectrum, strides_host, ext, off, val, k0, dk, nk, out, ws, ws_bytes, stream);
 }

@@ -86,6 +86,8 @@ def index_split(n, world):
 # collectives (any backend / device)
 # ----------------------------------------------------------------------------------------------------------
 def _world(group):
+    if not dist.is_initialized():  # a single process without a process group is the 1-rank case
+        return 0, 1
     return dist.get_rank(group), dist.get_world_size(group)
 
 
@@ -437,3 +439,116 @@ def _runs(sorted_rows):
     if start is not None:
         out.append((start, prev + 1))
     return out
+
+
+# ----------------------------------------------------------------------------------------------------------
+# Delta P(k) on N GPUs: slab-decomposed transform (last row)
+# ----------------------------------------------------------------------------------------------------------
+def reduce_to_slab(full, rows, group=None):
+    """Sum the ranks' full-size deposit grids [N, N, N] and keep this rank's x-slab ``rows[rank]``.  NGP counts are
+    whole numbers, so the sum is exact in any order.  NCCL: one reduce-scatter when the slabs are equal, otherwise
+    (and on gloo, which has no reduce-scatter) an all-reduce followed by the slice."""
+    rank, world = _world(group)
+    a, b = rows[rank]
+    if world == 1:
+        return full[a:b]
+    equal = all(r[1] - r[0] == b - a for r in rows)
+    if equal and dist.get_backend(group) == "nccl":
+        out = torch.empty((b - a,) + tuple(full.shape[1:]), dtype=full.dtype, device=full.device)
+        dist.reduce_scatter_tensor(out, full.contiguous(), group=group)
+        return out
+    dist.all_reduce(full, group=group)
+    return full[a:b]
+
+
+def slab_rfftn(slab, rows, group=None):
+    """rfftn of a real [N, N, N] mesh held as x-slabs: rank g passes ``slab`` = planes ``rows[g]``.
+
+    Local 2-D real transforms over (y, z) -> the only exchange of the path, an all-to-all TRANSPOSE (every rank
+    sends rank h the y-range ``cols[h]`` of its planes and receives all x for its own y-range) -> 1-D transforms over
+    x.  Returns ``(piece, (j0, j1))`` with ``piece[i, j - j0, l] = rfftn(mesh)[i, j, l]`` complex, all i, j in
+    [j0, j1), all l = 0..N/2.  Device-agnostic (torch.fft is cuFFT on the GPU), point-to-point through
+    ``batch_isend_irecv`` so that the same code runs on gloo in the CPU tests."""
+    rank, world = _world(group)
+    N = int(slab.shape[1])
+    nh = N // 2 + 1
+    cols = index_split(N, world)
+    j0, j1 = cols[rank]
+    A = torch.fft.rfft2(slab, dim=(1, 2))  # [nx_loc, N, nh]
+    if world == 1:
+        return torch.fft.fft(A, dim=0), (j0, j1)
+    T = torch.empty((N, j1 - j0, nh), dtype=A.dtype, device=A.device)
+    ops, keep = [], []
+    for h in range(world):
+        c0, c1 = cols[h]
+        x0, x1 = rows[h]
+        if h == rank:
+            T[x0:x1] = A[:, j0:j1]
+            continue
+        if c1 > c0 and A.shape[0] > 0:
+            payload = torch.view_as_real(A[:, c0:c1].contiguous())
+            keep.append(payload)
+            ops.append(dist.P2POp(dist.isend, payload, dist.get_global_rank(group, h) if group is not None else h,
+                                  group=group))
+        if x1 > x0 and j1 > j0:  # planes x0..x1 of T are one contiguous block: receive in place
+            ops.append(dist.P2POp(dist.irecv, torch.view_as_real(T[x0:x1]),
+                                  dist.get_global_rank(group, h) if group is not None else h, group=group))
+    if ops:
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+    return torch.fft.fft(T, dim=0), (j0, j1)
+
+
+class ShardedPowerSpectrum:
+    """``pk.PowerSpectrumGrid`` on N ranks: every rank deposits ITS particles (any partition: e.g. the slice
+    ``ShardedSnapshot.process(gather=False)`` returns), the mesh is reduced onto x-slabs, transformed with
+    :func:`slab_rfftn`, k-binned piece by piece (``bf_pk_bin_part``) and the ``[3][Nk]`` bin sums are all-reduced, so
+    every rank returns the whole spectrum.  Mode counts equal the single-GPU ones exactly; the power agrees to FFT
+    rounding (the 2-D + 1-D factorisation adds in a different order than cuFFT's 3-D plan)."""
+
+    def __init__(self, Ngrd, Lbox, Nk=180, group=None, device=None):
+        from .pk import PowerSpectrumGrid
+        self.local = PowerSpectrumGrid(Ngrd, Lbox, Nk, device=device)
+        self.Ngrd, self.Lbox, self.Nk, self.group, self.device = int(Ngrd), float(Lbox), int(Nk), group, device
+        self.rank, self.world = _world(group)
+        self.rows = index_split(self.Ngrd, self.world)
+
+    def density_slab(self, particles_local, factor=1):
+        """This rank's x-slab of the NGP counts of ALL ranks' particles, [rows[rank], N, N] float64 on the device."""
+        full = self.local.density(particles_local, factor)
+        return reduce_to_slab(full, self.rows, self.group)
+
+    def power_of_slab(self, slab, factor=1):
+        from . import _device as dv
+        dev = slab.device
+        _, val, k0, dk = self.local._setup(factor)
+        with torch.cuda.device(dev):
+            piece, (j0, j1) = slab_rfftn(slab, self.rows, self.group)
+            lib = _lib.load(require_cuda=True)
+            ext = (C.c_int64 * 3)(self.Ngrd, j1 - j0, self.Ngrd // 2 + 1)
+            off = (C.c_int64 * 3)(0, j0, 0)
+            nb = lib.bf_pk_bin_part_ws_bytes(ext, self.Nk)
+            ws = torch.empty(max(nb, 256), dtype=torch.uint8, device=dev)
+            out = dv.empty((3, self.Nk), dev=dev)
+            strides = (C.c_int64 * 3)(*piece.stride())
+            _lib.call("bf_pk_bin_part", self.Ngrd, dv.ptr(piece) if piece.numel() else None, strides, ext, off, val, k0,
+                      dk, self.Nk, dv.ptr(out), dv.ptr(ws), ws.numel(), dv.stream_ptr())
+            if self.world > 1:
+                dist.all_reduce(out, group=self.group)
+            o = out.cpu().numpy()
+        with np.errstate(divide="ignore", invalid="ignore"):
+            return o[1] / o[2] * factor, o[0] / o[2], o[2]
+
+    def power(self, particles_local, factor=1):
+        """(k_cen * factor, P(k), modes per bin) of the union of the ranks' particle sets, on every rank."""
+        return self.power_of_slab(self.density_slab(particles_local, factor), factor)
+
+    def suppression(self, part_baryon_local, part_dmo_local, factors=(1, 8)):
+        """{factor: {'k', 'S' = P_baryon / P_dmo}} as ``PowerSpectrumGrid.suppression``, on every rank."""
+        res = {}
+        pb, pd = self.local.upload(part_baryon_local), self.local.upload(part_dmo_local)
+        for f in factors:
+            k, PB, _ = self.power(pb, f)
+            _, PD, _ = self.power(pd, f)
+            res[f"Factor{f}"] = {"k": k, "S": PB / PD}
+        return res

@@ -246,6 +246,14 @@ int bf_pk_ngp_deposit(int64_t np, const double *x, const double *y, const double
 size_t bf_pk_bin_ws_bytes(int64_t ngrid, int64_t nk);
 int bf_pk_bin(int64_t ngrid, const void *spectrum, const int64_t *strides_host, double val, double k0, double dk,
               int64_t nk, double *out, void *ws, size_t ws_bytes, void *stream);
+/* The same over a rectangular PIECE of the spectrum, for the slab-decomposed transform of the N-GPU path (SURVEY.md
+ * 8(e), last row): ext_host[3] = logical extents of the piece (axes i, j, l), off_host[3] = global index of its first
+ * element, strides_host as above (NULL = C order of the piece).  The [3][nk] sums of all pieces add up to bf_pk_bin's
+ * (counts exactly); an empty piece zeroes `out`. */
+size_t bf_pk_bin_part_ws_bytes(const int64_t *ext_host, int64_t nk);
+int bf_pk_bin_part(int64_t ngrid, const void *spectrum, const int64_t *strides_host, const int64_t *ext_host,
+                   const int64_t *off_host, double val, double k0, double dk, int64_t nk, double *out, void *ws,
+                   size_t ws_bytes, void *stream);
 
 #ifdef __cplusplus
 }

@@ -658,6 +658,45 @@ def test_delta_pk_matches_notebook_recipe(gpu, ngrd, nk, factor):
     assert np.array_equal(P, P2) and np.array_equal(k, k2)  # deterministic reduction: bit-reproducible
 
 
+@pytest.mark.parametrize("ngrd,nk,parts", [(32, 12, 2), (27, 9, 4), (20, 7, 8)])
+def test_delta_pk_piecewise_binning_adds_up(gpu, ngrd, nk, parts):
+    """bf_pk_bin_part over y-ranges of the spectrum (the pieces the slab-decomposed transform leaves on the ranks):
+    mode counts add up exactly to the whole-spectrum binning, power and k sums to rounding; the 1-rank
+    ShardedPowerSpectrum (2-D + 1-D transforms) agrees with PowerSpectrumGrid."""
+    import ctypes as C
+    import torch
+    from baryonification_b200 import _device as dv, _lib, sharding as sh
+    from baryonification_b200.pk import PowerSpectrumGrid
+    rng = np.random.default_rng(ngrd)
+    L = 150.0
+    pts = rng.uniform(0, L, (100_000, 3))
+    ps = PowerSpectrumGrid(ngrd, L, nk)
+    grid = ps.density(pts)
+    k, P, nm = ps.power(grid)
+    _, val, k0, dk = ps._setup(1)
+    F = torch.fft.rfftn(grid)
+    lib = _lib.load(require_cuda=True)
+    tot = np.zeros((3, nk))
+    for j0, j1 in sh.index_split(ngrd, parts):
+        piece = F[:, j0:j1].contiguous()
+        ext = (C.c_int64 * 3)(ngrd, j1 - j0, ngrd // 2 + 1)
+        off = (C.c_int64 * 3)(0, j0, 0)
+        nb = lib.bf_pk_bin_part_ws_bytes(ext, nk)
+        ws = torch.empty(max(nb, 256), dtype=torch.uint8, device=grid.device)
+        out = dv.empty((3, nk), dev=grid.device)
+        _lib.call("bf_pk_bin_part", ngrd, dv.ptr(piece) if piece.numel() else None, None, ext, off, val, k0, dk, nk,
+                  dv.ptr(out), dv.ptr(ws), ws.numel(), dv.stream_ptr())
+        tot += out.cpu().numpy()
+    assert np.array_equal(tot[2], nm)
+    ok = nm > 0
+    assert np.allclose(tot[0][ok] / tot[2][ok], P[ok], rtol=1e-12, atol=0)
+    assert np.allclose(tot[1][ok] / tot[2][ok], k[ok], rtol=1e-13, atol=0)
+    sp = sh.ShardedPowerSpectrum(ngrd, L, nk)
+    k1, P1, nm1 = sp.power(pts)
+    assert np.array_equal(nm1, nm)
+    assert np.allclose(P1[ok], P[ok], rtol=1e-11, atol=0) and np.allclose(k1[ok], k[ok], rtol=1e-13, atol=0)
+
+
 def test_delta_pk_suppression_of_a_baryonified_snapshot(gpu):
     import baryonification_b200 as bf
     from baryonification_b200 import synthetic as syn

@@ -216,3 +216,50 @@ def test_ghost_width_from_the_displacement_window_covers_every_deposit():
         allowed = np.zeros(n, dtype=bool)
         allowed[[g % n for g in range(a0 - below, a1 + above)]] = True
         assert np.all(allowed[a[dest_hit]])
+
+
+# ------------------------------------------------------------------ Delta P(k): slab-decomposed transform
+def _bin_piece(piece, j0, N, Nk, L):
+    """Test-side k-binning of a [N, j1 - j0, N/2 + 1] piece of rfftn (what bf_pk_bin_part does on the device): the
+    notebook's bin index (cell 12) with every mirrored mode (0 < l < N/2) counted twice."""
+    kf = 2 * np.pi / L
+    kbins = np.linspace(kf, kf * N / 2, Nk + 1)
+    klin = np.fft.fftfreq(N, 1 / kf / N)
+    nh = N // 2 + 1
+    nj = piece.shape[1]
+    k = np.sqrt((klin[:, None, None] ** 2 + klin[None, None, :nh] ** 2) + klin[None, j0:j0 + nj, None] ** 2)
+    kinds = np.floor((k - kbins[0]) / (kbins[1] - kbins[0])).astype(int)
+    l = np.arange(nh)[None, None, :]
+    wt = np.where((l > 0) & (l < N / 2), 2.0, 1.0) * np.ones_like(k)
+    m = (kinds >= 0) & (kinds < Nk)
+    pw = (piece.real ** 2 + piece.imag ** 2) * wt
+    return np.stack([np.bincount(kinds[m], weights=pw[m], minlength=Nk), np.bincount(kinds[m], weights=wt[m], minlength=Nk)])
+
+
+def _slab_fft_ranks(rank, world, N, Nk):
+    from oracle import pk as opk
+    rng = np.random.default_rng(77)
+    pts = rng.uniform(0, 50.0, size=(4000, 3))
+    rows = sh.index_split(N, world)
+    mine = pts[rank::world]                       # any partition of the particles works
+    full = torch.from_numpy(opk.histogram3d(mine, N, 0.0, 50.0).astype(np.float64))
+    slab = sh.reduce_to_slab(full, rows)
+    Map = opk.histogram3d(pts, N, 0.0, 50.0)
+    a, b = rows[rank]
+    assert np.array_equal(slab.numpy(), Map[a:b])
+    piece, (j0, j1) = sh.slab_rfftn(slab, rows)
+    want = np.fft.rfftn(Map)
+    assert piece.shape == (N, j1 - j0, N // 2 + 1)
+    scale = np.abs(want).max()
+    assert np.max(np.abs(piece.numpy() - want[:, j0:j1])) < 1e-12 * scale
+    sums = torch.from_numpy(_bin_piece(piece.numpy(), j0, N, Nk, 50.0))
+    dist.all_reduce(sums)
+    _, Pk, k_c, _ = opk.power(pts, N, Nk, 50.0)
+    assert np.array_equal(sums[1].numpy(), k_c)   # every mode of the cube exactly once across the pieces
+    ok = k_c > 0
+    assert np.allclose(sums[0].numpy()[ok] / k_c[ok], Pk[ok], rtol=1e-11)
+
+
+@pytest.mark.parametrize("world,N,Nk", [(2, 16, 7), (3, 10, 5), (3, 9, 4), (2, 2, 1)])
+def test_slab_decomposed_rfftn_and_piecewise_binning(world, N, Nk):
+    _run(_slab_fft_ranks, world, N, Nk)
