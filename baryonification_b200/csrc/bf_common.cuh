@@ -97,18 +97,35 @@ __device__ __forceinline__ void bf_logtab_init(double2 *tab, int t, int nthreads
     }
 }
 
+// Polynomial coefficients of the pair loops live in constant memory: an fp64 instruction takes a c[bank][offset]
+// operand directly, whereas a 64-bit literal costs two MOVs per use once the register budget is spent (the hot
+// loops run at 64 registers per thread, so ptxas rematerialises them every iteration).
+static __constant__ double bf_kc[8] = {-1.0 / 6.0, 0.2, 1.0 / 3.0, 0.693147180559945309417232121458, 0.375, 0.2734375,
+                                       -0.3125, 1e-3};
+
 __device__ __forceinline__ double bf_fastlog(const double2 *__restrict__ tab, double x) {
     const int hi = __double2hiint(x);
     const int e = (hi >> 20) - 1023;
     const double m = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(x));
     const double2 t = tab[(hi >> 13) & (BF_LOGTAB - 1)];
     const double r = fma(m, t.x, -1.0);
-    double p = fma(r, -1.0 / 6.0, 0.2);
+    double p = fma(r, bf_kc[0], bf_kc[1]);
     p = fma(r, p, -0.25);
-    p = fma(r, p, 1.0 / 3.0);
+    p = fma(r, p, bf_kc[2]);
     p = fma(r, p, -0.5);
     p = fma(r, p, 1.0);
-    return fma((double)e, 0.693147180559945309417232121458, fma(r, p, t.y));
+    return fma((double)e, bf_kc[3], fma(r, p, t.y));
+}
+
+// 1 / sqrt(x) for normal x > 0: the hardware seed (MUFU.RSQ64H, 2^-22) refined by one third-order step -- the
+// instruction sequence of the library rsqrt() without its special-case branch.  x = 0 gives NaN (inf seed), which
+// every caller turns into 0 like the reference's `offset[~isfinite(offset)] = 0`.
+__device__ __forceinline__ double bf_rsqrt(double x) {
+    double y0;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y0) : "d"(x));
+    const double e = fma(x, -(y0 * y0), 1.0);
+    const double p = fma(e, bf_kc[4], 0.5);
+    return fma(p, y0 * e, y0);
 }
 
 // value of one collapsed row at ln r = x; NaN outside the table (fill_value).  The two-product form

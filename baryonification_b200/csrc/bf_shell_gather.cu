@@ -87,9 +87,11 @@ template <int MODE>
 __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather_args A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     gather_smem &sm = *reinterpret_cast<gather_smem *>(smem_raw);
-    double *g_s = reinterpret_cast<double *>(smem_raw + sizeof(gather_smem));
-    double *ig_s = g_s + A.ax.nr;
-    double2 *logtab = reinterpret_cast<double2 *>((reinterpret_cast<uintptr_t>(ig_s + A.ax.nr) + 15) & ~(uintptr_t)15);
+    // dynamic shared memory after the struct: ln table [BF_LOGTAB] double2, then the radial axis as (g[k], 1 / (g[k+1] - g[k]))
+    // pairs so that one 16-byte load serves the lerp, then the plain axis for the (rare) exact search
+    double2 *logtab = reinterpret_cast<double2 *>(smem_raw + sizeof(gather_smem));
+    double2 *gi_s = logtab + BF_LOGTAB;
+    double *g_s = reinterpret_cast<double *>(gi_s + A.ax.nr);
 
     const bf_hpx &h = A.h;
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
@@ -121,11 +123,13 @@ __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather
     for (int k = t; k < A.ax.nr; k += GT_THREADS) g_s[k] = A.ax.g[k];
     bf_logtab_init(logtab, t, GT_THREADS);
     __syncthreads();
-    for (int k = t; k < A.ax.nr - 1; k += GT_THREADS) ig_s[k] = 1.0 / (g_s[k + 1] - g_s[k]);
+    for (int k = t; k < A.ax.nr; k += GT_THREADS)
+        gi_s[k] = make_double2(g_s[k], (k < A.ax.nr - 1) ? 1.0 / (g_s[k + 1] - g_s[k]) : 0.0);
+    const double tt_max = 1.0 - 0x1p-50;
     bf_raxis ax = A.ax;
     ax.g = g_s;
 
-    u64 my_pairs = 0;
+    unsigned my_pairs32 = 0;  // per lane and cell: far below 2^32
     for (int cb = beg; cb < end; cb += GT_CMAX) {
         const int nc = min(GT_CMAX, end - cb);
         __syncthreads();
@@ -186,8 +190,12 @@ __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather
                 __syncwarp();
                 int kw = 0;
                 unsigned hm = valid ? sm.hits[w][0][lane] : 0u;
+                my_pairs32 += __popc(hm);
                 for (;;) {
-                    while (hm == 0u && kw + 1 < nw) hm = valid ? sm.hits[w][++kw][lane] : (++kw, 0u);
+                    while (hm == 0u && kw + 1 < nw) {
+                        hm = valid ? sm.hits[w][++kw][lane] : (++kw, 0u);
+                        my_pairs32 += __popc(hm);
+                    }
                     const bool act = hm != 0u;
                     if (!__any_sync(0xffffffffu, act)) break;
                     if (act) {
@@ -198,14 +206,17 @@ __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather
                         double x = fma(0.5, bf_fastlog(logtab, d2), sm.lnDa[c]);
                         double val = nan("");
                         if (x >= ax.g0 && x <= ax.glast) {
-                            int k = (int)((x - ax.g0) * ax.inv_dx);  // uniform-grid guess, verified against the stored grid
+                            // uniform-grid guess; accepted when 0 <= tt < 1 - 2^-50, which PROVES g[k] <= x < g[k+1]
+                            // (tt >= 0 iff x >= g[k]; x >= g[k+1] would give tt >= 1 - 4 ulp), else the exact search
+                            int k = (int)((x - ax.g0) * ax.inv_dx);
                             k = max(0, min(k, ax.nr - 2));
-                            double gk = g_s[k];
-                            if (x < gk || (x >= g_s[k + 1] && k < ax.nr - 2)) {  // rounding at a node / non-uniform axis
+                            double2 gi = gi_s[k];
+                            double tt = (x - gi.x) * gi.y;
+                            if (!(tt >= 0.0 && tt < tt_max)) {  // rounding at a node / non-uniform axis / x == glast
                                 k = bf_find_cell(ax, x);
-                                gk = g_s[k];
+                                gi = gi_s[k];
+                                tt = (x - gi.x) * gi.y;
                             }
-                            double tt = (x - gk) * ig_s[k];
                             const double *row = sm.row[c];
                             val = fma(__ldg(row + k + 1), tt, __ldg(row + k) * (1.0 - tt));
                         }
@@ -214,17 +225,16 @@ __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather
                             acc0 += bf_finite(P) ? P : 0.0;
                         } else {
                             double dsp = (d2 < sm.cut2[c]) ? val : 0.0;  // BaryonCorrection.py:381-382
-                            double e = dsp * sm.aD[c] * rsqrt(d2);
+                            double e = dsp * sm.aD[c] * bf_rsqrt(d2);
                             if (!bf_finite(e)) e = 0.0;                   // HealpixRunner.py:323
                             double q = e * d2 * (1.0 + e);
-                            double gg = q * fma(q, fma(q, fma(q, 0.2734375, -0.3125), 0.375), -0.5);  // (1+q)^-1/2 - 1
-                            if (fabs(q) > 1e-3) gg = rsqrt(1.0 + q) - 1.0;  // pixel (almost) on the halo centre
+                            double gg = q * fma(q, fma(q, fma(q, bf_kc[5], bf_kc[6]), bf_kc[4]), -0.5);  // (1+q)^-1/2 - 1
+                            if (fabs(q) > bf_kc[7]) gg = rsqrt(1.0 + q) - 1.0;  // pixel (almost) on the halo centre
                             double ef = fma(e, gg, e);
                             acc0 += fma(v[0], gg, ef * dx);
                             acc1 += fma(v[1], gg, ef * dy);
                             acc2 += fma(v[2], gg, ef * dz);
                         }
-                        ++my_pairs;
                     }
                 }
                 if (valid) {
@@ -240,6 +250,7 @@ __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather
             }
         }
     }
+    u64 my_pairs = my_pairs32;
     for (int s = 16; s > 0; s >>= 1) my_pairs += __shfl_down_sync(0xffffffffu, my_pairs, s);
     if (lane == 0 && A.npairs && my_pairs) atomicAdd(A.npairs, my_pairs);
 }
@@ -293,7 +304,8 @@ extern "C" int bf_shell_gather(int64_t nside, int mode, const bf_shell_halos *S,
     A.pix_base = pix_base;
     A.accumulate = accumulate;
     A.npairs = npairs;
-    size_t smem = sizeof(gather_smem) + 2 * sizeof(double) * (size_t)T->nr + sizeof(double2) * BF_LOGTAB + 16;
+    static_assert(sizeof(gather_smem) % 16 == 0, "the ln table behind the struct must stay 16-byte aligned");
+    size_t smem = sizeof(gather_smem) + 3 * sizeof(double) * (size_t)T->nr + sizeof(double2) * BF_LOGTAB;
     BF_REQUIRE(smem <= 200 * 1024, "table r-axis too long for the shared-memory stage");
     unsigned grid = (unsigned)((band_hi - band_lo) * BF_MAX_COLS);
     if (mode == 0) {

@@ -41,6 +41,7 @@ single = bf.BaryonifySnapshot(scfg["catalog"], scfg["field"], scfg["epsilon_max"
 want = single.process()
 ss = sh.ShardedSnapshot(bf.BaryonifySnapshot(scfg["catalog"], scfg["field"], scfg["epsilon_max"], scfg["model"], verbose=False), device=local)
 got = ss.process()
+snap_want = want
 exact = all(np.array_equal(got[k], want[k]) for k in want.dtype.names)
 if rank == 0:
     print(f"BaryonifySnapshot: world {world} pairs {ss.npairs} (single {single.npairs}) bit-identical {exact}", flush=True)
@@ -71,12 +72,12 @@ for ngrd in (128, 250):
     sp = sh.ShardedPowerSpectrum(ngrd, scfg["field"].L, 60, device=local)
     one = PowerSpectrumGrid(ngrd, scfg["field"].L, 60, device=local)
     res = sp.suppression(B, D, factors=(1, 4))
-    ref = one.suppression(want, scfg["field"].cat, factors=(1, 4))
+    ref = one.suppression(snap_want, scfg["field"].cat, factors=(1, 4))
     torch.cuda.synchronize(); dist.barrier()
     t0 = time.perf_counter(); sp.power(B); torch.cuda.synchronize(); dt = time.perf_counter() - t0
-    t0 = time.perf_counter(); one.power(one.density(want)); torch.cuda.synchronize(); d1 = time.perf_counter() - t0
+    t0 = time.perf_counter(); one.power(one.density(snap_want)); torch.cuda.synchronize(); d1 = time.perf_counter() - t0
     k_s, P_s, n_s = sp.power(B)
-    k_1, P_1, n_1 = one.power(one.density(want))
+    k_1, P_1, n_1 = one.power(one.density(snap_want))
     good = np.array_equal(n_s, n_1)
     m = n_1 > 0
     errP = np.max(np.abs(P_s[m] / P_1[m] - 1))
