@@ -42,7 +42,9 @@ class ShellEngine:
         dev, s = self.dev, self.s
         self.table = dv.DeviceTable(self.host_table, dev=dev)
         keys = ("vec", "lon", "lat", "radius", "D", "a", "cut", "lnr_shift", "z_in", "M_in")
-        self.t = {k: dv.to_dev(s[k], dev=dev, pinned=pinned) for k in keys}
+        pins = s.get("_pinned") or {}  # page-locked outputs of the parallel host set-up: asynchronous copies
+        self.t = {k: pins[k].to(dev, non_blocking=True) if k in pins else dv.to_dev(s[k], dev=dev, pinned=pinned)
+                  for k in keys}
         self.t["extras"] = dv.to_dev(s["extras"], dev=dev) if s.get("extras") is not None else None  # p_keys columns
         self.rows = self.table.collapse(self.t["z_in"], self.t["M_in"], self.t["extras"])
         self.order = torch.argsort(self.t["radius"], descending=True) if self.variant == "atomic" else None

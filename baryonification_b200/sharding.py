@@ -246,7 +246,7 @@ def exchange_rows(buf, rows, below, above, group=None):
 # ----------------------------------------------------------------------------------------------------------
 def _subset(scalars, keep):
     return {k: (np.ascontiguousarray(v[keep]) if isinstance(v, np.ndarray) and v.shape[:1] == keep.shape else v)
-            for k, v in scalars.items()}
+            for k, v in scalars.items() if k != "_pinned"}  # (the page-locked slabs hold the WHOLE catalogue)
 
 
 class ShardedShell:
