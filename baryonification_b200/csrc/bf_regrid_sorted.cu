@@ -58,6 +58,22 @@ static sorted_ws sorted_layout(void *base, i64 nent, i64 nout) {
     return w;
 }
 
+// arrival order of one entry inside its destination (saturating u8; the flag sends the bucket pass to its cursor mode)
+__device__ __forceinline__ u8 take_rank(u32 k, u32 nout, int *__restrict__ count, int *__restrict__ overflow) {
+    if (k >= nout) return 0;  // sentinel: masked source
+    int r = atomicAdd(count + k, 1);
+    if (r > 255) { r = 255; *overflow = 1; }
+    return (u8)r;
+}
+
+// only when a bucket overflowed: the counters become the cursors of the bucket pass (decided on the device, so the
+// call never waits for the host)
+__global__ void __launch_bounds__(256) reset_if_overflow_kernel(const int *__restrict__ overflow, int *__restrict__ count,
+                                                                i64 n) {
+    if (*overflow == 0) return;
+    for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (i64)gridDim.x * blockDim.x) count[i] = 0;
+}
+
 __global__ void __launch_bounds__(256) rank_kernel(i64 n, const u32 *__restrict__ key, u32 nout, int *__restrict__ count,
                                                    u8 *__restrict__ rank, int *__restrict__ overflow) {
     i64 e = (i64)blockIdx.x * blockDim.x + threadIdx.x;
@@ -72,13 +88,14 @@ __global__ void __launch_bounds__(256) rank_kernel(i64 n, const u32 *__restrict_
 __global__ void __launch_bounds__(256) bucket_kernel(i64 n, const u32 *__restrict__ key, const double *__restrict__ val,
                                                      const u8 *__restrict__ rank, u32 nout,
                                                      const int *__restrict__ start, int *__restrict__ cursor,
-                                                     u32 *__restrict__ bid, double *__restrict__ bval) {
+                                                     const int *__restrict__ overflow, u32 *__restrict__ bid,
+                                                     double *__restrict__ bval) {
     i64 e = (i64)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= n) return;
     u32 k = key[e];
     if (k >= nout) return;
-    // cursor == NULL: the rank recorded by rank_kernel is the slot; otherwise (a bucket overflowed u8) take a fresh one
-    int slot = start[k] + (cursor ? atomicAdd(cursor + k, 1) : (int)rank[e]);
+    // normally the recorded rank is the slot; if a bucket overflowed u8, every entry takes a fresh one from the cursors
+    int slot = start[k] + (*overflow ? atomicAdd(cursor + k, 1) : (int)rank[e]);
     bid[slot] = (u32)e;
     bval[slot] = val[e];
 }
@@ -107,23 +124,26 @@ __global__ void __launch_bounds__(256) bucket_reduce_kernel(u32 nout, const int 
     out[d] += s;
 }
 
-static int sort_and_reduce(sorted_ws &w, i64 nent, u32 nout, double *out, cudaStream_t s) {
+// zero the counters and the flag; the emit kernels take the ranks themselves (`ranked`), saving a pass over the keys
+static int sort_prepare(sorted_ws &w, u32 nout, cudaStream_t s) {
     BF_CUDA_OK(cudaMemsetAsync(w.count, 0, sizeof(int) * ((size_t)nout + 2), s));
     BF_CUDA_OK(cudaMemsetAsync(w.overflow, 0, sizeof(int), s));
+    return BF_OK;
+}
+
+static int sort_and_reduce(sorted_ws &w, i64 nent, u32 nout, double *out, bool ranked, cudaStream_t s) {
     unsigned eb = (unsigned)((nent + 255) / 256);
-    rank_kernel<<<eb, 256, 0, s>>>(nent, w.key, nout, w.count, w.rank, w.overflow);
-    BF_LAUNCH_OK();
+    if (!ranked) {
+        int rc = sort_prepare(w, nout, s);
+        if (rc) return rc;
+        rank_kernel<<<eb, 256, 0, s>>>(nent, w.key, nout, w.count, w.rank, w.overflow);
+        BF_LAUNCH_OK();
+    }
     size_t cb = w.cub_bytes;
     BF_CUDA_OK(cub::DeviceScan::ExclusiveSum(w.cub_tmp, cb, w.count, w.start, (int)(nout + 1), s));
-    int overflow = 0;
-    BF_CUDA_OK(cudaMemcpyAsync(&overflow, w.overflow, sizeof(int), cudaMemcpyDeviceToHost, s));
-    BF_CUDA_OK(cudaStreamSynchronize(s));
-    int *cursor = nullptr;
-    if (overflow) {  // > 255 deposits into one destination: park with a cursor instead of the saturated rank
-        cursor = w.count;
-        BF_CUDA_OK(cudaMemsetAsync(w.count, 0, sizeof(int) * ((size_t)nout + 2), s));
-    }
-    bucket_kernel<<<eb, 256, 0, s>>>(nent, w.key, w.val, w.rank, nout, w.start, cursor, w.bid, w.bval);
+    reset_if_overflow_kernel<<<bf_sm_count() * 8, 256, 0, s>>>(w.overflow, w.count, (i64)nout + 2);
+    BF_LAUNCH_OK();
+    bucket_kernel<<<eb, 256, 0, s>>>(nent, w.key, w.val, w.rank, nout, w.start, w.count, w.overflow, w.bid, w.bval);
     BF_LAUNCH_OK();
     bucket_reduce_kernel<<<(nout + 255) / 256, 256, 0, s>>>(nout, w.start, w.bid, w.bval, out);
     BF_LAUNCH_OK();
@@ -136,7 +156,8 @@ static int sort_and_reduce(sorted_ws &w, i64 nent, u32 nout, double *out, cudaSt
 __global__ void __launch_bounds__(256) shell_emit_kernel(bf_hpx h, i64 pix_first, i64 pix_last,
                                                          const double *__restrict__ orig,
                                                          const double *__restrict__ off, u32 *__restrict__ key,
-                                                         double *__restrict__ val) {
+                                                         double *__restrict__ val, int *__restrict__ count,
+                                                         u8 *__restrict__ rank, int *__restrict__ overflow) {
     i64 q = (i64)blockIdx.x * blockDim.x + threadIdx.x;
     i64 p = pix_first + q;
     if (p >= pix_last) return;
@@ -157,6 +178,9 @@ __global__ void __launch_bounds__(256) shell_emit_kernel(bf_hpx h, i64 pix_first
 #pragma unroll
         for (int k = 0; k < 4; ++k) vv[k] = w[k] * m;
     }
+    const u32 nout = (u32)h.npix;
+    reinterpret_cast<uchar4 *>(rank)[q] = make_uchar4(take_rank(kk.x, nout, count, overflow), take_rank(kk.y, nout, count, overflow),
+                                                      take_rank(kk.z, nout, count, overflow), take_rank(kk.w, nout, count, overflow));
     reinterpret_cast<uint4 *>(key)[q] = kk;
     reinterpret_cast<double2 *>(val)[2 * q] = make_double2(vv[0], vv[1]);
     reinterpret_cast<double2 *>(val)[2 * q + 1] = make_double2(vv[2], vv[3]);
@@ -183,10 +207,12 @@ extern "C" int bf_shell_regrid_sorted(int64_t nside, int64_t pix_first, int64_t 
         return BF_E_WORKSPACE;
     }
     cudaStream_t s = (cudaStream_t)stream;
+    int rc = sort_prepare(w, (u32)h.npix, s);
+    if (rc) return rc;
     shell_emit_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(h, pix_first, pix_last, orig_map, pix_offsets, w.key,
-                                                                  w.val);
+                                                                  w.val, w.count, w.rank, w.overflow);
     BF_LAUNCH_OK();
-    return sort_and_reduce(w, 4 * n, (u32)h.npix, new_map, s);
+    return sort_and_reduce(w, 4 * n, (u32)h.npix, new_map, true, s);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -265,5 +291,5 @@ extern "C" int bf_grid_regrid_sorted(int dim, int64_t npix, const double *offset
     if (dim == 2) grid_emit_kernel<2><<<blocks, 256, 0, s>>>(npix, offsets, orig, w.key, w.val);
     else grid_emit_kernel<3><<<blocks, 256, 0, s>>>(npix, offsets, orig, w.key, w.val);
     BF_LAUNCH_OK();
-    return sort_and_reduce(w, nent, (u32)ncell, new_map, s);
+    return sort_and_reduce(w, nent, (u32)ncell, new_map, false, s);
 }

@@ -26,7 +26,7 @@
 #define GT_WARPS BF_BAND_RINGS
 #define GT_THREADS (32 * GT_WARPS)
 #ifndef GT_CMAX
-#define GT_CMAX 192
+#define GT_CMAX 128
 #endif
 #ifndef GT_MINBLOCKS
 #define GT_MINBLOCKS 4
@@ -204,28 +204,31 @@ __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather
                         double dx = v[0] - sm.c0[c], dy = v[1] - sm.c1[c], dz = v[2] - sm.c2[c];
                         double d2 = fma(dz, dz, fma(dy, dy, dx * dx));
                         double x = fma(0.5, bf_fastlog(logtab, d2), sm.lnDa[c]);
-                        double val = nan("");
-                        if (x >= ax.g0 && x <= ax.glast) {
-                            // uniform-grid guess; accepted when 0 <= tt < 1 - 2^-50, which PROVES g[k] <= x < g[k+1]
-                            // (tt >= 0 iff x >= g[k]; x >= g[k+1] would give tt >= 1 - 4 ulp), else the exact search
-                            int k = (int)((x - ax.g0) * ax.inv_dx);
-                            k = max(0, min(k, ax.nr - 2));
-                            double2 gi = gi_s[k];
-                            double tt = (x - gi.x) * gi.y;
-                            if (!(tt >= 0.0 && tt < tt_max)) {  // rounding at a node / non-uniform axis / x == glast
-                                k = bf_find_cell(ax, x);
-                                gi = gi_s[k];
-                                tt = (x - gi.x) * gi.y;
-                            }
-                            const double *row = sm.row[c];
-                            val = fma(__ldg(row + k + 1), tt, __ldg(row + k) * (1.0 - tt));
+                        // Table cell, branch-free up to the (rare) exact search, so that the two row loads are in
+                        // flight while the reciprocal square root and the cut are evaluated.  Uniform-grid guess,
+                        // accepted when 0 <= tt < 1 - 2^-50, which PROVES g[k] <= x < g[k+1] (tt >= 0 iff x >= g[k];
+                        // x >= g[k+1] would give tt >= 1 - 4 ulp); out of range (fill_value NaN) is decided by `inr`.
+                        const bool inr = x >= ax.g0 && x <= ax.glast;
+                        int k = (int)((x - ax.g0) * ax.inv_dx);
+                        k = max(0, min(k, ax.nr - 2));
+                        double2 gi = gi_s[k];
+                        double tt = (x - gi.x) * gi.y;
+                        if (inr && !(tt >= 0.0 && tt < tt_max)) {  // rounding at a node / non-uniform axis / x == glast
+                            k = bf_find_cell(ax, x);
+                            gi = gi_s[k];
+                            tt = (x - gi.x) * gi.y;
                         }
+                        const double *row = sm.row[c] + k;
+                        const double r0 = __ldg(row), r1 = __ldg(row + 1);
                         if (MODE == 0) {
-                            double P = exp(val);
+                            double val = fma(r1, tt, r0 * (1.0 - tt));
+                            double P = exp(inr ? val : nan(""));
                             acc0 += bf_finite(P) ? P : 0.0;
                         } else {
-                            double dsp = (d2 < sm.cut2[c]) ? val : 0.0;  // BaryonCorrection.py:381-382
-                            double e = dsp * sm.aD[c] * bf_rsqrt(d2);
+                            const double sc = sm.aD[c] * bf_rsqrt(d2);
+                            const bool use = inr && d2 < sm.cut2[c];  // NaN fill / BaryonCorrection.py:381-382: both end as 0
+                            double val = fma(r1, tt, r0 * (1.0 - tt));
+                            double e = (use ? val : 0.0) * sc;
                             if (!bf_finite(e)) e = 0.0;                   // HealpixRunner.py:323
                             double q = e * d2 * (1.0 + e);
                             double gg = q * fma(q, fma(q, fma(q, bf_kc[5], bf_kc[6]), bf_kc[4]), -0.5);  // (1+q)^-1/2 - 1

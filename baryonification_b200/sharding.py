@@ -160,26 +160,38 @@ def exchange_boundary(acc, ranges, group=None, window=None):
 
 
 def gather_slices(own, ranges, group=None, out=None):
-    """All ranks' slices -> the full array on every rank (slices have different lengths: padded all-gather)."""
+    """All ranks' slices -> the full array on every rank.  Slices have different lengths (whole ring bands), so this is
+    an all-gather-v: one batched group of point-to-point copies in which every rank sends its slice to every peer and
+    receives the peers' slices IN PLACE at ``out[a:b]`` -- no padding, no staging buffers, the only bytes moved are
+    the ones that cross the links.  ``own`` may already be ``out[ranges[rank]]`` (then nothing is copied locally)."""
     rank, world = _world(group)
     n = ranges[-1][1]
     if world == 1:
         return own
-    width = max(b - a for a, b in ranges)
     tail = own.shape[1:]
-    pad = torch.zeros((width,) + tuple(tail), dtype=own.dtype, device=own.device)
-    pad[:own.shape[0]] = own
-    parts = [torch.empty_like(pad) for _ in range(world)]
-    dist.all_gather(parts, pad, group=group)
     if out is None:
         out = torch.empty((n,) + tuple(tail), dtype=own.dtype, device=own.device)
-    for r, (a, b) in enumerate(ranges):
-        out[a:b] = parts[r][:b - a]
+    a, b = ranges[rank]
+    mine = out[a:b]
+    if b > a and mine.data_ptr() != own.data_ptr():
+        mine.copy_(own)
+    ops = []
+    peer = (lambda r: dist.get_global_rank(group, r)) if group is not None else (lambda r: r)
+    for r, (ra, rb) in enumerate(ranges):
+        if r == rank:
+            continue
+        if b > a:
+            ops.append(dist.P2POp(dist.isend, mine, peer(r), group=group))
+        if rb > ra:
+            ops.append(dist.P2POp(dist.irecv, out[ra:rb], peer(r), group=group))
+    if ops:
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
     return out
 
 
 # ----------------------------------------------------------------------------------------------------------
-# periodic grids: slabs of the first grid axis
+# grid slabs
 # ----------------------------------------------------------------------------------------------------------
 def halos_touching_rows(x, bins, Nsize, a_first, a_last):
     """Mask of the halos whose cut-out box (Map2DRunner.py:494-512: ``Nsize`` cells around ``argmin|bins - x|``,

@@ -252,6 +252,25 @@ def run_ours(args, rank, local_rank, world):
     ms = torch.tensor([t_a.elapsed_time(t_b) / args.steps, float(np.mean([a.elapsed_time(b) for a, b in acc_ms]))],
                       dtype=torch.float64, device=dev)
     pairs = torch.tensor([eng.pair_count()], dtype=torch.int64, device=dev)
+    if os.environ.get("BF_STEP_BREAKDOWN"):  # diagnostic: per-phase wall time with a device sync after every phase
+        ph = {}
+
+        def tick(name, t0):
+            torch.cuda.synchronize(dev)
+            ph[name] = ph.get(name, 0.0) + (time.perf_counter() - t0) * 1e3 / 3
+            return time.perf_counter()
+
+        for _ in range(3):
+            barrier()
+            t0 = time.perf_counter()
+            eng.recollapse(); t0 = tick("collapse", t0)
+            eng.bin(); t0 = tick("bin", t0)
+            eng.accumulate(off); t0 = tick("accumulate", t0)
+            eng.regrid(orig_d, off, new_d, method=args.regrid); t0 = tick("regrid", t0)
+            if world > 1:
+                own = sh.exchange_boundary(new_d, ranges, window=64 * 4 * nside); t0 = tick("exchange", t0)
+                sh.gather_slices(own, ranges, out=full_d); t0 = tick("gather", t0)
+        print(f"[rank {rank}] step phases (ms): " + ", ".join(f"{k} {v:.2f}" for k, v in ph.items()), file=sys.stderr, flush=True)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(pairs)

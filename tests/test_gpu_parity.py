@@ -435,6 +435,38 @@ def test_shell_regrid_sorted_equals_serial_order_sum(gpu):
     assert np.mean(got == want) > 0.5
 
 
+def test_shell_regrid_sorted_bucket_overflow_path(gpu):
+    """> 255 deposits into one destination (every pixel displaced onto the same point): the u8 ranks saturate, the
+    device-side flag switches the bucket pass to its cursors (no host round trip), and the sums are still the serial
+    entry-order sums -- bit-reproducible and equal to a host accumulation of the same deposits in (i, j) order."""
+    import torch
+    from baryonification_b200 import _device as dv, _lib
+    from oracle import healpix as ohp
+    nside = 16
+    npix = 12 * nside * nside
+    rng = np.random.default_rng(11)
+    orig = rng.lognormal(size=npix)
+    pv = np.stack(ohp.pix2vec(nside, np.arange(npix)), 1)
+    target = np.array([0.3, -0.5, np.sqrt(1 - 0.34)])
+    off = np.ascontiguousarray(target[None, :] - pv)  # every displaced vector is `target` (up to rounding)
+    od, fd = dv.to_dev(orig), dv.to_dev(off)
+    lib = _lib.load()
+    nb = lib.bf_shell_regrid_sorted_ws_bytes(nside, npix)
+    ws = torch.empty(nb, dtype=torch.uint8, device=od.device)
+    outs = []
+    for _ in range(2):
+        new = dv.zeros(npix)
+        _lib.call("bf_shell_regrid_sorted", nside, 0, npix, dv.ptr(od), dv.ptr(fd), dv.ptr(new), dv.ptr(ws), nb,
+                  dv.stream_ptr())
+        outs.append(new.cpu().numpy())
+    assert np.array_equal(outs[0], outs[1])
+    assert np.count_nonzero(outs[0]) <= 16 and abs(outs[0].sum() / orig.sum() - 1) < 1e-13
+    at = dv.zeros(npix)
+    _lib.call("bf_shell_regrid_range", nside, 0, npix, dv.ptr(od), dv.ptr(fd), dv.ptr(at), dv.stream_ptr())
+    at = at.cpu().numpy()
+    assert np.array_equal(at != 0, outs[0] != 0) and np.allclose(at, outs[0], rtol=1e-12, atol=0)
+
+
 @pytest.mark.parametrize("dim,npix", [(2, 128), (3, 32)])
 def test_grid_regrid_sorted_matches_atomic_and_oracle(gpu, dim, npix):
     import baryonification_b200 as bf
