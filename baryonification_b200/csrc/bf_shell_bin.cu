@@ -2,9 +2,9 @@
 //
 // For every halo the exact query_disc ring walk (HealpixRunner.py:306 / :432 semantics, bf_healpix.cuh) is
 // run once per ring by one lane; the columns its pixel segments touch are OR-ed over the 8 rings of a band
-// into a 64-bit mask, and one (cell, halo) key is emitted per set bit.  Keys are placed with a per-halo
-// exclusive scan (no atomics -> deterministic layout), radix-sorted by (cell, halo) with CUB, and cell
-// boundaries are marked.  After this, cell c's halos are keys[cell_begin[c] .. cell_end[c]) in catalogue
+// into a 64-bit mask, and one (cell, halo) key is emitted per set bit.  Keys are unique; they are written in ONE
+// pass at blocks taken from a cursor, then radix-sorted by (cell, halo) with CUB (which makes the layout
+// deterministic whatever order the blocks were taken in), and cell boundaries are marked.  After this, cell c's halos are keys[cell_begin[c] .. cell_end[c]) in catalogue
 // order -- the order in which the reference's serial loop would have touched those pixels.
 #include <cub/cub.cuh>
 
@@ -25,17 +25,18 @@ __device__ __forceinline__ u64 seg_mask(int s, int e, int wc) {  // columns touc
     return hi & ~((1ull << c0) - 1ull);
 }
 
-// FILL = false: counts[j] = number of (cell, halo) entries of halo j (0 for "tiny" halos in baryonify mode,
-// which are appended to tiny_list instead).  FILL = true: write the keys at offsets[j].
-template <bool FILL>
+// One pass: every halo's keys go to a block of the key array taken from a global cursor (one atomic per 32 rings).
+// Where a block lands depends on scheduling, but the keys are unique and are radix-sorted next, so the result does
+// not.  Blocks that would pass `max_entries` are counted but not written: the caller learns the exact size from the
+// cursor and comes back with a larger workspace.  "Tiny" halos (baryonify mode, < 4 pixel centres in the disc,
+// HealpixRunner.py:309-310) emit no keys and are appended to tiny_list instead.
 __global__ void __launch_bounds__(128) bin_kernel(bf_hpx h, bf_cells cg, int mode, bf_shell_halos S, i64 band_lo,
-                                                  i64 band_hi, double resol, i64 *__restrict__ counts,
-                                                  const i64 *__restrict__ offsets, u64 *__restrict__ keys,
+                                                  i64 band_hi, double resol, i64 max_entries,
+                                                  unsigned long long *__restrict__ cursor, u64 *__restrict__ keys,
                                                   int *__restrict__ tiny_list, int *__restrict__ tiny_count) {
     i64 j = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     int lane = threadIdx.x & 31;
     if (j >= S.nh) return;
-    if (FILL && counts[j] == 0) return;
     double v[3] = {S.vec[3 * j], S.vec[3 * j + 1], S.vec[3 * j + 2]};
     double radius = S.radius[j];
     bf_disc d = bfh_disc_setup(h, v, radius);
@@ -44,7 +45,7 @@ __global__ void __launch_bounds__(128) bin_kernel(bf_hpx h, bf_cells cg, int mod
     if (ring_lo < 1) ring_lo = 1;
     if (ring_hi > 4 * h.nside - 1) ring_hi = 4 * h.nside - 1;
 
-    if (!FILL && mode == 1 && radius < 3.0 * resol) {  // HealpixRunner.py:309-310 candidates
+    if (mode == 1 && radius < 3.0 * resol) {  // HealpixRunner.py:309-310 candidates
         i64 cnt = 0;
         for (i64 iz = ring_lo + lane; iz <= ring_hi; iz += 32) {
             i64 nr; int s0, e0, s1, e1;
@@ -52,7 +53,7 @@ __global__ void __launch_bounds__(128) bin_kernel(bf_hpx h, bf_cells cg, int mod
         }
         for (int s = 16; s > 0; s >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, s);
         if (cnt < 4) {
-            if (lane == 0) { counts[j] = 0; tiny_list[atomicAdd(tiny_count, 1)] = (int)j; }
+            if (lane == 0) tiny_list[atomicAdd(tiny_count, 1)] = (int)j;
             return;
         }
     }
@@ -60,8 +61,6 @@ __global__ void __launch_bounds__(128) bin_kernel(bf_hpx h, bf_cells cg, int mod
     i64 b_first = (ring_lo - 1) / BF_BAND_RINGS, b_last = (ring_hi - 1) / BF_BAND_RINGS;
     if (b_first < band_lo) b_first = band_lo;
     if (b_last > band_hi - 1) b_last = band_hi - 1;
-    i64 total = 0;
-    i64 base = FILL ? offsets[j] : 0;
     for (i64 b0 = b_first; b0 <= b_last; b0 += 4) {  // 4 bands = 32 rings per pass, one ring per lane
         i64 band = b0 + (lane >> 3);
         i64 iz = band * BF_BAND_RINGS + 1 + (lane & 7);
@@ -77,18 +76,21 @@ __global__ void __launch_bounds__(128) bin_kernel(bf_hpx h, bf_cells cg, int mod
         // exclusive prefix of the 4 band counts (lanes 0, 8, 16, 24)
         int c0 = __shfl_sync(0xffffffffu, c, 0), c1 = __shfl_sync(0xffffffffu, c, 8);
         int c2 = __shfl_sync(0xffffffffu, c, 16), c3 = __shfl_sync(0xffffffffu, c, 24);
-        if (FILL && (lane & 7) == 0 && c > 0) {
+        const int tot = c0 + c1 + c2 + c3;
+        if (tot == 0) continue;
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(cursor, (unsigned long long)tot);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if ((i64)base + tot <= max_entries && (lane & 7) == 0 && c > 0) {
             int g = lane >> 3;
-            i64 o = base + total + ((g > 0) ? c0 : 0) + ((g > 1) ? c1 : 0) + ((g > 2) ? c2 : 0);
+            i64 o = (i64)base + ((g > 0) ? c0 : 0) + ((g > 1) ? c1 : 0) + ((g > 2) ? c2 : 0);
             while (m) {
                 int col = __ffsll((long long)m) - 1;
                 m &= m - 1;
                 keys[o++] = ((u64)(band * BF_MAX_COLS + col) << 32) | (u64)j;
             }
         }
-        total += c0 + c1 + c2 + c3;
     }
-    if (!FILL && lane == 0) counts[j] = total;
 }
 
 __global__ void cell_bounds_kernel(i64 n, const u64 *__restrict__ keys, int *__restrict__ cell_begin,
@@ -145,17 +147,16 @@ extern "C" int bf_shell_bin_halos(int64_t nside, int mode, const bf_shell_halos 
     BF_CUDA_OK(cudaMemsetAsync(w.cell_begin, 0, sizeof(int) * (size_t)w.ncells, s));
     BF_CUDA_OK(cudaMemsetAsync(w.cell_end, 0, sizeof(int) * (size_t)w.ncells, s));
     BF_CUDA_OK(cudaMemsetAsync(w.tiny_count, 0, sizeof(int), s));
-    BF_CUDA_OK(cudaMemsetAsync(w.counts, 0, sizeof(i64) * (size_t)(S->nh + 1), s));
+    unsigned long long *cursor = (unsigned long long *)w.counts;  // counts[0] holds the key cursor
+    BF_CUDA_OK(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), s));
     *nentries_host = 0;
     if (S->nh == 0) return BF_OK;
     unsigned blocks = (unsigned)((S->nh * 32 + 127) / 128);
-    bin_kernel<false><<<blocks, 128, 0, s>>>(h, cg, mode, *S, band_lo, band_hi, resol, w.counts, nullptr, nullptr,
-                                             w.tiny_list, w.tiny_count);
+    bin_kernel<<<blocks, 128, 0, s>>>(h, cg, mode, *S, band_lo, band_hi, resol, max_entries, cursor, w.keys, w.tiny_list,
+                                      w.tiny_count);
     BF_LAUNCH_OK();
-    size_t cb = w.cub_bytes;
-    BF_CUDA_OK(cub::DeviceScan::ExclusiveSum(w.cub_tmp, cb, w.counts, w.offsets, (int)(S->nh + 1), s));
     i64 total = 0;
-    BF_CUDA_OK(cudaMemcpyAsync(&total, w.offsets + S->nh, sizeof(i64), cudaMemcpyDeviceToHost, s));
+    BF_CUDA_OK(cudaMemcpyAsync(&total, cursor, sizeof(i64), cudaMemcpyDeviceToHost, s));
     BF_CUDA_OK(cudaStreamSynchronize(s));
     *nentries_host = total;
     if (total > max_entries) {
@@ -163,13 +164,10 @@ extern "C" int bf_shell_bin_halos(int64_t nside, int mode, const bf_shell_halos 
         return BF_E_WORKSPACE;
     }
     if (total == 0) return BF_OK;
-    bin_kernel<true><<<blocks, 128, 0, s>>>(h, cg, mode, *S, band_lo, band_hi, resol, w.counts, w.offsets, w.keys,
-                                            w.tiny_list, w.tiny_count);
-    BF_LAUNCH_OK();
     int cell_bits = 1;
     while (((i64)1 << cell_bits) < w.ncells) ++cell_bits;
     cub::DoubleBuffer<u64> db(w.keys, w.keys_alt);
-    cb = w.cub_bytes;
+    size_t cb = w.cub_bytes;
     BF_CUDA_OK(cub::DeviceRadixSort::SortKeys(w.cub_tmp, cb, db, (int)total, 0, 32 + cell_bits, s));
     if (db.Current() != w.keys)
         BF_CUDA_OK(cudaMemcpyAsync(w.keys, db.Current(), sizeof(u64) * (size_t)total, cudaMemcpyDeviceToDevice, s));
