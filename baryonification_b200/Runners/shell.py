@@ -23,7 +23,7 @@ __all__ = ["DefaultRunner", "BaryonifyShell", "PaintProfilesShell"]
 
 class DefaultRunner:
     def __init__(self, HaloLightConeCatalog, LightconeShell, epsilon_max, model, use_ellipticity=False,
-                 mass_def=None, verbose=True, *, device=None, variant="gather", regrid="sorted", pinned_output=True):
+                 mass_def=None, verbose=True, *, device=None, variant="gather", regrid="gather", pinned_output=True):
         self.HaloLightConeCatalog = HaloLightConeCatalog
         self.LightconeShell = LightconeShell
         self.cosmo = HaloLightConeCatalog.cosmology
@@ -34,7 +34,7 @@ class DefaultRunner:
         self.use_ellipticity = use_ellipticity
         self.device = device
         self.variant = variant          # pair stage: "gather" (deterministic, default) | "atomic"
-        self.regrid = regrid            # re-binning: "sorted" (deterministic, default) | "atomic"
+        self.regrid = regrid            # re-binning: "gather" (deterministic, default; falls back to "sorted") | "sorted" | "atomic"
         self.pinned_output = pinned_output
         # opt-in (pipeline_chunks > 1): catalogues of at least `pipeline_min_halos` are cut into runs of consecutive halos
         # and the host set-up of run k+1 overlaps the GPU stages of run k (sums continue on the device in catalogue
@@ -172,6 +172,7 @@ class BaryonifyShell(DefaultRunner):
             t0 = time.perf_counter()
             orig_d = (box.get("up") or dv.AsyncUpload(orig, dev)).result()
             new_d = self._eng.regrid(orig_d, off, method=self.regrid)
+            self.regrid_used = self._eng.regrid_used
             self._eng = None
             new_sum_d, old_sum_d = new_d.sum(), orig_d.sum()  # the reference's two np.sum's, on the device
             t0 = self._tick("regrid", t0, dev)

@@ -210,10 +210,11 @@ __device__ __forceinline__ void bfh_ang2vec_lonlat(double lon, double lat, doubl
 }
 
 // get_interpol(pointing(theta, phi)) with phi already normalised to [0, 2pi)
-__device__ __forceinline__ void bfh_get_interpol(const bf_hpx &h, double theta, double phi, i64 pix[4],
-                                                 double wgt[4]) {
+// (ir1 = ring above the point, 0 at the north pole: pix[0..1] lie on ring max(ir1, 1), pix[2..3] on min(ir1 + 1, 4N - 1))
+__device__ __forceinline__ void bfh_get_interpol_r(const bf_hpx &h, double theta, double phi, i64 pix[4],
+                                                   double wgt[4], i64 &ir1) {
     double z = cos(theta);
-    i64 ir1 = bfh_ring_above(h, z);
+    ir1 = bfh_ring_above(h, z);
     i64 ir2 = ir1 + 1;
     double theta1 = 0, theta2 = 0, w1, tmp, dphi;
     i64 sp, nr, i1, i2;
@@ -263,11 +264,44 @@ __device__ __forceinline__ void bfh_get_interpol(const bf_hpx &h, double theta, 
     }
 }
 
-__device__ __forceinline__ void bfh_interp_lonlat(const bf_hpx &h, double lon, double lat, i64 pix[4],
-                                                  double wgt[4]) {
+__device__ __forceinline__ void bfh_get_interpol(const bf_hpx &h, double theta, double phi, i64 pix[4],
+                                                 double wgt[4]) {
+    i64 ir1;
+    bfh_get_interpol_r(h, theta, phi, pix, wgt, ir1);
+}
+
+__device__ __forceinline__ void bfh_interp_lonlat_r(const bf_hpx &h, double lon, double lat, i64 pix[4],
+                                                    double wgt[4], i64 &ir1) {
     double theta = BFH_PI / 2.0 - lat * BFH_DEG2RAD;
     double phi = bfh_fmodulo(lon * BFH_DEG2RAD, BFH_TWOPI);
-    bfh_get_interpol(h, theta, phi, pix, wgt);
+    bfh_get_interpol_r(h, theta, phi, pix, wgt, ir1);
+}
+
+__device__ __forceinline__ void bfh_interp_lonlat(const bf_hpx &h, double lon, double lat, i64 pix[4],
+                                                  double wgt[4]) {
+    i64 ir1;
+    bfh_interp_lonlat_r(h, lon, lat, pix, wgt, ir1);
+}
+
+// The 4 deposits of one displaced pixel (HealpixRunner.py:333-341): new_vec = pix2vec(p) + offsets[p] ->
+// vec2ang(lonlat=True) in DEGREES -> get_interp_weights(lonlat=True).  One definition for every re-binning variant,
+// so that their deposits are the same bits.
+__device__ __forceinline__ void bfh_displaced_deposits_r(const bf_hpx &h, i64 p, const double off[3], i64 cp[4],
+                                                         double w[4], i64 &ir1) {
+    double v[3];
+    bfh_pix2vec(h, p, v);
+    double x = v[0] + off[0], y = v[1] + off[1], z = v[2] + off[2];
+    double dnorm = sqrt(x * x + y * y + z * z);
+    double theta = acos(z / dnorm);
+    double phi = atan2(y, x);
+    if (phi < 0) phi += BFH_TWOPI;
+    bfh_interp_lonlat_r(h, phi * BFH_RAD2DEG, 90.0 - theta * BFH_RAD2DEG, cp, w, ir1);
+}
+
+__device__ __forceinline__ void bfh_displaced_deposits(const bf_hpx &h, i64 p, const double off[3], i64 cp[4],
+                                                       double w[4]) {
+    i64 ir1;
+    bfh_displaced_deposits_r(h, p, off, cp, w, ir1);
 }
 
 // ------------------------------------------------------------------------------------------

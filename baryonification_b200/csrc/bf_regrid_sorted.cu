@@ -165,15 +165,9 @@ __global__ void __launch_bounds__(256) shell_emit_kernel(bf_hpx h, i64 pix_first
     uint4 kk = make_uint4((u32)h.npix, (u32)h.npix, (u32)h.npix, (u32)h.npix);
     double vv[4] = {0.0, 0.0, 0.0, 0.0};
     if (m > 0) {  // :335
-        double v[3];
-        bfh_pix2vec(h, p, v);
-        double x = v[0] + off[3 * q], y = v[1] + off[3 * q + 1], z = v[2] + off[3 * q + 2];
-        double dnorm = sqrt(x * x + y * y + z * z);
-        double theta = acos(z / dnorm);
-        double phi = atan2(y, x);
-        if (phi < 0) phi += BFH_TWOPI;
+        const double o3[3] = {off[3 * q], off[3 * q + 1], off[3 * q + 2]};
         i64 cp[4]; double w[4];
-        bfh_interp_lonlat(h, phi * BFH_RAD2DEG, 90.0 - theta * BFH_RAD2DEG, cp, w);
+        bfh_displaced_deposits(h, p, o3, cp, w);
         kk = make_uint4((u32)cp[0], (u32)cp[1], (u32)cp[2], (u32)cp[3]);
 #pragma unroll
         for (int k = 0; k < 4; ++k) vv[k] = w[k] * m;

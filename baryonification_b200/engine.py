@@ -117,22 +117,41 @@ class ShellEngine:
         return self.npairs
 
     # ---- stage 3 (baryonify): re-binning ------------------------------------------------------------
-    def regrid(self, orig_d, off, new_d=None, method="sorted"):
-        """orig_d / off are the engine's pixel slice; new_d is the full sphere.  method "sorted" = deterministic
-        sort-by-destination + in-order segmented sum (the reference's summation order); "atomic" = fp64 RED.ADD."""
+    def regrid(self, orig_d, off, new_d=None, method="gather"):
+        """orig_d / off are the engine's pixel slice; new_d is the full sphere.  "gather" = deterministic destination
+        gather (whole sphere only; a pixel slice, or a displacement window that is too wide, takes "sorted");
+        "sorted" = deterministic counting sort by destination + in-order segmented sum; both give the reference's
+        summation order and the same bits.  "atomic" = fp64 RED.ADD.  ``self.regrid_used`` names what ran."""
         if new_d is None:
             new_d = dv.zeros(self.npix, dev=self.dev)
         else:
             new_d.zero_()
-        if method == "sorted":
+        if method not in ("gather", "sorted", "atomic"):
+            raise ValueError(f"unknown regrid method {method!r}")
+        whole = self.pix_first == 0 and self.pix_last == self.npix
+        if method == "gather" and whole:
+            need = self.lib.bf_shell_regrid_gather_ws_bytes(self.nside)
+            if getattr(self, "_rg_ws", None) is None or self._rg_ws.numel() < need:
+                self._rg_ws = None
+                self._rg_ws = torch.empty(need, dtype=torch.uint8, device=self.dev)
+            win = (C.c_int * 3)()
+            rc = self.lib.bf_shell_regrid_gather(self.nside, dv.ptr(orig_d), dv.ptr(off), dv.ptr(new_d),
+                                                 dv.ptr(self._rg_ws), self._rg_ws.numel(), win, dv.stream_ptr())
+            self.regrid_window = tuple(win)
+            if rc != -3:  # BF_E_WINDOW: displacements span too many pixels for the gather -> counting sort
+                _lib.check(rc, "bf_shell_regrid_gather")
+                self.regrid_used = "gather"
+                return new_d
+        if method in ("gather", "sorted"):
             need = self.lib.bf_shell_regrid_sorted_ws_bytes(self.nside, self.pix_last - self.pix_first)
             if getattr(self, "_rg_ws", None) is None or self._rg_ws.numel() < need:
+                self._rg_ws = None
                 self._rg_ws = torch.empty(need, dtype=torch.uint8, device=self.dev)
             _lib.call("bf_shell_regrid_sorted", self.nside, self.pix_first, self.pix_last, dv.ptr(orig_d), dv.ptr(off),
                       dv.ptr(new_d), dv.ptr(self._rg_ws), self._rg_ws.numel(), dv.stream_ptr())
-        elif method == "atomic":
+            self.regrid_used = "sorted"
+        else:
             _lib.call("bf_shell_regrid_range", self.nside, self.pix_first, self.pix_last, dv.ptr(orig_d), dv.ptr(off),
                       dv.ptr(new_d), dv.stream_ptr())
-        else:
-            raise ValueError(f"unknown regrid method {method!r}")
+            self.regrid_used = "atomic"
         return new_d

@@ -26,7 +26,7 @@ extern "C" {
 #define BF_OK 0
 #define BF_E_INVALID (-1)   /* bad argument */
 #define BF_E_WORKSPACE (-2) /* workspace too small */
-#define BF_E_WINDOW (-3)    /* bf_grid_regrid_gather: displacement window too wide, use bf_grid_regrid_sorted */
+#define BF_E_WINDOW (-3)    /* bf_{grid,shell}_regrid_gather: displacement window too wide, use the _sorted variant */
 
 const char *bf_last_error(void);
 int bf_version(void);
@@ -137,6 +137,19 @@ int bf_shell_regrid_range(int64_t nside, int64_t pix_first, int64_t pix_last, co
 size_t bf_shell_regrid_sorted_ws_bytes(int64_t nside, int64_t npix_local);
 int bf_shell_regrid_sorted(int64_t nside, int64_t pix_first, int64_t pix_last, const double *orig_map,
                            const double *pix_offsets, double *new_map, void *ws, size_t ws_bytes, void *stream);
+/* The same sums (same deposits, same ascending (source, j) order: bit-identical to bf_shell_regrid_sorted) as a
+ * DESTINATION GATHER over the whole sphere: displaced mass lands next to its source, so a first pass writes every
+ * pixel's 4 deposits and measures the field's window (range of ring(destination) - ring(source); largest in-ring
+ * distance between a source and its destination's projection on the source ring), and every destination then scans the
+ * sources inside that window.  No sort, no atomics on the map, 48 B of workspace per pixel.  Destinations within
+ * BF_SHELL_GATHER_POLAR rings of a pole scan whole source rings.  window_host[3] (may be NULL) receives
+ * (dr_min, dr_max, dj_max).  BF_E_WINDOW when a destination would have to scan more than BF_SHELL_GATHER_MAX_WINDOW
+ * sources (fall back to bf_shell_regrid_sorted).  new_map is += (zero it first).  Synchronises `stream` once. */
+#define BF_SHELL_GATHER_POLAR 8
+#define BF_SHELL_GATHER_MAX_WINDOW 165
+size_t bf_shell_regrid_gather_ws_bytes(int64_t nside);
+int bf_shell_regrid_gather(int64_t nside, const double *orig_map, const double *pix_offsets, double *new_map, void *ws,
+                           size_t ws_bytes, int *window_host, void *stream);
 
 /* ---- Grid runners (Map2DRunner.py) ---- */
 typedef struct {

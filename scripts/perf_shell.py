@@ -34,8 +34,10 @@ for var in variants:
     line = f"{var:7s} upload {t_up:8.2f} ms  bin {t_bin:8.2f} ms (entries {eng.nentries})  accumulate {t_acc0:9.2f}/{t_acc:9.2f}/{t_acc2:9.2f} ms  pairs {npairs:.4e}  -> {npairs/t_acc2*1e-6:9.2f} Gpairs/s"
     if m:
         new, t_rg = ev(lambda: eng.regrid(orig, out))
-        new, t_rg = ev(lambda: eng.regrid(orig, out, new))
-        line += f"  regrid {t_rg:8.2f} ms  mass err {abs(new.sum().item()/orig.sum().item()-1):.2e}"
+        for meth in ("gather", "sorted", "atomic"):
+            new, t_rg = ev(lambda: eng.regrid(orig, out, new, method=meth))
+            line += f"  regrid[{eng.regrid_used}] {t_rg:8.2f} ms"
+        line += f" window {getattr(eng, 'regrid_window', None)} mass err {abs(new.sum().item()/orig.sum().item()-1):.2e}"
     print(line, flush=True)
     res[var] = out.clone()
 if len(res) == 2:

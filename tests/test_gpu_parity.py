@@ -435,6 +435,65 @@ def test_shell_regrid_sorted_equals_serial_order_sum(gpu):
     assert np.mean(got == want) > 0.5
 
 
+def _shell_regrid(kind, nside, orig, off):
+    import ctypes as C
+    import torch
+    from baryonification_b200 import _device as dv, _lib
+    lib = _lib.load(require_cuda=True)
+    npix = 12 * nside * nside
+    od, fd, new = dv.to_dev(orig), dv.to_dev(off), dv.zeros(npix)
+    win = (C.c_int * 3)()
+    if kind == "gather":
+        nb = lib.bf_shell_regrid_gather_ws_bytes(nside)
+        ws = torch.empty(nb, dtype=torch.uint8, device=od.device)
+        rc = lib.bf_shell_regrid_gather(nside, dv.ptr(od), dv.ptr(fd), dv.ptr(new), dv.ptr(ws), nb, win, dv.stream_ptr())
+    else:
+        nb = lib.bf_shell_regrid_sorted_ws_bytes(nside, npix)
+        ws = torch.empty(nb, dtype=torch.uint8, device=od.device)
+        rc = lib.bf_shell_regrid_sorted(nside, 0, npix, dv.ptr(od), dv.ptr(fd), dv.ptr(new), dv.ptr(ws), nb, dv.stream_ptr())
+    return rc, new.cpu().numpy(), tuple(win)
+
+
+@pytest.mark.parametrize("nside,amp", [(1, 0.3), (2, 0.2), (4, 0.05), (16, 0.01), (16, 0.1), (64, 0.002), (64, 0.03),
+                                       (256, 0.0005), (256, 0.004)])
+def test_shell_regrid_gather_is_bit_identical_to_the_sorted_serial_order_sum(gpu, nside, amp):
+    """Destination gather == counting sort bit for bit (same deposits, same ascending (source, j) order), from
+    sub-pixel to many-pixel displacements, with masked pixels, on rings of every kind (caps, belt, poles)."""
+    npix = 12 * nside * nside
+    rng = np.random.default_rng(nside)
+    orig = rng.lognormal(size=npix)
+    orig[rng.random(npix) < 0.2] = 0.0
+    off = rng.normal(scale=amp, size=(npix, 3))
+    off[rng.random(npix) < 0.1] = 0.0
+    rc_s, want, _ = _shell_regrid("sorted", nside, orig, off)
+    rc_g, got, win = _shell_regrid("gather", nside, orig, off)
+    assert rc_s == 0
+    if rc_g == -3:  # BF_E_WINDOW: too wide for the gather at this amplitude; the runner then takes the sorted variant
+        assert (win[1] - win[0] + 1) * (2 * win[2] + 1) > 165
+        return
+    assert rc_g == 0
+    assert np.array_equal(got, want), (win, np.max(np.abs(got - want)))
+    assert abs(got.sum() / orig.sum() - 1) < 1e-12
+
+
+def test_shell_regrid_gather_window_fallback_and_runner_default(gpu):
+    import baryonification_b200 as bf
+    from baryonification_b200 import synthetic as syn
+    nside = 32
+    npix = 12 * nside * nside
+    rng = np.random.default_rng(5)
+    rc, _, win = _shell_regrid("gather", nside, np.ones(npix), rng.normal(scale=0.5, size=(npix, 3)))
+    assert rc == -3 and (win[1] - win[0] + 1) * (2 * win[2] + 1) > 165
+    rc, out, win = _shell_regrid("gather", nside, np.zeros(npix), np.zeros((npix, 3)))  # nothing to deposit
+    assert rc == 0 and not out.any()
+    cfg = syn.config_shell(nside=64, nhalo=400)
+    g = bf.BaryonifyShell(cfg["catalog"], cfg["field"], 20.0, cfg["model"], verbose=False)  # default: gather
+    a = g.process()
+    assert g.regrid_used == "gather"
+    s = bf.BaryonifyShell(cfg["catalog"], cfg["field"], 20.0, cfg["model"], verbose=False, regrid="sorted")
+    assert np.array_equal(a, s.process()) and s.regrid_used == "sorted"
+
+
 def test_shell_regrid_sorted_bucket_overflow_path(gpu):
     """> 255 deposits into one destination (every pixel displaced onto the same point): the u8 ranks saturate, the
     device-side flag switches the bucket pass to its cursors (no host round trip), and the sums are still the serial
