@@ -83,6 +83,50 @@ __device__ __forceinline__ unsigned warp_transpose32(unsigned x, int lane) {
     return x;
 }
 
+// One (pixel, candidate) pair: contribution to the pixel's sum (paint: p[0]; baryonify: the unit-vector shift p[0..2]).
+template <int MODE>
+__device__ __forceinline__ void gather_pair(const gather_smem &sm, int c, const double v[3], const bf_raxis &ax,
+                                            const double2 *__restrict__ gi_s, const double2 *__restrict__ logtab,
+                                            double tt_max, double p[3]) {
+    double dx = v[0] - sm.c0[c], dy = v[1] - sm.c1[c], dz = v[2] - sm.c2[c];
+    double d2 = fma(dz, dz, fma(dy, dy, dx * dx));
+    double x = fma(0.5, bf_fastlog(logtab, d2), sm.lnDa[c]);
+    // Table cell, branch-free up to the (rare) exact search, so that the two row loads are in flight while the
+    // reciprocal square root and the cut are evaluated.  Uniform-grid guess, accepted when 0 <= tt < 1 - 2^-50, which
+    // PROVES g[k] <= x < g[k+1] (tt >= 0 iff x >= g[k]; x >= g[k+1] would give tt >= 1 - 4 ulp); out of range
+    // (fill_value NaN) is decided by `inr`.
+    const bool inr = x >= ax.g0 && x <= ax.glast;
+    int k = (int)((x - ax.g0) * ax.inv_dx);
+    k = max(0, min(k, ax.nr - 2));
+    double2 gi = gi_s[k];
+    double tt = (x - gi.x) * gi.y;
+    if (inr && !(tt >= 0.0 && tt < tt_max)) {  // rounding at a node / non-uniform axis / x == glast
+        k = bf_find_cell(ax, x);
+        gi = gi_s[k];
+        tt = (x - gi.x) * gi.y;
+    }
+    const double *row = sm.row[c] + k;
+    const double r0 = __ldg(row), r1 = __ldg(row + 1);
+    if (MODE == 0) {
+        double val = fma(r1, tt, r0 * (1.0 - tt));
+        double P = exp(inr ? val : nan(""));
+        p[0] = bf_finite(P) ? P : 0.0;
+    } else {
+        const double sc = sm.aD[c] * bf_rsqrt(d2);
+        const bool use = inr && d2 < sm.cut2[c];  // NaN fill / BaryonCorrection.py:381-382: both end as 0
+        double val = fma(r1, tt, r0 * (1.0 - tt));
+        double e = (use ? val : 0.0) * sc;
+        if (!bf_finite(e)) e = 0.0;                   // HealpixRunner.py:323
+        double q = e * d2 * (1.0 + e);
+        double gg = q * fma(q, fma(q, fma(q, bf_kc[5], bf_kc[6]), bf_kc[4]), -0.5);  // (1+q)^-1/2 - 1
+        if (fabs(q) > bf_kc[7]) gg = rsqrt(1.0 + q) - 1.0;  // pixel (almost) on the halo centre
+        double ef = fma(e, gg, e);
+        p[0] = fma(v[0], gg, ef * dx);
+        p[1] = fma(v[1], gg, ef * dy);
+        p[2] = fma(v[2], gg, ef * dz);
+    }
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather_args A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -201,43 +245,10 @@ __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather
                     if (act) {
                         const int c = kw * 32 + __ffs((int)hm) - 1;
                         hm &= hm - 1u;
-                        double dx = v[0] - sm.c0[c], dy = v[1] - sm.c1[c], dz = v[2] - sm.c2[c];
-                        double d2 = fma(dz, dz, fma(dy, dy, dx * dx));
-                        double x = fma(0.5, bf_fastlog(logtab, d2), sm.lnDa[c]);
-                        // Table cell, branch-free up to the (rare) exact search, so that the two row loads are in
-                        // flight while the reciprocal square root and the cut are evaluated.  Uniform-grid guess,
-                        // accepted when 0 <= tt < 1 - 2^-50, which PROVES g[k] <= x < g[k+1] (tt >= 0 iff x >= g[k];
-                        // x >= g[k+1] would give tt >= 1 - 4 ulp); out of range (fill_value NaN) is decided by `inr`.
-                        const bool inr = x >= ax.g0 && x <= ax.glast;
-                        int k = (int)((x - ax.g0) * ax.inv_dx);
-                        k = max(0, min(k, ax.nr - 2));
-                        double2 gi = gi_s[k];
-                        double tt = (x - gi.x) * gi.y;
-                        if (inr && !(tt >= 0.0 && tt < tt_max)) {  // rounding at a node / non-uniform axis / x == glast
-                            k = bf_find_cell(ax, x);
-                            gi = gi_s[k];
-                            tt = (x - gi.x) * gi.y;
-                        }
-                        const double *row = sm.row[c] + k;
-                        const double r0 = __ldg(row), r1 = __ldg(row + 1);
-                        if (MODE == 0) {
-                            double val = fma(r1, tt, r0 * (1.0 - tt));
-                            double P = exp(inr ? val : nan(""));
-                            acc0 += bf_finite(P) ? P : 0.0;
-                        } else {
-                            const double sc = sm.aD[c] * bf_rsqrt(d2);
-                            const bool use = inr && d2 < sm.cut2[c];  // NaN fill / BaryonCorrection.py:381-382: both end as 0
-                            double val = fma(r1, tt, r0 * (1.0 - tt));
-                            double e = (use ? val : 0.0) * sc;
-                            if (!bf_finite(e)) e = 0.0;                   // HealpixRunner.py:323
-                            double q = e * d2 * (1.0 + e);
-                            double gg = q * fma(q, fma(q, fma(q, bf_kc[5], bf_kc[6]), bf_kc[4]), -0.5);  // (1+q)^-1/2 - 1
-                            if (fabs(q) > bf_kc[7]) gg = rsqrt(1.0 + q) - 1.0;  // pixel (almost) on the halo centre
-                            double ef = fma(e, gg, e);
-                            acc0 += fma(v[0], gg, ef * dx);
-                            acc1 += fma(v[1], gg, ef * dy);
-                            acc2 += fma(v[2], gg, ef * dz);
-                        }
+                        double p1[3];
+                        gather_pair<MODE>(sm, c, v, ax, gi_s, logtab, tt_max, p1);
+                        acc0 += p1[0];
+                        if (MODE == 1) { acc1 += p1[1]; acc2 += p1[2]; }
                     }
                 }
                 if (valid) {
