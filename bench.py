@@ -37,7 +37,7 @@ B_SNAP_PAIR = 72.0 # snapshot: 24 B particle xyz read + 48 B offsets RMW per pai
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE gather_kernel<1> launch at the default workload, N = 1, from the
 # ncu --set full capture summarised in profiles/ (the kernel writes every pixel once; it never re-reads accumulators)
 GATHER_TRAFFIC_BYTES = 7.06e9
-SNAP_TRAFFIC_BYTES = 10.69e9
+SNAP_TRAFFIC_BYTES = 10.92e9
 
 
 def parse():

@@ -455,7 +455,7 @@ def _shell_regrid(kind, nside, orig, off):
 
 
 @pytest.mark.parametrize("nside,amp", [(1, 0.3), (2, 0.2), (4, 0.05), (16, 0.01), (16, 0.1), (64, 0.002), (64, 0.03),
-                                       (256, 0.0005), (256, 0.004)])
+                                       (256, 0.0005), (256, 0.004), (12, 0.02), (100, 0.003)])
 def test_shell_regrid_gather_is_bit_identical_to_the_sorted_serial_order_sum(gpu, nside, amp):
     """Destination gather == counting sort bit for bit (same deposits, same ascending (source, j) order), from
     sub-pixel to many-pixel displacements, with masked pixels, on rings of every kind (caps, belt, poles)."""
