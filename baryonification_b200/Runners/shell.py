@@ -171,14 +171,15 @@ class BaryonifyShell(DefaultRunner):
                 self._after_host = None
             t0 = time.perf_counter()
             orig_d = (box.get("up") or dv.AsyncUpload(orig, dev)).result()
-            new_d = self._eng.regrid(orig_d, off, method=self.regrid)
+            old_sum_d = orig_d.sum()  # the reference's two np.sum's (HealpixRunner.py:344-346), on the device
+            # re-binning and read-back overlap: the gather variant hands over the map range by range
+            new_map, new_sum_d, t_dev = self._eng.regrid_to_host(orig_d, off, method=self.regrid, pinned=self.pinned_output)
             self.regrid_used = self._eng.regrid_used
             self._eng = None
-            new_sum_d, old_sum_d = new_d.sum(), orig_d.sum()  # the reference's two np.sum's, on the device
-            t0 = self._tick("regrid", t0, dev)
-            new_map = dv.to_host(new_d, self.pinned_output)
-            new_sum, old_sum = float(new_sum_d.item()), float(old_sum_d.item())  # HealpixRunner.py:344-346
-            self._tick("d2h", t0, dev)
+            new_sum, old_sum = float(new_sum_d.item()), float(old_sum_d.item())
+            torch.cuda.synchronize(dev)
+            t_all = time.perf_counter() - t0
+            self.timings["regrid"], self.timings["d2h"] = t_dev, max(t_all - t_dev, 0.0)  # (d2h: what the copy adds)
         assert np.isclose(new_sum, old_sum), \
             "ERROR in pixel regridding, sum(new_map) [%0.14e] != sum(oldmap) [%0.14e]" % (new_sum, old_sum)
         return new_map

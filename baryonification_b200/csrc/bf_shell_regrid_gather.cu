@@ -128,11 +128,11 @@ __device__ __forceinline__ void rg_scan(const uint4 *__restrict__ key, const dou
     }
 }
 
-__global__ void __launch_bounds__(256) rg_gather_kernel(bf_hpx h, int dr_min, int dr_max, int P,
-                                                        const uint4 *__restrict__ key, const double *__restrict__ val,
-                                                        double *__restrict__ out) {
-    const i64 d64 = (i64)blockIdx.x * blockDim.x + threadIdx.x;
-    if (d64 >= h.npix) return;
+__global__ void __launch_bounds__(256) rg_gather_kernel(bf_hpx h, int dr_min, int dr_max, int P, i64 d_first,
+                                                        i64 d_last, const uint4 *__restrict__ key,
+                                                        const double *__restrict__ val, double *__restrict__ out) {
+    const i64 d64 = d_first + (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (d64 >= d_last) return;
     const u32 d = (u32)d64;
     i64 r64, j64;
     bfh_pix2ring(h, d64, r64, j64);
@@ -170,42 +170,75 @@ extern "C" size_t bf_shell_regrid_gather_ws_bytes(int64_t nside) {
     return (size_t)(12 * nside * nside) * 48 + 512;
 }
 
-extern "C" int bf_shell_regrid_gather(int64_t nside, const double *orig_map, const double *pix_offsets, double *new_map,
-                                      void *ws, size_t ws_bytes, int *window_host, void *stream) {
-    BF_REQUIRE(nside > 0 && orig_map && pix_offsets && new_map, "null / nside");
-    bf_hpx h = bf_hpx_make(nside);
+// workspace layout: [window | keys uint4[npix] | values double[4 npix]]
+static int rg_layout(int64_t nside, void *ws, size_t ws_bytes, const char *who, bf_hpx &h, rg_window *&win, uint4 *&key,
+                     double *&val) {
+    BF_REQUIRE(nside > 0, "nside");
+    h = bf_hpx_make(nside);
     BF_REQUIRE(h.npix < 0xffffffffll, "nside too large for 32-bit destination keys");
     size_t need = bf_shell_regrid_gather_ws_bytes(nside);
     if (!ws || ws_bytes < need) {
-        bf_set_error("bf_shell_regrid_gather: workspace %zu < %zu bytes", ws_bytes, need);
+        bf_set_error("%s: workspace %zu < %zu bytes", who, ws_bytes, need);
         return BF_E_WORKSPACE;
     }
     BF_REQUIRE((((uintptr_t)ws) & 255) == 0, "workspace must be 256-byte aligned");
     char *base = (char *)ws;
-    rg_window *win = (rg_window *)base;
-    uint4 *key = (uint4 *)(base + 256);
-    double *val = (double *)(base + 256 + (size_t)h.npix * 16);
+    win = (rg_window *)base;
+    key = (uint4 *)(base + 256);
+    val = (double *)(base + 256 + (size_t)h.npix * 16);
+    return BF_OK;
+}
+
+extern "C" int bf_shell_regrid_gather_emit(int64_t nside, const double *orig_map, const double *pix_offsets, void *ws,
+                                           size_t ws_bytes, int *window_host, void *stream) {
+    BF_REQUIRE(orig_map && pix_offsets && window_host, "null argument");
+    bf_hpx h; rg_window *win; uint4 *key; double *val;
+    int rc = rg_layout(nside, ws, ws_bytes, "bf_shell_regrid_gather_emit", h, win, key, val);
+    if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
-    const unsigned blocks = (unsigned)((h.npix + 255) / 256);
     rg_init_kernel<<<1, 1, 0, s>>>(win);
     BF_LAUNCH_OK();
-    rg_emit_kernel<<<blocks, 256, 0, s>>>(h, orig_map, pix_offsets, key, val, win);
+    rg_emit_kernel<<<(unsigned)((h.npix + 255) / 256), 256, 0, s>>>(h, orig_map, pix_offsets, key, val, win);
     BF_LAUNCH_OK();
     rg_window w;
     BF_CUDA_OK(cudaMemcpyAsync(&w, win, sizeof(w), cudaMemcpyDeviceToHost, s));
     BF_CUDA_OK(cudaStreamSynchronize(s));
-    if (w.dr_max < w.dr_min) {  // nothing to deposit (orig <= 0 everywhere)
-        if (window_host) window_host[0] = window_host[1] = window_host[2] = 0;
+    if (w.dr_max < w.dr_min) {  // nothing to deposit (orig <= 0 everywhere): an empty window
+        window_host[0] = 1; window_host[1] = 0; window_host[2] = 0;
         return BF_OK;
     }
-    if (window_host) { window_host[0] = w.dr_min; window_host[1] = w.dr_max; window_host[2] = w.dj_max; }
+    window_host[0] = w.dr_min; window_host[1] = w.dr_max; window_host[2] = w.dj_max;
     const long long cost = (long long)(w.dr_max - w.dr_min + 1) * (2LL * w.dj_max + 1);
     if (cost > BF_SHELL_GATHER_MAX_WINDOW) {
         bf_set_error("bf_shell_regrid_gather: window of %d rings x %d pixels exceeds %d sources per destination",
                      w.dr_max - w.dr_min + 1, 2 * w.dj_max + 1, BF_SHELL_GATHER_MAX_WINDOW);
         return BF_E_WINDOW;
     }
-    rg_gather_kernel<<<blocks, 256, 0, s>>>(h, w.dr_min, w.dr_max, w.dj_max, key, val, new_map);
+    return BF_OK;
+}
+
+extern "C" int bf_shell_regrid_gather_range(int64_t nside, const void *ws, size_t ws_bytes, const int *window_host,
+                                            int64_t dest_first, int64_t dest_last, double *new_map, void *stream) {
+    BF_REQUIRE(window_host && new_map, "null argument");
+    bf_hpx h; rg_window *win; uint4 *key; double *val;
+    int rc = rg_layout(nside, const_cast<void *>(ws), ws_bytes, "bf_shell_regrid_gather_range", h, win, key, val);
+    if (rc) return rc;
+    BF_REQUIRE(dest_first >= 0 && dest_first <= dest_last && dest_last <= h.npix, "destination range");
+    if (dest_last == dest_first || window_host[1] < window_host[0]) return BF_OK;
+    const i64 n = dest_last - dest_first;
+    rg_gather_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        h, window_host[0], window_host[1], window_host[2], dest_first, dest_last, key, val, new_map);
     BF_LAUNCH_OK();
     return BF_OK;
+}
+
+extern "C" int bf_shell_regrid_gather(int64_t nside, const double *orig_map, const double *pix_offsets, double *new_map,
+                                      void *ws, size_t ws_bytes, int *window_host, void *stream) {
+    BF_REQUIRE(nside > 0 && orig_map && pix_offsets && new_map, "null / nside");
+    int win[3] = {1, 0, 0};
+    int rc = bf_shell_regrid_gather_emit(nside, orig_map, pix_offsets, ws, ws_bytes, win, stream);
+    const bool empty = win[1] < win[0];
+    if (window_host) { window_host[0] = empty ? 0 : win[0]; window_host[1] = empty ? 0 : win[1]; window_host[2] = win[2]; }
+    if (rc) return rc;
+    return bf_shell_regrid_gather_range(nside, ws, ws_bytes, win, 0, 12 * nside * nside, new_map, stream);
 }

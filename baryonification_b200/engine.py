@@ -155,3 +155,53 @@ class ShellEngine:
                       dv.ptr(new_d), dv.stream_ptr())
             self.regrid_used = "atomic"
         return new_d
+
+    def regrid_to_host(self, orig_d, off, method="gather", pinned=True, chunks=4):
+        """Re-binning + read-back of the new map -> (host array, device scalar sum(new map), seconds of the device part).
+
+        With the destination-gather variant the map is PRODUCED in destination ranges, so every finished range starts its
+        way to the host (side stream, page-locked target) while the next one is computed; the other variants (and a
+        window that is too wide) re-bin first and copy afterwards."""
+        whole = self.pix_first == 0 and self.pix_last == self.npix
+        if method == "gather" and whole and pinned and chunks > 1:
+            need = self.lib.bf_shell_regrid_gather_ws_bytes(self.nside)
+            if getattr(self, "_rg_ws", None) is None or self._rg_ws.numel() < need:
+                self._rg_ws = None
+                self._rg_ws = torch.empty(need, dtype=torch.uint8, device=self.dev)
+            main = torch.cuda.current_stream(self.dev)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(main)
+            win = (C.c_int * 3)()
+            rc = self.lib.bf_shell_regrid_gather_emit(self.nside, dv.ptr(orig_d), dv.ptr(off), dv.ptr(self._rg_ws),
+                                                      self._rg_ws.numel(), win, dv.stream_ptr())
+            self.regrid_window = tuple(win)
+            if rc == 0:
+                new_d = dv.zeros(self.npix, dev=self.dev)
+                out = torch.empty(self.npix, dtype=torch.float64, pin_memory=True)
+                side = torch.cuda.Stream(device=self.dev)
+                edges = [self.npix * i // chunks for i in range(chunks + 1)]
+                for a, b in zip(edges[:-1], edges[1:]):
+                    _lib.call("bf_shell_regrid_gather_range", self.nside, dv.ptr(self._rg_ws), self._rg_ws.numel(), win,
+                              a, b, dv.ptr(new_d), dv.stream_ptr())
+                    done = torch.cuda.Event()
+                    done.record(main)
+                    side.wait_event(done)
+                    with torch.cuda.stream(side):
+                        out[a:b].copy_(new_d[a:b], non_blocking=True)
+                e1.record(main)
+                new_sum = new_d.sum()
+                new_d.record_stream(side)
+                side.synchronize()
+                main.synchronize()
+                self.regrid_used = "gather"
+                return out.numpy(), new_sum, e0.elapsed_time(e1) * 1e-3
+            if rc != -3:  # (BF_E_WINDOW: displacements span too many pixels for the gather -> counting sort)
+                _lib.check(rc, "bf_shell_regrid_gather_emit")
+            method = "sorted"
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        new_d = self.regrid(orig_d, off, method=method)
+        e1.record()
+        new_sum = new_d.sum()
+        host = dv.to_host(new_d, pinned)
+        return host, new_sum, e0.elapsed_time(e1) * 1e-3

@@ -150,6 +150,14 @@ int bf_shell_regrid_sorted(int64_t nside, int64_t pix_first, int64_t pix_last, c
 size_t bf_shell_regrid_gather_ws_bytes(int64_t nside);
 int bf_shell_regrid_gather(int64_t nside, const double *orig_map, const double *pix_offsets, double *new_map, void *ws,
                            size_t ws_bytes, int *window_host, void *stream);
+/* The two passes on their own, so that a caller can produce the map in destination ranges and start reading each
+ * range back while the next one is computed: _emit writes the deposits into ws and returns the window in
+ * window_host[3] (an empty field gives dr_min > dr_max; BF_E_WINDOW as above; synchronises `stream` once), _range
+ * adds the deposits of destinations dest_first <= d < dest_last to new_map (+=), given that window. */
+int bf_shell_regrid_gather_emit(int64_t nside, const double *orig_map, const double *pix_offsets, void *ws,
+                                size_t ws_bytes, int *window_host, void *stream);
+int bf_shell_regrid_gather_range(int64_t nside, const void *ws, size_t ws_bytes, const int *window_host,
+                                 int64_t dest_first, int64_t dest_last, double *new_map, void *stream);
 
 /* ---- Grid runners (Map2DRunner.py) ---- */
 typedef struct {
