@@ -196,4 +196,15 @@ class PaintProfilesShell(DefaultRunner):
     def process(self):
         dev = dv.device(self.device)
         with torch.cuda.device(dev):
-            return dv.to_host(self.process_device(dev), self.pinned_output)
+            nh = len(self.HaloLightConeCatalog.cat)
+            if (not self.pinned_output or self.variant != "gather"
+                    or (self.pipeline_chunks > 1 and nh >= self.pipeline_min_halos)):
+                return dv.to_host(self.process_device(dev), self.pinned_output)
+            # pixel owners finish band by band: the read-back of a finished band group overlaps the next group's kernel
+            assert self.model is not None, "You must provide a model"
+            eng = self._engine(dev, engine.PAINT)
+            t0 = time.perf_counter()
+            out = eng.accumulate_to_host()
+            self.npairs = eng.npairs
+            self._tick("accumulate_d2h", t0, dev)
+            return out

@@ -156,7 +156,7 @@ class ShellEngine:
             self.regrid_used = "atomic"
         return new_d
 
-    def regrid_to_host(self, orig_d, off, method="gather", pinned=True, chunks=4):
+    def regrid_to_host(self, orig_d, off, method="gather", pinned=True, chunks=8):
         """Re-binning + read-back of the new map -> (host array, device scalar sum(new map), seconds of the device part).
 
         With the destination-gather variant the map is PRODUCED in destination ranges, so every finished range starts its
@@ -205,3 +205,34 @@ class ShellEngine:
         new_sum = new_d.sum()
         host = dv.to_host(new_d, pinned)
         return host, new_sum, e0.elapsed_time(e1) * 1e-3
+
+    def accumulate_to_host(self, chunks=8):
+        """Pair stage + read-back of the accumulator (PaintProfilesShell) -> host array.  Pixel owners finish ring band
+        by ring band, so the gather kernel is launched over ``chunks`` groups of bands (equal pixel counts) and every
+        finished group is copied to page-locked host memory on a side stream while the next one is evaluated."""
+        whole = self.pix_first == 0 and self.pix_last == self.npix
+        if self.variant != "gather" or not whole or chunks < 2 or self.nh == 0:
+            out = self.accumulate()
+            self.pair_count()
+            return dv.to_host(out, True)
+        from .sharding import band_pixel_range, band_split
+        nb = self.lib.bf_shell_num_bands(self.nside)
+        groups = [g for g in band_split(self.nside, min(chunks, nb)) if g[1] > g[0]]
+        shape = (self.npix,) if self.mode == PAINT else (self.npix, 3)
+        out_d = dv.empty(shape, dev=self.dev)
+        out_h = torch.empty(shape, dtype=torch.float64, pin_memory=True)
+        main, side = torch.cuda.current_stream(self.dev), torch.cuda.Stream(device=self.dev)
+        self.cnt.zero_()
+        for lo, hi in groups:
+            _lib.call("bf_shell_gather", self.nside, self.mode, C.byref(self.desc), C.byref(self.table.desc), lo, hi,
+                      dv.ptr(self.ws), dv.ptr(out_d), 0, 0, dv.ptr(self.cnt), dv.stream_ptr())
+            a, b = band_pixel_range(self.nside, lo, hi)
+            done = torch.cuda.Event()
+            done.record(main)
+            side.wait_event(done)
+            with torch.cuda.stream(side):
+                out_h[a:b].copy_(out_d[a:b], non_blocking=True)
+        out_d.record_stream(side)
+        self.pair_count()  # (synchronises the main stream)
+        side.synchronize()
+        return out_h.numpy()
