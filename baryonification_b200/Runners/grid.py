@@ -130,16 +130,35 @@ class BaryonifyGrid(DefaultRunnerGrid):
             dim = 2 if G.is2D else 3
             lib = _lib.load(require_cuda=True)
             mode = self.regrid
+            new_map = None
             if mode == "gather":
+                # destination gather, produced in runs of rows of the first axis: every finished run is read back (side
+                # stream, page-locked target) while the next one is computed
                 ws = torch.empty(lib.bf_grid_regrid_gather_ws_bytes(), dtype=torch.uint8, device=dev)
-                win = (C.c_int * 3)()
-                rc = lib.bf_grid_regrid_gather(dim, G.Npix, dv.ptr(off), dv.ptr(orig_d), dv.ptr(new_d), dv.ptr(ws),
-                                               ws.numel(), win, dv.stream_ptr())
-                self.regrid_window = tuple(win)
-                if rc == -3:  # BF_E_WINDOW: displacements span too many cells for the gather
-                    mode = "sorted"
-                else:
-                    _lib.check(rc, "bf_grid_regrid_gather")
+                lohi, win = (C.c_int * 6)(), (C.c_int * 3)()
+                _lib.call("bf_grid_regrid_window", dim, G.Npix, dv.ptr(off), 0, G.Npix, dv.ptr(ws), ws.numel(), lohi,
+                          dv.stream_ptr())
+                rowlen = orig.size // G.Npix
+                nchunk = 8 if G.Npix >= 64 else 1
+                out_h = torch.empty(orig.size, dtype=torch.float64, pin_memory=True)
+                main, side = torch.cuda.current_stream(dev), torch.cuda.Stream(device=dev)
+                for i in range(nchunk):
+                    a, b = G.Npix * i // nchunk, G.Npix * (i + 1) // nchunk
+                    rc = lib.bf_grid_regrid_gather_rows(dim, G.Npix, dv.ptr(off), dv.ptr(orig_d), dv.ptr(new_d), lohi,
+                                                        a, b, win, dv.stream_ptr())
+                    self.regrid_window = tuple(win)
+                    if rc == -3:  # BF_E_WINDOW: displacements span too many cells for the gather (decided on the window,
+                        mode = "sorted"  # i.e. at the first run: nothing has been written yet)
+                        break
+                    _lib.check(rc, "bf_grid_regrid_gather_rows")
+                    done = torch.cuda.Event()
+                    done.record(main)
+                    side.wait_event(done)
+                    with torch.cuda.stream(side):
+                        out_h[a * rowlen:b * rowlen].copy_(new_d[a * rowlen:b * rowlen], non_blocking=True)
+                if mode == "gather":
+                    new_d.record_stream(side)
+                    new_map = out_h
             self.regrid_used = mode
             if mode == "gather":
                 pass
@@ -155,7 +174,11 @@ class BaryonifyGrid(DefaultRunnerGrid):
             torch.cuda.synchronize(dev)
             self.timings["regrid"] = time.perf_counter() - t0
             t0 = time.perf_counter()
-            new_map = dv.to_host(new_d, True).reshape(G.map.shape)
+            if new_map is not None:
+                side.synchronize()
+                new_map = new_map.numpy().reshape(G.map.shape)
+            else:
+                new_map = dv.to_host(new_d, True).reshape(G.map.shape)
             new_sum, old_sum = float(new_sum_d.item()), float(old_sum_d.item())  # Map2DRunner.py:611-613
             self.timings["d2h"] = time.perf_counter() - t0
             self.timings["process"] = time.perf_counter() - t00
