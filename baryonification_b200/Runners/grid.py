@@ -69,8 +69,10 @@ class DefaultRunnerGrid:
         bins = dv.to_dev(G.bins, dev=dev)
         return table, s, desc, bins, (t, rows)
 
-    def _accumulate(self, mode, s, desc, bins, table, out, cnt, dev):
-        """The per-halo loop (Map2DRunner.py:476-580 / :714-810) into ``out``: cell-owner gather, or atomics."""
+    def _accumulate(self, mode, s, desc, bins, table, out, cnt, dev, row_runs=None, after_run=None):
+        """The per-halo loop (Map2DRunner.py:476-580 / :714-810) into ``out``: cell-owner gather, or atomics.
+        ``row_runs``: evaluate the cell owners in these runs of rows of the first axis, one launch each, and call
+        ``after_run(a, b)`` after every launch (the caller starts the read-back of the finished rows there)."""
         G = self.GriddedMap
         lib = _lib.load(require_cuda=True)
         dim, nh = s["dim"], s["cut"].size
@@ -90,9 +92,14 @@ class DefaultRunnerGrid:
                 _lib.check(rc, "bf_grid_bin_halos")
                 break
             self.nentries = n.value
-            a0, a1 = self.rows if self.rows is not None else (0, G.Npix)
-            _lib.call("bf_grid_gather_rows", dim, mode, G.Npix, float(G.res), C.byref(desc), C.byref(table.desc),
-                      max_entries, dv.ptr(ws), dv.ptr(out), a0, a1, dv.ptr(cnt), dv.stream_ptr())
+            runs = [self.rows if self.rows is not None else (0, G.Npix)]
+            if row_runs and self.rows is None:
+                runs = row_runs
+            for a0, a1 in runs:
+                _lib.call("bf_grid_gather_rows", dim, mode, G.Npix, float(G.res), C.byref(desc), C.byref(table.desc),
+                          max_entries, dv.ptr(ws), dv.ptr(out), a0, a1, dv.ptr(cnt), dv.stream_ptr())
+                if after_run is not None and runs is row_runs:
+                    after_run(a0, a1)
         elif nh > 0:
             if self.rows is not None:
                 raise _lib.BFError("slab-sharded grids need the cell-owner gather (variant='gather')")
@@ -188,13 +195,15 @@ class BaryonifyGrid(DefaultRunnerGrid):
 
 
 class PaintProfilesGrid(DefaultRunnerGrid):
-    def paint_device(self, dev):
+    def paint_device(self, dev, row_runs=None, after_run=None):
         """The painted map as a device tensor [Npix^D] (rows outside ``self.rows`` stay zero)."""
         G = self.GriddedMap
         table, s, desc, bins, keep = self._prepare(profile_host_table(self.model, "2D" if G.is2D else "3D"), False, dev)
         out = dv.zeros(G.map.size, dev=dev)
         cnt = dv.pair_counter(dev)
-        self._accumulate(1, s, desc, bins, table, out, cnt, dev)
+        if after_run is not None:
+            after_run(None, None, out)  # hand the accumulator to the caller's read-back
+        self._accumulate(1, s, desc, bins, table, out, cnt, dev, row_runs, after_run)
         del keep
         return out
 
@@ -203,6 +212,38 @@ class PaintProfilesGrid(DefaultRunnerGrid):
         G = self.GriddedMap
         with torch.cuda.device(dev):
             t0 = time.perf_counter()
+            n = G.Npix
+            if self.variant == "gather" and self.rows is None and n >= 128 and G.map.size >= (1 << 23):  # >= 64 MB
+                # cell owners finish run by run of rows (tile-aligned): a finished run's read-back overlaps the next launch
+                rowlen = G.map.size // n
+                edges = sorted(set([0, n] + [min(n, (n * i // 8 + 15) // 16 * 16) for i in range(1, 8)]))
+                runs = [(a, b) for a, b in zip(edges[:-1], edges[1:]) if b > a]
+                out_h = torch.empty(G.map.size, dtype=torch.float64, pin_memory=True)
+                main, side = torch.cuda.current_stream(dev), torch.cuda.Stream(device=dev)
+                copied, box = [], {}
+
+                def after_run(a, b, acc=None):  # (no reference to itself: a cycle would keep the pinned block alive)
+                    if acc is not None:
+                        box["out"] = acc
+                        return
+                    done = torch.cuda.Event()
+                    done.record(main)
+                    side.wait_event(done)
+                    with torch.cuda.stream(side):
+                        out_h[a * rowlen:b * rowlen].copy_(box["out"][a * rowlen:b * rowlen], non_blocking=True)
+                    copied.append((a, b))
+
+                out = self.paint_device(dev, runs, after_run)
+                box.clear()
+                self.timings["accumulate"] = time.perf_counter() - t0
+                if copied:  # (the atomic fall-back of a too-wide cut-out evaluates everything at once)
+                    out.record_stream(side)
+                    side.synchronize()
+                    res = out_h.numpy().reshape(G.map.shape)
+                else:
+                    res = dv.to_host(out, True).reshape(G.map.shape)
+                self.timings["process"] = time.perf_counter() - t0
+                return res
             out = self.paint_device(dev)
             self.timings["accumulate"] = time.perf_counter() - t0
             res = dv.to_host(out, True).reshape(G.map.shape)

@@ -81,6 +81,14 @@ for tag, npix, nh in (("c5a", 512, 20_000), ("c5b", 1024, 100_000)):
                mass_relerr=float(abs(out.sum() / cfg["field"].map.sum() - 1))))
         del out, r, cfg
 
+if "c5p" in which:  # PaintProfilesGrid 3-D 512^3 (the paint counterpart of C5)
+    cfg = syn.config_grid(npix=512, nhalo=20_000, dim=3)
+    r = bf.PaintProfilesGrid(cfg["catalog"], cfg["field"], 20.0, cfg["paint_model"], verbose=False)
+    out, t = timed(r.process, n=2)
+    report("C5 PaintProfilesGrid 3D 512^3, 20000 halos", dict(pairs=r.npairs, gpu_process_ms=t * 1e3,
+           gpu_pairs_per_s=r.npairs / t, stages_ms={k: round(v * 1e3, 2) for k, v in r.timings.items()}))
+    del out, r, cfg
+
 if "pk" in which:  # Delta P(k) of a baryonified 256^3 snapshot on a 256^3 mesh, folding factors 1 and 8
     cfg = syn.config_snapshot(npart_side=256, nhalo=20_000, dim=3)
     new = bf.BaryonifySnapshot(cfg["catalog"], cfg["field"], 5.0, cfg["model"], verbose=False).process()
