@@ -128,6 +128,37 @@ __device__ __forceinline__ double bf_rsqrt(double x) {
     return fma(p, y0 * e, y0);
 }
 
+// ------------------------------------------------------------------------------------------
+// TMA bulk copy (cp.async.bulk, global -> shared, completion on an mbarrier): the per-call constant tables of a pair
+// kernel (ln table, radial axis) are prepared ONCE in global memory and every CTA stages them with a single
+// asynchronous bulk copy issued by one thread, instead of 256 threads recomputing them with divisions and logarithms.
+// Sizes and addresses must be multiples of 16 bytes.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned bf_smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void bf_mbar_init(u64 *bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bf_smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");  // visible to the async proxy
+}
+
+__device__ __forceinline__ void bf_tma_load_1d(void *dst_smem, const void *src_gmem, unsigned bytes, u64 *bar) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bf_smem_u32(bar)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     bf_smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(bf_smem_u32(bar))
+                 : "memory");
+}
+
+__device__ __forceinline__ void bf_mbar_wait(u64 *bar, unsigned parity) {
+    unsigned done;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.b32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done)
+                     : "r"(bf_smem_u32(bar)), "r"(parity)
+                     : "memory");
+    } while (!done);
+}
+
 // value of one collapsed row at ln r = x; NaN outside the table (fill_value).  The two-product form
 // keeps scipy's inf/NaN propagation: a zero weight still multiplies (0 * -inf = NaN).
 __device__ __forceinline__ double bf_row_lerp(const bf_raxis &ax, const double *__restrict__ row, double x) {

@@ -9,6 +9,8 @@
 #include "bf_healpix.cuh"
 
 #define BF_BAND_RINGS 8
+#define BF_GATHER_NR_MAX 8192  // longest radial axis the gather kernel stages (24 B per node + 2 KB of ln table)
+#define BF_GATHER_AUX_BYTES (2048 + 24 * BF_GATHER_NR_MAX + 16)
 #define BF_MAX_COLS 64
 
 struct bf_cells {
@@ -40,6 +42,7 @@ struct bf_bin_ws {
     int *cell_end;      // [ncells]
     int *tiny_list;     // [nh]   halos diverted to the < 4-pixel fallback (baryonify)
     int *tiny_count;    // [1]
+    void *aux;          // [BF_GATHER_AUX_BYTES] per-call constant tables of the gather kernel (ln table, radial axis)
     void *cub_tmp;
     size_t cub_bytes;
     i64 ncells;
@@ -64,6 +67,7 @@ static inline bf_bin_ws bf_bin_ws_layout(void *base, i64 nside, i64 nh, i64 max_
     w.cell_end = (int *)(p + o);    o += bf_al256(sizeof(int) * (size_t)w.ncells);
     w.tiny_list = (int *)(p + o);   o += bf_al256(sizeof(int) * (size_t)(nh + 1));
     w.tiny_count = (int *)(p + o);  o += 256;
+    w.aux = (void *)(p + o);        o += bf_al256(BF_GATHER_AUX_BYTES);
     w.keys = (u64 *)(p + o);        o += bf_al256(sizeof(u64) * (size_t)(max_entries + 1));
     w.keys_alt = (u64 *)(p + o);    o += bf_al256(sizeof(u64) * (size_t)(max_entries + 1));
     w.cub_bytes = bf_bin_cub_bytes(nh, max_entries);

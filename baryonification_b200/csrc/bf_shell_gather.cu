@@ -33,6 +33,8 @@
 #endif
 
 struct gather_args {
+    const void *aux;     // [ln table | (g, 1/dg) pairs | g] prepared once per call (gather_aux_kernel)
+    unsigned aux_bytes;  // multiple of 16
     bf_hpx h;
     bf_cells cg;
     bf_shell_halos S;
@@ -53,6 +55,7 @@ struct gather_smem {
     int irmin[GT_CMAX], irmax[GT_CMAX], wn[GT_CMAX], ws[GT_CMAX];
     int2 rng[GT_WARPS][GT_CMAX];
     unsigned hits[GT_WARPS][GT_CMAX / 32][32];  // [warp][candidate word][lane]: bit c = candidate 32*word+c hits my pixel
+    u64 mbar, mbar_pad;                         // completion barrier of the TMA bulk copy of the constant tables
 };
 
 // bits a..e (inclusive) of a 32-bit word, clipped to the word
@@ -164,11 +167,11 @@ __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather
         return;
     }
 
-    for (int k = t; k < A.ax.nr; k += GT_THREADS) g_s[k] = A.ax.g[k];
-    bf_logtab_init(logtab, t, GT_THREADS);
+    // stage the constant tables: ONE asynchronous bulk copy (TMA) issued by thread 0, completion on an mbarrier
+    if (t == 0) bf_mbar_init(&sm.mbar, 1);
     __syncthreads();
-    for (int k = t; k < A.ax.nr; k += GT_THREADS)
-        gi_s[k] = make_double2(g_s[k], (k < A.ax.nr - 1) ? 1.0 / (g_s[k + 1] - g_s[k]) : 0.0);
+    if (t == 0) bf_tma_load_1d(logtab, A.aux, A.aux_bytes, &sm.mbar);
+    bf_mbar_wait(&sm.mbar, 0);
     const double tt_max = 1.0 - 0x1p-50;
     bf_raxis ax = A.ax;
     ax.g = g_s;
@@ -269,6 +272,20 @@ __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather
     if (lane == 0 && A.npairs && my_pairs) atomicAdd(A.npairs, my_pairs);
 }
 
+// The tables every CTA of the gather kernel stages: ln table, the radial axis as (g[k], 1 / (g[k+1] - g[k])) pairs, the
+// plain axis.  Computed once per call (the same expressions the kernel used to evaluate per CTA).
+__global__ void __launch_bounds__(256) gather_aux_kernel(bf_raxis ax, double2 *__restrict__ logtab,
+                                                         double2 *__restrict__ gi, double *__restrict__ g) {
+    const int t = threadIdx.x;
+    bf_logtab_init(logtab, t, 256);
+    for (int k = t; k < ax.nr; k += 256) {
+        const double gk = ax.g[k];
+        g[k] = gk;
+        gi[k] = make_double2(gk, (k < ax.nr - 1) ? 1.0 / (ax.g[k + 1] - gk) : 0.0);
+    }
+    if (t == 0 && (ax.nr & 1)) g[ax.nr] = 0.0;  // pad to a multiple of 16 bytes
+}
+
 // Baryonify only: discs with < 4 pixels use the 4 interpolation neighbours (HealpixRunner.py:309-310).  These
 // halos were diverted by the binning stage; they are applied on top of the gathered offsets with fp64
 // atomics (4 pixels each; order only matters if >= 3 of them share a pixel).
@@ -319,8 +336,18 @@ extern "C" int bf_shell_gather(int64_t nside, int mode, const bf_shell_halos *S,
     A.accumulate = accumulate;
     A.npairs = npairs;
     static_assert(sizeof(gather_smem) % 16 == 0, "the ln table behind the struct must stay 16-byte aligned");
-    size_t smem = sizeof(gather_smem) + 3 * sizeof(double) * (size_t)T->nr + sizeof(double2) * BF_LOGTAB;
+    BF_REQUIRE(T->nr <= BF_GATHER_NR_MAX, "table r-axis too long for the shared-memory stage");
+    const size_t aux_bytes = sizeof(double2) * BF_LOGTAB + 16 * (size_t)T->nr + ((8 * (size_t)T->nr + 15) & ~(size_t)15);
+    size_t smem = sizeof(gather_smem) + aux_bytes;
     BF_REQUIRE(smem <= 200 * 1024, "table r-axis too long for the shared-memory stage");
+    {
+        char *aux = (char *)w.aux;
+        gather_aux_kernel<<<1, 256, 0, s>>>(A.ax, (double2 *)aux, (double2 *)(aux + sizeof(double2) * BF_LOGTAB),
+                                            (double *)(aux + sizeof(double2) * BF_LOGTAB + 16 * (size_t)T->nr));
+        BF_LAUNCH_OK();
+        A.aux = w.aux;
+        A.aux_bytes = (unsigned)aux_bytes;
+    }
     unsigned grid = (unsigned)((band_hi - band_lo) * BF_MAX_COLS);
     if (mode == 0) {
         BF_CUDA_OK(cudaFuncSetAttribute(gather_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -724,6 +724,21 @@ def test_param_tabulated_profiles_parity(gpu):
     dm.p_keys = []
 
 
+def test_paint_grid_pipelined_readback_equals_single_launch(gpu):
+    """Maps of >= 64 MB are painted in tile-aligned runs of rows whose read-back overlaps the next launch: the host
+    map must be the single-launch device result bit for bit, with the same pair count."""
+    import torch
+    import baryonification_b200 as bf
+    from baryonification_b200 import synthetic as syn
+    cfg = syn.config_grid(npix=208, nhalo=400, dim=3, epsilon_max=8.0)
+    assert cfg["field"].map.size >= (1 << 23)
+    r = bf.PaintProfilesGrid(cfg["catalog"], cfg["field"], 8.0, cfg["paint_model"], verbose=False)
+    got = r.process()
+    n1 = r.npairs
+    want = r.paint_device(torch.device("cuda", torch.cuda.current_device())).cpu().numpy().reshape(got.shape)
+    assert r.npairs == n1 and np.array_equal(got, want) and np.count_nonzero(got) > 0
+
+
 # ------------------------------------------------------------------ Delta P(k)
 @pytest.mark.parametrize("ngrd,nk,factor", [(32, 12, 1), (48, 20, 2), (27, 9, 1), (64, 30, 8)])
 def test_delta_pk_matches_notebook_recipe(gpu, ngrd, nk, factor):
