@@ -83,6 +83,8 @@ _SIGS = {
                                          C.c_void_p]),
     "bf_shell_regrid_gather_emit": (C.c_int, [_i64, _dbl_p, _dbl_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_int),
                                               C.c_void_p]),
+    "bf_shell_regrid_gather_emit_range": (C.c_int, [_i64, _i64, _i64, _dbl_p, _dbl_p, C.c_void_p, C.c_size_t,
+                                                    C.POINTER(C.c_int), C.c_void_p]),
     "bf_shell_regrid_gather_range": (C.c_int, [_i64, C.c_void_p, C.c_size_t, C.POINTER(C.c_int), _i64, _i64, _dbl_p,
                                                C.c_void_p]),
     "bf_grid_baryonify_atomic": (C.c_int, [C.c_int, _i64, _dbl_p, C.c_double, _P(GridHalos), _P(Table), _dbl_p,

@@ -52,12 +52,18 @@ __global__ void __launch_bounds__(256) rg_init_kernel(rg_window *w) {
     w->dr_min = 0x7fffffff; w->dr_max = -0x7fffffff; w->dj_max = 0; w->pad = 0;
 }
 
-__global__ void __launch_bounds__(256) rg_emit_kernel(bf_hpx h, const double *__restrict__ orig,
-                                                      const double *__restrict__ off, uint4 *__restrict__ key,
+// Sources p_first <= p < p_last (orig / off are that slice); pixels of the margin e_first <= p < e_last around it only
+// get the "no deposit" key, so that a ring-band shard can gather its partial sums without reading stale keys.
+__global__ void __launch_bounds__(256) rg_emit_kernel(bf_hpx h, i64 p_first, i64 p_last, i64 e_first, i64 e_last,
+                                                      const double *__restrict__ orig_s,
+                                                      const double *__restrict__ off_s, uint4 *__restrict__ key,
                                                       double *__restrict__ val, rg_window *__restrict__ win) {
-    const i64 p = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    const i64 p = e_first + (i64)blockIdx.x * blockDim.x + threadIdx.x;
     int dr_min = 0x7fffffff, dr_max = -0x7fffffff, dj_max = 0;
-    if (p < h.npix) {
+    if (p < e_last && (p < p_first || p >= p_last)) {
+        key[p] = make_uint4((u32)h.npix, (u32)h.npix, (u32)h.npix, (u32)h.npix);
+    } else if (p < e_last) {
+        const double *orig = orig_s - p_first, *off = off_s - 3 * p_first;
         const double m = orig[p];
         uint4 kk = make_uint4((u32)h.npix, (u32)h.npix, (u32)h.npix, (u32)h.npix);
         double vv[4] = {0.0, 0.0, 0.0, 0.0};
@@ -189,17 +195,26 @@ static int rg_layout(int64_t nside, void *ws, size_t ws_bytes, const char *who, 
     return BF_OK;
 }
 
-extern "C" int bf_shell_regrid_gather_emit(int64_t nside, const double *orig_map, const double *pix_offsets, void *ws,
-                                           size_t ws_bytes, int *window_host, void *stream) {
+// sources pix_first <= p < pix_last; orig_map / pix_offsets are that slice
+extern "C" int bf_shell_regrid_gather_emit_range(int64_t nside, int64_t pix_first, int64_t pix_last, const double *orig_map,
+                                                 const double *pix_offsets, void *ws, size_t ws_bytes, int *window_host,
+                                                 void *stream) {
     BF_REQUIRE(orig_map && pix_offsets && window_host, "null argument");
     bf_hpx h; rg_window *win; uint4 *key; double *val;
     int rc = rg_layout(nside, ws, ws_bytes, "bf_shell_regrid_gather_emit", h, win, key, val);
     if (rc) return rc;
+    BF_REQUIRE(pix_first >= 0 && pix_first <= pix_last && pix_last <= h.npix, "pixel range");
+    const i64 margin = (i64)BF_SHELL_GATHER_MARGIN_RINGS * 4 * nside;
+    const i64 e_first = (pix_first - margin > 0) ? pix_first - margin : 0;
+    const i64 e_last = (pix_last + margin < h.npix) ? pix_last + margin : h.npix;
     cudaStream_t s = (cudaStream_t)stream;
     rg_init_kernel<<<1, 1, 0, s>>>(win);
     BF_LAUNCH_OK();
-    rg_emit_kernel<<<(unsigned)((h.npix + 255) / 256), 256, 0, s>>>(h, orig_map, pix_offsets, key, val, win);
-    BF_LAUNCH_OK();
+    if (e_last > e_first) {
+        rg_emit_kernel<<<(unsigned)((e_last - e_first + 255) / 256), 256, 0, s>>>(h, pix_first, pix_last, e_first, e_last,
+                                                                                 orig_map, pix_offsets, key, val, win);
+        BF_LAUNCH_OK();
+    }
     rg_window w;
     BF_CUDA_OK(cudaMemcpyAsync(&w, win, sizeof(w), cudaMemcpyDeviceToHost, s));
     BF_CUDA_OK(cudaStreamSynchronize(s));
@@ -209,12 +224,21 @@ extern "C" int bf_shell_regrid_gather_emit(int64_t nside, const double *orig_map
     }
     window_host[0] = w.dr_min; window_host[1] = w.dr_max; window_host[2] = w.dj_max;
     const long long cost = (long long)(w.dr_max - w.dr_min + 1) * (2LL * w.dj_max + 1);
-    if (cost > BF_SHELL_GATHER_MAX_WINDOW) {
+    const int reach = (w.dr_max > -w.dr_min ? w.dr_max : -w.dr_min) + 1;  // rings between a source and its destination
+    const bool part = pix_first > 0 || pix_last < h.npix;
+    if (cost > BF_SHELL_GATHER_MAX_WINDOW || (part && 2 * reach > BF_SHELL_GATHER_MARGIN_RINGS)) {
         bf_set_error("bf_shell_regrid_gather: window of %d rings x %d pixels exceeds %d sources per destination",
                      w.dr_max - w.dr_min + 1, 2 * w.dj_max + 1, BF_SHELL_GATHER_MAX_WINDOW);
         return BF_E_WINDOW;
     }
     return BF_OK;
+}
+
+extern "C" int bf_shell_regrid_gather_emit(int64_t nside, const double *orig_map, const double *pix_offsets, void *ws,
+                                           size_t ws_bytes, int *window_host, void *stream) {
+    BF_REQUIRE(nside > 0, "nside");
+    return bf_shell_regrid_gather_emit_range(nside, 0, 12 * nside * nside, orig_map, pix_offsets, ws, ws_bytes,
+                                             window_host, stream);
 }
 
 extern "C" int bf_shell_regrid_gather_range(int64_t nside, const void *ws, size_t ws_bytes, const int *window_host,

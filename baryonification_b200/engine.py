@@ -142,6 +142,26 @@ class ShellEngine:
                 _lib.check(rc, "bf_shell_regrid_gather")
                 self.regrid_used = "gather"
                 return new_d
+        if method == "gather" and not whole and self.pix_last > self.pix_first:
+            # ring-band shard: PARTIAL sums of the shard's own sources over the destinations they can reach; the shards
+            # then exchange the boundary mass (sharding.exchange_boundary)
+            need = self.lib.bf_shell_regrid_gather_ws_bytes(self.nside)
+            if getattr(self, "_rg_ws", None) is None or self._rg_ws.numel() < need:
+                self._rg_ws = None
+                self._rg_ws = torch.empty(need, dtype=torch.uint8, device=self.dev)
+            win = (C.c_int * 3)()
+            rc = self.lib.bf_shell_regrid_gather_emit_range(self.nside, self.pix_first, self.pix_last, dv.ptr(orig_d),
+                                                            dv.ptr(off), dv.ptr(self._rg_ws), self._rg_ws.numel(), win,
+                                                            dv.stream_ptr())
+            self.regrid_window = tuple(win)
+            if rc != -3:
+                _lib.check(rc, "bf_shell_regrid_gather_emit_range")
+                reach = (max(win[1], -win[0]) + 1) * 4 * self.nside
+                _lib.call("bf_shell_regrid_gather_range", self.nside, dv.ptr(self._rg_ws), self._rg_ws.numel(), win,
+                          max(0, self.pix_first - reach), min(self.npix, self.pix_last + reach), dv.ptr(new_d),
+                          dv.stream_ptr())
+                self.regrid_used = "gather"
+                return new_d
         if method in ("gather", "sorted"):
             need = self.lib.bf_shell_regrid_sorted_ws_bytes(self.nside, self.pix_last - self.pix_first)
             if getattr(self, "_rg_ws", None) is None or self._rg_ws.numel() < need:

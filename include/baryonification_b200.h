@@ -158,6 +158,15 @@ int bf_shell_regrid_gather_emit(int64_t nside, const double *orig_map, const dou
                                 size_t ws_bytes, int *window_host, void *stream);
 int bf_shell_regrid_gather_range(int64_t nside, const void *ws, size_t ws_bytes, const int *window_host,
                                  int64_t dest_first, int64_t dest_last, double *new_map, void *stream);
+/* _emit for the sources pix_first <= p < pix_last only (orig_map / pix_offsets are that slice): what a ring-band shard
+ * runs.  Keys within BF_SHELL_GATHER_MARGIN_RINGS * 4 * nside pixels of the range are set to "no deposit", so that
+ * _range over the destinations the shard's sources can reach (its range widened by (max |dr| + 1) * 4 * nside pixels)
+ * yields the shard's PARTIAL sums: own destinations complete up to the neighbours' boundary mass, which the shards
+ * exchange and add (sharding.exchange_boundary).  BF_E_WINDOW also when the reach exceeds half the margin. */
+#define BF_SHELL_GATHER_MARGIN_RINGS 192
+int bf_shell_regrid_gather_emit_range(int64_t nside, int64_t pix_first, int64_t pix_last, const double *orig_map,
+                                      const double *pix_offsets, void *ws, size_t ws_bytes, int *window_host,
+                                      void *stream);
 
 /* ---- Grid runners (Map2DRunner.py) ---- */
 typedef struct {

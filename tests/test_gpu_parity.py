@@ -476,6 +476,42 @@ def test_shell_regrid_gather_is_bit_identical_to_the_sorted_serial_order_sum(gpu
     assert abs(got.sum() / orig.sum() - 1) < 1e-12
 
 
+@pytest.mark.parametrize("nside,parts,amp", [(64, 3, 0.01), (32, 5, 0.03), (128, 2, 0.002)])
+def test_shell_regrid_gather_partial_sums_of_ring_band_shards_add_up(gpu, nside, parts, amp):
+    """The N-GPU form: every ring-band shard emits ITS sources only (keys around it are "no deposit") and gathers over
+    the destinations they reach; the shards' partial maps add up to the whole-sphere result (bit-identical wherever a
+    destination's sources lie in one shard, to rounding at the shard boundaries)."""
+    import ctypes as C
+    import torch
+    from baryonification_b200 import _device as dv, _lib, sharding as sh
+    lib = _lib.load(require_cuda=True)
+    npix = 12 * nside * nside
+    rng = np.random.default_rng(nside + parts)
+    orig = rng.lognormal(size=npix)
+    orig[rng.random(npix) < 0.2] = 0.0
+    off = rng.normal(scale=amp, size=(npix, 3))
+    rc, want, _ = _shell_regrid("gather", nside, orig, off)
+    assert rc == 0
+    nb = lib.bf_shell_regrid_gather_ws_bytes(nside)
+    ws = torch.empty(nb, dtype=torch.uint8, device="cuda")
+    ws.fill_(0x5a)  # stale keys everywhere: the margin must be rewritten by every shard
+    total = np.zeros(npix)
+    for lo, hi in sh.band_split(nside, parts):
+        a, b = sh.band_pixel_range(nside, lo, hi)
+        od, fd, new = dv.to_dev(orig[a:b]), dv.to_dev(off[a:b]), dv.zeros(npix)
+        win = (C.c_int * 3)()
+        _lib.check(lib.bf_shell_regrid_gather_emit_range(nside, a, b, dv.ptr(od), dv.ptr(fd), dv.ptr(ws), nb, win,
+                                                         dv.stream_ptr()), "emit_range")
+        reach = (max(win[1], -win[0]) + 1) * 4 * nside
+        _lib.call("bf_shell_regrid_gather_range", nside, dv.ptr(ws), nb, win, max(0, a - reach), min(npix, b + reach),
+                  dv.ptr(new), dv.stream_ptr())
+        part = new.cpu().numpy()
+        assert abs(part.sum() / orig[a:b].sum() - 1) < 1e-12  # a shard's partial map holds exactly its own mass
+        total += part
+    assert np.allclose(total, want, rtol=1e-13, atol=0)
+    assert np.mean(total == want) > 0.9
+
+
 def test_shell_regrid_gather_window_fallback_and_runner_default(gpu):
     import baryonification_b200 as bf
     from baryonification_b200 import synthetic as syn
