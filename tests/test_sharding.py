@@ -123,6 +123,11 @@ def _paint_ranks(rank, world, nside):
     assert np.array_equal(full, want)
     off3 = torch.from_numpy(np.stack([want[first:last]] * 3, axis=1).copy())  # [n, 3] slices gather too
     assert np.array_equal(sh.gather_slices(off3, ranges).numpy()[:, 1], want)
+    # in place: the rank's slice already sits at its offset of the output (what the benchmark step does), ghosts around it
+    buf = torch.full((want.size,), float("nan"), dtype=torch.float64)
+    buf[first:last] = own
+    out = sh.gather_slices(buf[first:last], ranges, out=buf)
+    assert out.data_ptr() == buf.data_ptr() and np.array_equal(buf.numpy(), want)
 
 
 def test_pixel_owner_gather_is_exact():
