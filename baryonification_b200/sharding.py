@@ -92,26 +92,35 @@ def _world(group):
 
 
 def _touched_extent(acc, first, last, window=None):
-    """[lo, hi) of the non-zero entries of ``acc`` outside the own range [first, last) (lo = first / hi = last if none).
-    ``window``: look at that many entries next to the range first (displaced mass lands a few rings away) and scan
-    the whole array only if the window's far edge is itself non-zero."""
+    """``[lo, hi, widen]`` (int64 tensor on acc's device, NO host synchronisation): [lo, hi) is the extent of the non-zero
+    entries of ``acc`` outside the own range [first, last) (lo = first / hi = last if none).  ``window``: look at that
+    many entries next to the range only (displaced mass lands a few rings away); ``widen`` = 1 when the window's far
+    edge is itself non-zero, i.e. the whole array has to be scanned (``window=None``) to be sure."""
     n = acc.numel()
-    lo, hi = first, last
-    if first > 0:
-        a = 0 if window is None else max(0, first - window)
-        nz = torch.nonzero(acc[a:first])
-        if nz.numel():
-            lo = a + int(nz[0])
-            if lo == a and a > 0:
-                return _touched_extent(acc, first, last, None)
-    if last < n:
-        b = n if window is None else min(n, last + window)
-        nz = torch.nonzero(acc[last:b])
-        if nz.numel():
-            hi = last + int(nz[-1]) + 1
-            if hi == b and b < n:
-                return _touched_extent(acc, first, last, None)
-    return lo, hi
+    dev = acc.device
+    lo = torch.full((), first, dtype=torch.int64, device=dev)
+    hi = torch.full((), last, dtype=torch.int64, device=dev)
+    widen = torch.zeros((), dtype=torch.bool, device=dev)
+    flat = acc.reshape(n, -1) if acc.dim() > 1 else acc
+    a = 0 if window is None else max(0, first - window)
+    if first > a:
+        nz = flat[a:first] != 0
+        nz = nz.any(dim=1) if nz.dim() > 1 else nz
+        any_ = nz.any()
+        i0 = torch.argmax(nz.to(torch.uint8))  # index of the FIRST non-zero entry
+        lo = torch.where(any_, a + i0, lo)
+        if a > 0:
+            widen = widen | (any_ & (i0 == 0))
+    b = n if window is None else min(n, last + window)
+    if last < b:
+        nz = flat[last:b] != 0
+        nz = nz.any(dim=1) if nz.dim() > 1 else nz
+        any_ = nz.any()
+        i1 = (b - last - 1) - torch.argmax(nz.flip(0).to(torch.uint8))  # index of the LAST non-zero entry
+        hi = torch.where(any_, last + i1 + 1, hi)
+        if b < n:
+            widen = widen | (any_ & (i1 == b - last - 1))
+    return torch.stack([lo, hi, widen.to(torch.int64)])
 
 
 def exchange_boundary(acc, ranges, group=None, window=None):
@@ -121,21 +130,29 @@ def exchange_boundary(acc, ranges, group=None, window=None):
     ``ranges[rank] = [first, last)`` plus the few that landed outside (displaced mass crossing the shard
     boundary).  Every rank sends those outside parts to their owners; the owner adds what it receives to its own
     slice in SOURCE-RANK order (a fixed order: bit-reproducible).  Returns the finished own slice (a view of acc).
+    The touched extents are found on the device and reach the host with ONE read-back (after the all-gather); a rank
+    whose window turned out too narrow rescans its whole array and the extents are gathered once more.
     """
     rank, world = _world(group)
     first, last = ranges[rank]
     own = acc[first:last]
     if world == 1:
         return own
-    lo, hi = _touched_extent(acc, first, last, window)
-    ext = torch.tensor([lo, hi], dtype=torch.int64, device=acc.device)
-    all_ext = [torch.empty_like(ext) for _ in range(world)]
-    dist.all_gather(all_ext, ext, group=group)
-    all_ext = [tuple(int(v) for v in e.cpu()) for e in all_ext]
+
+    def gathered(ext):
+        parts = [torch.empty_like(ext) for _ in range(world)]
+        dist.all_gather(parts, ext, group=group)
+        return torch.stack(parts).cpu().tolist()
+
+    all_ext = gathered(_touched_extent(acc, first, last, window))
+    if any(e[2] for e in all_ext):  # (every rank sees the same flags, so every rank takes this branch)
+        mine = _touched_extent(acc, first, last, None) if all_ext[rank][2] else \
+            torch.tensor(all_ext[rank], dtype=torch.int64, device=acc.device)
+        all_ext = gathered(mine)
     ops, recvs = [], []
     for src in range(world):
         s_first, s_last = ranges[src]
-        s_lo, s_hi = all_ext[src]
+        s_lo, s_hi = all_ext[src][0], all_ext[src][1]
         for dst in range(world):
             if dst == src:
                 continue

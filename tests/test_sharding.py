@@ -51,6 +51,27 @@ def test_band_split_covers_sphere_with_balanced_pixel_counts(nside, world):
         assert n.max() / n.min() < 1.2
 
 
+def test_touched_extent_matches_brute_force_without_host_sync():
+    """[lo, hi, widen] of the device-side extent search: equal to a numpy scan; ``widen`` exactly when the window's far
+    edge is non-zero (the whole array must then be scanned)."""
+    rng = np.random.default_rng(4)
+    n = 400
+    for trial in range(200):
+        first, last = sorted(rng.integers(0, n + 1, 2))
+        acc = np.zeros(n)
+        k = rng.integers(0, 6)
+        acc[rng.integers(0, n, k)] = rng.normal(size=k)
+        acc[first:last] = 1.0
+        window = [None, 1, 7, 50, 1000][trial % 5]
+        lo, hi, widen = sh._touched_extent(torch.from_numpy(acc), int(first), int(last), window).tolist()
+        a = 0 if window is None else max(0, first - window)
+        b = n if window is None else min(n, last + window)
+        below, above = np.flatnonzero(acc[a:first]) + a, np.flatnonzero(acc[last:b]) + last
+        assert lo == (below[0] if below.size else first) and hi == (above[-1] + 1 if above.size else last)
+        want_widen = (below.size > 0 and below[0] == a and a > 0) or (above.size > 0 and above[-1] == b - 1 and b < n)
+        assert bool(widen) == bool(want_widen)
+
+
 def test_index_split():
     assert sh.index_split(10, 3) == [(0, 3), (3, 6), (6, 10)]
     assert sh.index_split(2, 4) == [(0, 0), (0, 1), (1, 1), (1, 2)]
