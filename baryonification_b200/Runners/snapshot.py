@@ -143,7 +143,8 @@ class BaryonifySnapshot(DefaultRunnerSnapshot):
         st["rows"] = rows = st["table"].collapse(t["z_in"], t["M_in"])
         st["desc"] = desc = _lib.SnapHalos(t["pos"].data_ptr(), t["Rq"].data_ptr(), t["cut"].data_ptr(),
                                            t["lnr_shift"].data_ptr(), rows.data_ptr(), nh)
-        for _ in range(2):  # counting pass first (exact size), then the real one
+        for _ in range(24):  # counting pass first (exact size), then the real one; a coarser grid when the list is too long
+            ng = st["ng"]
             need = max(lib.bf_snap_ws_bytes(dim, nh, L, ng, st["max_entries"]), 256)
             if st["ws"] is None or st["ws"].numel() < need:
                 st["ws"] = None
@@ -153,6 +154,9 @@ class BaryonifySnapshot(DefaultRunnerSnapshot):
                                        C.byref(n), dv.stream_ptr())
             if rc == -2 and n.value > st["max_entries"]:
                 st["max_entries"] = n.value
+                continue
+            if rc == -4 and ng > 1:  # BF_E_CAPACITY: >= 2^25 (cell, halo) entries; the list shrinks ~ ng^dim
+                st["ng"], st["max_entries"] = max(1, ng // 2), 0
                 continue
             _lib.check(rc, "bf_snap_bin_halos")
             break
@@ -164,6 +168,33 @@ class BaryonifySnapshot(DefaultRunnerSnapshot):
     def _setup(self, dev):
         """Table, per-halo arrays, (z, M) collapse and halo binning into the periodic grid."""
         return self._bin(self._upload(dev), dev)
+
+    def pair_list(self):
+        """The (particle, halo) pairs the run evaluates -- the union of the reference's per-halo
+        ``tree.query_ball_point`` answers (SnapshotRunner.py:219 / :234) -- as a sorted uint64 array of
+        ``particle << 32 | halo``.  A diagnostic for the parity tests; ``process()`` does not build it."""
+        dev = dv.device(self.device)
+        cat = self.ParticleSnapshot.cat
+        with torch.cuda.device(dev):
+            st = self._setup(dev)
+            dim, s = st["dim"], st["s"]
+            names = ("x", "y", "z")[:dim]
+            xin = [dv.to_dev(cat[k], dev=dev) for k in names]
+            xout = [torch.empty_like(v) for v in xin]
+            count = torch.zeros(1, dtype=torch.int64, device=dev)
+            cap = 0
+            for _ in range(2):  # first pass counts, second pass stores
+                pairs = torch.empty(max(cap, 1), dtype=torch.int64, device=dev)
+                _lib.call("bf_snap_pair_list", dim, xin[0].numel(), dv.ptr(xin[0]), dv.ptr(xin[1]),
+                          dv.ptr(xin[2] if dim == 3 else None), st["L"], float(s["a"]), C.byref(st["desc"]),
+                          C.byref(st["table"].desc), st["ng"], dv.ptr(st["ws"]), dv.ptr(xout[0]), dv.ptr(xout[1]),
+                          dv.ptr(xout[2] if dim == 3 else None), dv.ptr(pairs), cap, dv.ptr(count), dv.stream_ptr())
+                n = int(count.item())
+                if n <= cap:
+                    break
+                cap = n
+            self.npairs = n
+            return np.sort(pairs[:n].cpu().numpy().view(np.uint64))
 
     def process(self):
         dev = dv.device(self.device)

@@ -114,6 +114,9 @@ _SIGS = {
                                     C.c_void_p]),
     "bf_snap_displace": (C.c_int, [C.c_int, _i64, _dbl_p, _dbl_p, _dbl_p, C.c_double, C.c_double, _P(SnapHalos),
                                    _P(Table), _i64, C.c_void_p, _dbl_p, _dbl_p, _dbl_p, _dbl_p, C.c_void_p]),
+    "bf_snap_pair_list": (C.c_int, [C.c_int, _i64, _dbl_p, _dbl_p, _dbl_p, C.c_double, C.c_double, _P(SnapHalos),
+                                    _P(Table), _i64, C.c_void_p, _dbl_p, _dbl_p, _dbl_p, C.c_void_p, _i64, C.c_void_p,
+                                    C.c_void_p]),
     "bf_snap_displace_records": (C.c_int, [C.c_int, _i64, C.c_void_p, C.c_double, C.c_double, _P(SnapHalos), _P(Table),
                                            _i64, C.c_void_p, C.c_void_p, _dbl_p, C.c_void_p]),
     "bf_pk_ngp_deposit": (C.c_int, [_i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p, C.c_double, _i64, _dbl_p, C.c_void_p]),

@@ -48,13 +48,18 @@ struct gather_args {
     u64 *npairs;
 };
 
+// Pair constants of one staged candidate: (c0, c1 | c2, ln(D/a) | cut^2, a/D | row pointer, -), read with four 16-byte
+// shared-memory loads.  The stride of 10 doubles (80 B = 20 banks) spreads the records of 8 different candidates over all
+// 32 banks, so the per-lane reads of the partial path rarely conflict; the whole-strip path reads ONE record per warp
+// (a broadcast).
+#define GT_CSTRIDE 10
 struct gather_smem {
-    double c0[GT_CMAX], c1[GT_CMAX], c2[GT_CMAX], lnDa[GT_CMAX], cut2[GT_CMAX], aD[GT_CMAX];
-    const double *row[GT_CMAX];
+    double cand[GT_CMAX][GT_CSTRIDE];
     double phi[GT_CMAX], z0[GT_CMAX], xa[GT_CMAX], cosr[GT_CMAX];
     int irmin[GT_CMAX], irmax[GT_CMAX], wn[GT_CMAX], ws[GT_CMAX];
     int2 rng[GT_WARPS][GT_CMAX];
     unsigned hits[GT_WARPS][GT_CMAX / 32][32];  // [warp][candidate word][lane]: bit c = candidate 32*word+c hits my pixel
+    unsigned full[GT_WARPS][GT_CMAX / 32];      // [warp][candidate word]: bit c = candidate 32*word+c covers the WHOLE strip
     u64 mbar, mbar_pad;                         // completion barrier of the TMA bulk copy of the constant tables
 };
 
@@ -86,47 +91,77 @@ __device__ __forceinline__ unsigned warp_transpose32(unsigned x, int lane) {
     return x;
 }
 
-// One (pixel, candidate) pair: contribution to the pixel's sum (paint: p[0]; baryonify: the unit-vector shift p[0..2]).
+// ln(x) as bf_fastlog with the log1p series cut at degree 5: |r| <= 2^-8, so the truncation r^6/6 < 6e-16 stays at the
+// rounding level of the table coordinate 0.5 ln d2 + ln(D/a) (whose magnitude is 1..10).
+__device__ __forceinline__ double gather_log(const double2 *__restrict__ tab, double x) {
+    const int hi = __double2hiint(x);
+    const int e = (hi >> 20) - 1023;
+    const double m = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(x));
+    const double2 t = tab[(hi >> 13) & (BF_LOGTAB - 1)];
+    const double r = fma(m, t.x, -1.0);
+    double p = fma(r, bf_kc[1], -0.25);
+    p = fma(r, p, bf_kc[2]);
+    p = fma(r, p, -0.5);
+    p = fma(r, p, 1.0);
+    return fma((double)e, bf_kc[3], fma(r, p, t.y));
+}
+
+// One (pixel, candidate) pair, added to the pixel's running sums.  paint: acc[0] += P.  baryonify: the unit-vector
+// shift of the pair is v g + e (1 + g) delta; v is the pixel's own vector, so acc[3] collects sum g and acc[0..2] collect
+// sum e (1 + g) delta (one FMA per component) -- the pixel's shift is acc[0..2] + v acc[3], formed once at the end.
+// fp64 instructions are what bounds this kernel, so tests that do not need fp64 arithmetic (finite?, |q| > 1e-3,
+// 0 <= t < 1 - 2^-50) look at the bit patterns with integer instructions instead.
 template <int MODE>
 __device__ __forceinline__ void gather_pair(const gather_smem &sm, int c, const double v[3], const bf_raxis &ax,
                                             const double2 *__restrict__ gi_s, const double2 *__restrict__ logtab,
-                                            double tt_max, double p[3]) {
-    double dx = v[0] - sm.c0[c], dy = v[1] - sm.c1[c], dz = v[2] - sm.c2[c];
-    double d2 = fma(dz, dz, fma(dy, dy, dx * dx));
-    double x = fma(0.5, bf_fastlog(logtab, d2), sm.lnDa[c]);
-    // Table cell, branch-free up to the (rare) exact search, so that the two row loads are in flight while the
-    // reciprocal square root and the cut are evaluated.  Uniform-grid guess, accepted when 0 <= tt < 1 - 2^-50, which
-    // PROVES g[k] <= x < g[k+1] (tt >= 0 iff x >= g[k]; x >= g[k+1] would give tt >= 1 - 4 ulp); out of range
-    // (fill_value NaN) is decided by `inr`.
-    const bool inr = x >= ax.g0 && x <= ax.glast;
+                                            double acc[4]) {
+    const double2 *__restrict__ cq = reinterpret_cast<const double2 *>(sm.cand[c]);
+    const double2 q0 = cq[0], q1 = cq[1];  // (c0, c1), (c2, ln(D/a))
+    const double dx = v[0] - q0.x, dy = v[1] - q0.y, dz = v[2] - q1.x;
+    const double d2 = fma(dz, dz, fma(dy, dy, dx * dx));
+    const double x = fma(0.5, gather_log(logtab, d2), q1.y);
+    // Table cell: uniform-grid guess, accepted when 0 <= tt < 1 - 2^-50, which PROVES g[k] <= x < g[k+1] (tt >= 0 iff
+    // x >= g[k]; x >= g[k+1] would give tt >= 1 - 4 ulp) and with it that x lies inside the table.  For tt >= 0 the
+    // order of doubles is the order of their bit patterns; negative tt and NaN have larger patterns, so one unsigned
+    // compare decides.  Everything else -- rounding at a node, a non-uniform axis, x == glast, x outside the table
+    // (fill_value NaN) -- takes the exact route.
     int k = (int)((x - ax.g0) * ax.inv_dx);
     k = max(0, min(k, ax.nr - 2));
     double2 gi = gi_s[k];
     double tt = (x - gi.x) * gi.y;
-    if (inr && !(tt >= 0.0 && tt < tt_max)) {  // rounding at a node / non-uniform axis / x == glast
-        k = bf_find_cell(ax, x);
-        gi = gi_s[k];
-        tt = (x - gi.x) * gi.y;
+    bool inr = true;
+    if ((u64)__double_as_longlong(tt) >= 0x3feffffffffffff8ull) {  // (bits of 1 - 2^-50)
+        inr = x >= ax.g0 && x <= ax.glast;
+        if (inr) {
+            k = bf_find_cell(ax, x);
+            gi = gi_s[k];
+            tt = (x - gi.x) * gi.y;
+        }
     }
-    const double *row = sm.row[c] + k;
+    const double2 q3 = cq[3];
+    const double *row = reinterpret_cast<const double *>(__double_as_longlong(q3.x)) + k;
     const double r0 = __ldg(row), r1 = __ldg(row + 1);
     if (MODE == 0) {
-        double val = fma(r1, tt, r0 * (1.0 - tt));
-        double P = exp(inr ? val : nan(""));
-        p[0] = bf_finite(P) ? P : 0.0;
+        // the two-product form keeps scipy's propagation through zero weights (0 * -inf = NaN -> 0, Tabulate.py:237)
+        const double val = fma(r1, tt, r0 * (1.0 - tt));
+        const double P = exp(inr ? val : nan(""));
+        if ((__double2hiint(P) & 0x7ff00000) != 0x7ff00000) acc[0] += P;  // finite (HealpixRunner.py:442)
     } else {
-        const double sc = sm.aD[c] * bf_rsqrt(d2);
-        const bool use = inr && d2 < sm.cut2[c];  // NaN fill / BaryonCorrection.py:381-382: both end as 0
-        double val = fma(r1, tt, r0 * (1.0 - tt));
-        double e = (use ? val : 0.0) * sc;
-        if (!bf_finite(e)) e = 0.0;                   // HealpixRunner.py:323
-        double q = e * d2 * (1.0 + e);
+        const double2 q2 = cq[2];  // (cut^2, a/D)
+        const double sc = q2.y * bf_rsqrt(d2);
+        const bool use = inr && d2 < q2.x;  // NaN fill / BaryonCorrection.py:381-382: both end as 0
+        // (an inf or NaN anywhere in the cell gives a non-finite e in either form of the lerp, which ends as 0 below)
+        double e = fma(tt, r1 - r0, r0) * sc;
+        if (!use || (__double2hiint(e) & 0x7ff00000) == 0x7ff00000) e = 0.0;  // HealpixRunner.py:323
+        const double ed = e * d2;
+        const double q = fma(e, ed, ed);  // e d2 (1 + e)
         double gg = q * fma(q, fma(q, fma(q, bf_kc[5], bf_kc[6]), bf_kc[4]), -0.5);  // (1+q)^-1/2 - 1
-        if (fabs(q) > bf_kc[7]) gg = rsqrt(1.0 + q) - 1.0;  // pixel (almost) on the halo centre
-        double ef = fma(e, gg, e);
-        p[0] = fma(v[0], gg, ef * dx);
-        p[1] = fma(v[1], gg, ef * dy);
-        p[2] = fma(v[2], gg, ef * dz);
+        if ((__double2hiint(q) & 0x7fffffff) > 0x3f50624d) gg = rsqrt(1.0 + q) - 1.0;  // |q| > 1e-3: pixel (almost) on the centre
+        const double ef = fma(e, gg, e);
+        acc[3] += gg;
+        acc[0] = fma(ef, dx, acc[0]);
+        acc[1] = fma(ef, dy, acc[1]);
+        acc[2] = fma(ef, dz, acc[2]);
     }
 }
 
@@ -172,7 +207,6 @@ __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather
     __syncthreads();
     if (t == 0) bf_tma_load_1d(logtab, A.aux, A.aux_bytes, &sm.mbar);
     bf_mbar_wait(&sm.mbar, 0);
-    const double tt_max = 1.0 - 0x1p-50;
     bf_raxis ax = A.ax;
     ax.g = g_s;
 
@@ -184,12 +218,13 @@ __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather
             i64 j = (i64)(A.keys[cb + t] & 0xffffffffull);
             double c[3] = {A.S.vec[3 * j], A.S.vec[3 * j + 1], A.S.vec[3 * j + 2]};
             double D = A.S.D[j], a = A.S.a[j];
-            sm.c0[t] = c[0]; sm.c1[t] = c[1]; sm.c2[t] = c[2];
-            sm.aD[t] = a / D;
-            sm.lnDa[t] = log(D / a) - ((MODE == 1) ? A.S.lnr_shift[j] : 0.0);
+            double *cr = sm.cand[t];
+            cr[0] = c[0]; cr[1] = c[1]; cr[2] = c[2];
+            cr[3] = log(D / a) - ((MODE == 1) ? A.S.lnr_shift[j] : 0.0);
             double ct = (MODE == 1) ? A.S.cut[j] * (a / D) : 0.0;
-            sm.cut2[t] = ct * ct;
-            sm.row[t] = A.S.rows + j * (i64)A.ax.nr;
+            cr[4] = ct * ct;
+            cr[5] = a / D;
+            cr[6] = __longlong_as_double((long long)(A.S.rows + j * (i64)A.ax.nr));
             bf_disc d = bfh_disc_setup(h, c, A.S.radius[j]);
             sm.phi[t] = d.phi; sm.z0[t] = d.z0; sm.xa[t] = d.xa; sm.cosr[t] = d.cosr;
             sm.irmin[t] = (int)d.irmin; sm.irmax[t] = (int)d.irmax;
@@ -225,16 +260,34 @@ __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather
                     bfh_ringpix2loc(h, iz, (i64)ip + 1, z, phi, sth, have);
                     bfh_loc2vec(z, phi, sth, have, v);
                 }
-                double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0;
-                // hit matrix of this strip: lane c builds candidate c's lane mask from its range, the warp
-                // transposes it, so every lane ends up with one bit per candidate for ITS pixel
+                double acc[4] = {0.0, 0.0, 0.0, 0.0};
+                // hit matrix of this strip: lane c builds candidate c's lane mask from its range.  Candidates that cover
+                // the WHOLE strip (the common case: discs are wider than 32 pixels) are set aside in a warp-uniform word
+                // and evaluated by all 32 lanes together -- no transpose, no vote, no bit scan, and the candidate's
+                // constants are one broadcast read.  The remaining masks are transposed, so every lane ends up with one
+                // bit per candidate for ITS pixel.
                 const int nw = (nc + 31) >> 5;
                 for (int kw = 0; kw < nw; ++kw) {
                     const int c = kw * 32 + lane;
                     unsigned m = (c < nc) ? lanes_of_range(sm.rng[w][c], ip0 + s * 32) : 0u;
-                    sm.hits[w][kw][lane] = warp_transpose32(m, lane);
+                    const unsigned fw = __ballot_sync(0xffffffffu, m == 0xffffffffu);
+                    if (m == 0xffffffffu) m = 0u;
+                    const bool any_part = __any_sync(0xffffffffu, m != 0u);
+                    sm.hits[w][kw][lane] = any_part ? warp_transpose32(m, lane) : 0u;
+                    if (lane == 0) sm.full[w][kw] = fw;
                 }
                 __syncwarp();
+                // whole-strip candidates: one candidate at a time for the whole warp
+                for (int kw = 0; kw < nw; ++kw) {
+                    unsigned fm = sm.full[w][kw];
+                    my_pairs32 += __popc(fm);
+                    while (fm) {
+                        const int c = kw * 32 + __ffs((int)fm) - 1;
+                        fm &= fm - 1u;
+                        gather_pair<MODE>(sm, c, v, ax, gi_s, logtab, acc);
+                    }
+                }
+                // partial candidates: every lane pops ITS bits (lanes work on different candidates at the same time)
                 int kw = 0;
                 unsigned hm = valid ? sm.hits[w][0][lane] : 0u;
                 my_pairs32 += __popc(hm);
@@ -248,11 +301,14 @@ __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather
                     if (act) {
                         const int c = kw * 32 + __ffs((int)hm) - 1;
                         hm &= hm - 1u;
-                        double p1[3];
-                        gather_pair<MODE>(sm, c, v, ax, gi_s, logtab, tt_max, p1);
-                        acc0 += p1[0];
-                        if (MODE == 1) { acc1 += p1[1]; acc2 += p1[2]; }
+                        gather_pair<MODE>(sm, c, v, ax, gi_s, logtab, acc);
                     }
+                }
+                double acc0 = acc[0], acc1 = 0.0, acc2 = 0.0;
+                if (MODE == 1) {
+                    acc0 = fma(v[0], acc[3], acc[0]);
+                    acc1 = fma(v[1], acc[3], acc[1]);
+                    acc2 = fma(v[2], acc[3], acc[2]);
                 }
                 if (valid) {
                     double *o = A.out + (sp + ip - A.pix_base) * ncomp;

@@ -230,6 +230,9 @@ struct snap_args {
     const double2 *hpar;
     const snap_hdr *hdr;
     u64 *npairs;
+    u64 *pair_list;    // optional (bf_snap_pair_list): (particle << 32 | halo) of every pair, in arrival order
+    u64 *pair_cursor;
+    i64 pair_cap;
 };
 
 struct __align__(16) snap_q {  // one queued pair: min-image separation in, displacement vector out (in place)
@@ -358,6 +361,10 @@ __device__ __forceinline__ int snap_drain(const snap_args &A, const int *__restr
         for (int q = lane; q < nround; q += 32) {  // dense evaluation: lane q evaluates pair q
             snap_q &e = wq[q];
             const int j = e.j;
+            if (A.pair_list) {  // the KD-tree's answer, for the parity tests: which particle met which halo
+                const u64 slot = atomicAdd(A.pair_cursor, 1ull);
+                if ((i64)slot < A.pair_cap) A.pair_list[slot] = ((u64)(chunk0 + act[e.src].idx) << 32) | (u64)j;
+            }
             double dx[3] = {e.v[0], e.v[1], e.v[2]};
             double dsq = dx[0] * dx[0] + dx[1] * dx[1];
             if (DIM == 3) dsq += dx[2] * dx[2];
@@ -495,7 +502,8 @@ extern "C" int bf_snap_bin_halos(int dim, double L, int64_t ng, const bf_snap_ha
     BF_REQUIRE(H && H->nh >= 0 && H->nh < (1ll << 31), "halo record");
     BF_REQUIRE(H->nh == 0 || (H->pos && H->Rq), "null per-halo array");
     BF_REQUIRE(ws && nentries_host, "null outputs");
-    BF_REQUIRE(max_entries >= 0 && max_entries < (1ll << 25), "max_entries must be < 2^25 (use fewer cells)");
+    BF_REQUIRE(max_entries >= 0, "max_entries");
+    if (max_entries >= (1ll << 25)) max_entries = (1ll << 25) - 1;  // (more can never be used: BF_E_CAPACITY below)
     snap_grid G = make_grid(dim, L, ng);
     snap_ws w = snap_layout(ws, G, H->nh, max_entries);
     if (ws_bytes < w.total) {
@@ -521,7 +529,7 @@ extern "C" int bf_snap_bin_halos(int dim, double L, int64_t ng, const bf_snap_ha
     *nentries_host = total;
     if (total >= (1ll << 25)) {
         bf_set_error("bf_snap_bin_halos: %lld (cell, halo) entries do not fit the cell table; use a smaller ng", (long long)total);
-        return BF_E_INVALID;
+        return BF_E_CAPACITY;
     }
     if (total > max_entries) {
         bf_set_error("bf_snap_bin_halos: %lld entries exceed max_entries %lld", (long long)total, (long long)max_entries);
@@ -583,6 +591,23 @@ extern "C" int bf_snap_displace(int dim, int64_t np, const double *x, const doub
     A.rec = nullptr; A.rec_out = nullptr;
     A.a = a;
     A.npairs = npairs;
+    A.pair_list = nullptr; A.pair_cursor = nullptr; A.pair_cap = 0;
+    return snap_launch(dim, np, A, L, ng, H, T, ws, false, stream);
+}
+
+extern "C" int bf_snap_pair_list(int dim, int64_t np, const double *x, const double *y, const double *z, double L,
+                                 double a, const bf_snap_halos *H, const bf_table *T, int64_t ng, const void *ws,
+                                 double *xo, double *yo, double *zo, unsigned long long *pairs, int64_t pair_cap,
+                                 unsigned long long *pair_count, void *stream) {
+    BF_REQUIRE(np == 0 || (x && y && xo && yo && (dim == 2 || (z && zo))), "null particle array");
+    BF_REQUIRE(pairs && pair_count && pair_cap >= 0 && np < (1ll << 32), "pair list");
+    snap_args A;
+    A.x = x; A.y = y; A.z = z; A.xo = xo; A.yo = yo; A.zo = zo;
+    A.rec = nullptr; A.rec_out = nullptr;
+    A.a = a;
+    A.npairs = nullptr;
+    A.pair_list = pairs; A.pair_cursor = pair_count; A.pair_cap = pair_cap;
+    BF_CUDA_OK(cudaMemsetAsync(pair_count, 0, sizeof(unsigned long long), (cudaStream_t)stream));
     return snap_launch(dim, np, A, L, ng, H, T, ws, false, stream);
 }
 
@@ -596,5 +621,6 @@ extern "C" int bf_snap_displace_records(int dim, int64_t np, const void *cat, do
     A.rec = (const double4 *)cat; A.rec_out = (double4 *)cat_out;
     A.a = a;
     A.npairs = npairs;
+    A.pair_list = nullptr; A.pair_cursor = nullptr; A.pair_cap = 0;
     return snap_launch(dim, np, A, L, ng, H, T, ws, true, stream);
 }

@@ -26,6 +26,7 @@ extern "C" {
 #define BF_OK 0
 #define BF_E_INVALID (-1)   /* bad argument */
 #define BF_E_WORKSPACE (-2) /* workspace too small */
+#define BF_E_CAPACITY (-4)  /* bf_snap_bin_halos: >= 2^25 (cell, halo) entries at this `ng`; call again with fewer cells */
 #define BF_E_WINDOW (-3)    /* bf_{grid,shell}_regrid_gather: displacement window too wide, use the _sorted variant */
 
 const char *bf_last_error(void);
@@ -248,7 +249,8 @@ typedef struct {
 int64_t bf_snap_grid_cells(int dim, double L, double Rq_mean);
 size_t bf_snap_ws_bytes(int dim, int64_t nh, double L, int64_t ng, int64_t max_entries);
 /* Same protocol as bf_shell_bin_halos: *nentries_host = exact number of (cell, halo) entries; BF_E_WORKSPACE when
- * it exceeds max_entries (call again with a workspace sized for it).  Synchronises `stream` once. */
+ * it exceeds max_entries (call again with a workspace sized for it); BF_E_CAPACITY when the count reaches 2^25, the
+ * limit of the packed cell table (call again with a smaller `ng`: the list shrinks ~ ng^dim).  Synchronises `stream` once. */
 int bf_snap_bin_halos(int dim, double L, int64_t ng, const bf_snap_halos *h_host, int64_t max_entries, void *ws,
                       size_t ws_bytes, int64_t *nentries_host, void *stream);
 /* Periodic ball query + displacement (SnapshotRunner.py:205-247) as a particle-centric gather over the binned
@@ -256,6 +258,14 @@ int bf_snap_bin_halos(int dim, double L, int64_t ng, const bf_snap_halos *h_host
 int bf_snap_displace(int dim, int64_t np, const double *x, const double *y, const double *z, double L, double a,
                      const bf_snap_halos *h_host, const bf_table *tab_host, int64_t ng, const void *ws, double *xo,
                      double *yo, double *zo, unsigned long long *npairs, void *stream);
+/* bf_snap_displace that also reports WHICH pairs it evaluated -- the answer of the KD-tree's query_ball_point
+ * (SnapshotRunner.py:219 / :234) turned inside out: pairs[k] = (particle index << 32) | halo index for every (particle,
+ * halo) with min-image distance <= R_q, in no particular order (sort to compare); *pair_count (device) = how many there
+ * are, of which the first min(count, pair_cap) were stored.  Needs np < 2^32.  For parity tests and diagnostics. */
+int bf_snap_pair_list(int dim, int64_t np, const double *x, const double *y, const double *z, double L, double a,
+                      const bf_snap_halos *h_host, const bf_table *tab_host, int64_t ng, const void *ws, double *xo,
+                      double *yo, double *zo, unsigned long long *pairs, int64_t pair_cap,
+                      unsigned long long *pair_count, void *stream);
 /* Same on the reference's own particle records: ParticleSnapshot.cat is a structured array of float64
  * (M, x, y, z) (utils/io.py:581-589; z is a filler in 2-D).  cat / cat_out are [np] 32-byte records, 16-byte
  * aligned; cat_out receives M unchanged and the displaced, wrapped coordinates (new_cat, SnapshotRunner.py:250). */

@@ -47,6 +47,9 @@ def _lib():
         L.bfo_snapshot_offsets.argtypes = ([C.c_int, _i64, _dp, C.c_double, _i64, _dp, _dp, C.c_double,
                                             _dp, _dp, _dp, _dp] + _TAB + [_dp, C.c_int])
         L.bfo_snapshot_apply.argtypes = [_i64, _dp, _dp, C.c_double, _dp]
+        L.bfo_snapshot_pair_list.restype = _i64
+        L.bfo_snapshot_pair_list.argtypes = [C.c_int, _i64, _dp, C.c_double, _i64, _dp, _dp,
+                                             np.ctypeslib.ndpointer(dtype=np.uint64, flags="C_CONTIGUOUS"), _i64, C.c_int]
         L.bfo_set_extra_axes.argtypes = [C.c_int, _dp, _ip, _dp]
         _ready = True
     return L
@@ -392,6 +395,28 @@ class BaryonifySnapshot:
                                                   np.log(1 / a), _log_native(M), cut, shift, *T.args(), off,
                                                   self.nthreads)
         return off
+
+    def pair_list(self):
+        """Sorted uint64 array of ``particle << 32 | halo`` for every pair of the per-halo ``tree.query_ball_point``
+        calls (SnapshotRunner.py:219 / :234), by brute force over all particles (no cell list, no tree)."""
+        ccl, c = _ccl(), self.cosmo
+        cosmo = ccl.Cosmology(Omega_c=c["Omega_m"] - c["Omega_b"], Omega_b=c["Omega_b"], h=c["h"],
+                              sigma8=c["sigma8"], n_s=c["n_s"], matter_power_spectrum="linear")
+        S, cat = self.ParticleSnapshot, self.HaloNDCatalog.cat
+        dim = 2 if S.is2D else 3
+        a_j = 1 / (1 + self.HaloNDCatalog.redshift)
+        Rq = np.array([np.clip(self.epsilon_max * self.mass_def.get_radius(cosmo, cat["M"][j], a_j) / a_j, 0, S.L / 2)
+                       for j in range(cat.size)], dtype=np.float64)
+        hpos = _c(np.stack([np.asarray(cat[k], dtype=np.float64) for k in ("x", "y", "z")[:dim]], axis=1))
+        part = _c(np.stack([S.cat[k] for k in ("x", "y", "z")[:dim]], axis=1))
+        pairs, cap = np.empty(1, dtype=np.uint64), 0
+        for _ in range(2):
+            n = _lib().bfo_snapshot_pair_list(dim, part.shape[0], part, float(S.L), cat.size, hpos, Rq, pairs, cap,
+                                              self.nthreads)
+            if n <= cap:
+                break
+            pairs, cap = np.empty(n, dtype=np.uint64), n
+        return np.sort(pairs[:n])
 
     def process(self):
         S = self.ParticleSnapshot

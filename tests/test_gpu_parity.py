@@ -856,3 +856,29 @@ def test_delta_pk_suppression_of_a_baryonified_snapshot(gpu):
         ok = kc > 0
         assert np.allclose(res[f"Factor{f}"]["S"][ok], (PB / PD)[ok], rtol=1e-10)
         assert np.allclose(res[f"Factor{f}"]["k"][ok], k[ok], rtol=1e-13)
+
+
+@pytest.mark.gpu
+def test_paint_split_join_sum_equals_one_pass(gpu):
+    """The SplitJoinParallel property (utils/Parallelize.py:237-275, :316-318): shuffle the catalogue with seed 42, cut
+    it into njobs runs of ceil(N / njobs) halos, paint each onto a zero map with a re-instantiated Runner (positional
+    arguments, verbose=False) and np.sum the maps == one pass over the whole catalogue."""
+    import baryonification_b200 as bf
+    from baryonification_b200 import synthetic as syn
+    cfg = syn.config_shell(nside=64, nhalo=1501, zero_map=True)
+    runner = bf.PaintProfilesShell(cfg["catalog"], cfg["field"], 20.0, cfg["paint_model"], verbose=False)
+    want = runner.process()
+    njobs, n = 4, len(cfg["catalog"].cat)
+    per = int(np.ceil(n / njobs))
+    shuffled = runner.HaloLightConeCatalog[np.random.default_rng(42).choice(n, size=n, replace=False)]
+    empty = type(runner.LightconeShell)(map=np.zeros_like(runner.LightconeShell.map), cosmo=runner.cosmo)
+    outs, pairs = [], 0
+    for i in range(njobs):
+        sub = type(runner)(shuffled[i * per:(i + 1) * per], empty, runner.epsilon_max, runner.model,
+                           runner.use_ellipticity, runner.mass_def, verbose=False)
+        outs.append(sub.process())
+        pairs += sub.npairs
+    got = np.sum(outs, axis=0)
+    assert pairs == runner.npairs
+    assert np.array_equal(got != 0, want != 0)
+    assert relmax(got, want) < 1e-13
