@@ -18,6 +18,8 @@ from ..tables import displacement_host_table, profile_host_table
 
 __all__ = ["DefaultRunnerGrid", "BaryonifyGrid", "PaintProfilesGrid"]
 
+GRID_BARYONIFY, GRID_PAINT = 0, 1  # BF_GRID_MODE_* of the C ABI (the shell entries number them the other way round)
+
 
 class DefaultRunnerGrid:
     def __init__(self, HaloNDCatalog, GriddedMap, epsilon_max, model, use_ellipticity=False, mass_def=None,
@@ -118,7 +120,7 @@ class BaryonifyGrid(DefaultRunnerGrid):
         torch.cuda.synchronize(dev)
         self.timings["setup"] = time.perf_counter() - t0
         t0 = time.perf_counter()
-        self._accumulate(0, s, desc, bins, table, off, cnt, dev)
+        self._accumulate(GRID_BARYONIFY, s, desc, bins, table, off, cnt, dev)
         self.timings["accumulate"] = time.perf_counter() - t0
         del keep
         return off
@@ -203,7 +205,7 @@ class PaintProfilesGrid(DefaultRunnerGrid):
         cnt = dv.pair_counter(dev)
         if after_run is not None:
             after_run(None, None, out)  # hand the accumulator to the caller's read-back
-        self._accumulate(1, s, desc, bins, table, out, cnt, dev, row_runs, after_run)
+        self._accumulate(GRID_PAINT, s, desc, bins, table, out, cnt, dev, row_runs, after_run)
         del keep
         return out
 

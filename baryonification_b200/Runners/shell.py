@@ -62,11 +62,13 @@ class DefaultRunner:
         baryonify = mode == engine.BARYONIFY
         self._check_keys(baryonify)
         t0 = time.perf_counter()
+        self._progress("host set-up of %d halos" % len(self.HaloLightConeCatalog.cat))
         htab = displacement_host_table(self.model) if baryonify else profile_host_table(self.model, "2D")
         s = host.shell_scalars(self.HaloLightConeCatalog, self.cosmo, self.mass_def, self.epsilon_max, self.model,
                                baryonify)
         s["extras"] = host.property_columns(self.HaloLightConeCatalog.cat, self.model)
         self.timings["host_setup"] = time.perf_counter() - t0
+        self._progress("upload, (z, M) table collapse, halo binning into sky cells")
         after = getattr(self, "_after_host", None)
         if after is not None:  # e.g. start the map upload now: the host cores are free while the GPU works
             after()
@@ -144,6 +146,13 @@ class DefaultRunner:
         self.timings["pairs_pipelined"] = time.perf_counter() - t00
         return state["eng"], state["out"]
 
+    def _progress(self, what):
+        """Per-stage progress lines under the reference's ``verbose`` flag (its tqdm bar over halos, HealpixRunner.py:291,
+        has no per-halo counterpart here: the loop is a handful of kernel launches)."""
+        if self.verbose:
+            import sys
+            print("[%s] %s" % (type(self).__name__, what), file=sys.stderr, flush=True)
+
     def _tick(self, name, t0, dev):
         torch.cuda.synchronize(dev)
         self.timings[name] = time.perf_counter() - t0
@@ -157,10 +166,42 @@ class BaryonifyShell(DefaultRunner):
         self._eng, off = self._pairs(dev, engine.BARYONIFY)
         return off
 
+    PIPELINE_GROUPS = 8
+
+    def _process_pipelined(self, dev, orig):
+        """Pair stage, re-binning and read-back proceed ring-band group by group (``ShellEngine.baryonify_to_host``); the
+        map travels to the device in the same pieces, starting when the host set-up has released the host cores."""
+        nside = self.LightconeShell.NSIDE
+        _, edges = engine.band_groups(nside, self.PIPELINE_GROUPS)
+        box = {}
+        self._after_host = lambda: box.setdefault("up", dv.ChunkedUpload(orig, dev, edges))
+        try:
+            eng = self._engine(dev, engine.BARYONIFY)
+        finally:
+            self._after_host = None
+        t0 = time.perf_counter()
+        up = box.get("up") or dv.ChunkedUpload(orig, dev, edges)
+        self._progress("pair stage + re-binning + read-back in %d ring-band groups" % (len(edges) - 1))
+        new_map, new_sum_d, old_sum_d = eng.baryonify_to_host(up, self.PIPELINE_GROUPS)
+        self.npairs = eng.npairs
+        self.regrid_used, self.regrid_window = eng.regrid_used, getattr(eng, "regrid_window", None)
+        new_sum, old_sum = float(new_sum_d.item()), float(old_sum_d.item())
+        torch.cuda.synchronize(dev)
+        self.timings["pairs_regrid_d2h"] = time.perf_counter() - t0
+        self.timings["pipelined"] = bool(eng.regrid_pipelined)
+        return new_map, new_sum, old_sum
+
     def process(self):
         dev = dv.device(self.device)
         with torch.cuda.device(dev):
             orig = np.ascontiguousarray(self.LightconeShell.map, dtype=np.float64)
+            nh = len(self.HaloLightConeCatalog.cat)
+            if (self.variant == "gather" and self.regrid == "gather" and self.pinned_output and nh > 0
+                    and not (self.pipeline_chunks > 1 and nh >= self.pipeline_min_halos)):
+                new_map, new_sum, old_sum = self._process_pipelined(dev, orig)
+                assert np.isclose(new_sum, old_sum), \
+                    "ERROR in pixel regridding, sum(new_map) [%0.14e] != sum(oldmap) [%0.14e]" % (new_sum, old_sum)
+                return new_map
             # the 8 B/pixel map travels (pageable -> pinned -> HBM) while halos are binned and evaluated on the GPU; it
             # starts after the host set-up, which wants all host cores for itself
             box = {}
@@ -173,6 +214,7 @@ class BaryonifyShell(DefaultRunner):
             orig_d = (box.get("up") or dv.AsyncUpload(orig, dev)).result()
             old_sum_d = orig_d.sum()  # the reference's two np.sum's (HealpixRunner.py:344-346), on the device
             # re-binning and read-back overlap: the gather variant hands over the map range by range
+            self._progress("re-binning (%s)" % self.regrid)
             new_map, new_sum_d, t_dev = self._eng.regrid_to_host(orig_d, off, method=self.regrid, pinned=self.pinned_output)
             self.regrid_used = self._eng.regrid_used
             self._eng = None

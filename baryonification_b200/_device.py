@@ -75,6 +75,57 @@ class AsyncUpload:
         return self.out
 
 
+class ChunkedUpload:
+    """``AsyncUpload`` in consecutive pieces: ``edges`` cuts the (flat) array into ranges that are staged and copied in
+    order, each with its own completion event, so that a consumer that works through the array front to back
+    (the ring-band pipeline of ``ShellEngine.baryonify_to_host``) can start on the first range while the rest is still
+    on its way.  ``wait(i)`` makes the current stream wait for range i; ``.out`` is the whole device array."""
+
+    def __init__(self, a, dev, edges, dtype=np.float64):
+        import threading
+        self.dev = dev
+        self.side = torch.cuda.Stream(device=dev)
+        self.edges = [int(e) for e in edges]
+        self.events = [torch.cuda.Event() for _ in range(len(self.edges) - 1)]
+        self.ready = [threading.Event() for _ in self.events]
+        self.err = None
+        a = np.ascontiguousarray(a, dtype=dtype).reshape(-1)
+        self.out = torch.empty(a.shape, dtype=torch.float64, device=dev)
+
+        def work():
+            try:
+                with torch.cuda.device(dev):
+                    src = torch.from_numpy(a) if a.flags.writeable else torch.from_numpy(a.copy())
+                    pin = torch.empty(src.shape, dtype=src.dtype, pin_memory=True)
+                    for i, (lo, hi) in enumerate(zip(self.edges[:-1], self.edges[1:])):
+                        pin[lo:hi].copy_(src[lo:hi])
+                        with torch.cuda.stream(self.side):
+                            self.out[lo:hi].copy_(pin[lo:hi], non_blocking=True)
+                            self.events[i].record(self.side)
+                        self.ready[i].set()
+                    self.pin = pin  # (alive until the copies are done; released with the object)
+            except BaseException as e:  # re-raised in wait()
+                self.err = e
+                for r in self.ready:
+                    r.set()
+
+        self.th = threading.Thread(target=work, daemon=True)
+        self.th.start()
+
+    def wait(self, i):
+        self.ready[i].wait()
+        if self.err is not None:
+            raise self.err
+        torch.cuda.current_stream(self.dev).wait_event(self.events[i])
+
+    def result(self):
+        for i in range(len(self.events)):
+            self.wait(i)
+        self.th.join()
+        self.out.record_stream(torch.cuda.current_stream(self.dev))
+        return self.out
+
+
 def to_host(t, pinned=True):
     """Device tensor -> numpy array owned by the caller.  With ``pinned`` the array is backed by page-locked
     memory from torch's caching host allocator (returned to the cache when the array is garbage-collected): the

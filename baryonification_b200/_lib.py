@@ -54,6 +54,8 @@ _P = C.POINTER
 _SIGS = {
     "bf_last_error": (C.c_char_p, []),
     "bf_version": (C.c_int, []),
+    "bf_launch_count": (C.c_ulonglong, []),
+    "bf_probe_fp64": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_ulonglong), C.c_void_p]),
     "bf_device_sm_count": (C.c_int, [_P(C.c_int)]),
     "bf_table_collapse_zM": (C.c_int, [_P(Table), _i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p]),
     "bf_table_collapse_nd": (C.c_int, [_P(TableND), _i64, _dbl_p, _dbl_p, C.c_void_p]),
@@ -84,6 +86,8 @@ _SIGS = {
     "bf_shell_regrid_gather_emit": (C.c_int, [_i64, _dbl_p, _dbl_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_int),
                                               C.c_void_p]),
     "bf_shell_regrid_gather_emit_range": (C.c_int, [_i64, _i64, _i64, _dbl_p, _dbl_p, C.c_void_p, C.c_size_t,
+                                                    C.POINTER(C.c_int), C.c_void_p]),
+    "bf_shell_regrid_gather_emit_part": (C.c_int, [_i64, _i64, _i64, _dbl_p, _dbl_p, C.c_void_p, C.c_size_t,
                                                     C.POINTER(C.c_int), C.c_void_p]),
     "bf_shell_regrid_gather_range": (C.c_int, [_i64, C.c_void_p, C.c_size_t, C.POINTER(C.c_int), _i64, _i64, _dbl_p,
                                                C.c_void_p]),

@@ -34,7 +34,12 @@ void bf_set_error(const char *fmt, ...);
         }                                                            \
     } while (0)
 
-#define BF_LAUNCH_OK() BF_CUDA_OK(cudaGetLastError())
+void bf_count_launch();  // bf_abi.cu: every kernel launch of the library is counted (bf_launch_count)
+#define BF_LAUNCH_OK()                     \
+    do {                                   \
+        bf_count_launch();                 \
+        BF_CUDA_OK(cudaGetLastError());    \
+    } while (0)
 
 static inline int bf_sm_count() {
     static int n = 0;

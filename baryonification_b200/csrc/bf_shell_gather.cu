@@ -267,9 +267,10 @@ __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather
                 // constants are one broadcast read.  The remaining masks are transposed, so every lane ends up with one
                 // bit per candidate for ITS pixel.
                 const int nw = (nc + 31) >> 5;
+                const unsigned vmask = __ballot_sync(0xffffffffu, valid);  // lanes that hold a pixel (ring ends: caps)
                 for (int kw = 0; kw < nw; ++kw) {
                     const int c = kw * 32 + lane;
-                    unsigned m = (c < nc) ? lanes_of_range(sm.rng[w][c], ip0 + s * 32) : 0u;
+                    unsigned m = (c < nc) ? (lanes_of_range(sm.rng[w][c], ip0 + s * 32) & vmask) : 0u;
                     const unsigned fw = __ballot_sync(0xffffffffu, m == 0xffffffffu);
                     if (m == 0xffffffffu) m = 0u;
                     const bool any_part = __any_sync(0xffffffffu, m != 0u);
@@ -287,13 +288,14 @@ __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather
                         gather_pair<MODE>(sm, c, v, ax, gi_s, logtab, acc);
                     }
                 }
-                // partial candidates: every lane pops ITS bits (lanes work on different candidates at the same time)
+                // partial candidates: every lane pops ITS bits (lanes work on different candidates at the same time;
+                // lanes without a pixel have no bits)
                 int kw = 0;
-                unsigned hm = valid ? sm.hits[w][0][lane] : 0u;
+                unsigned hm = sm.hits[w][0][lane];
                 my_pairs32 += __popc(hm);
                 for (;;) {
                     while (hm == 0u && kw + 1 < nw) {
-                        hm = valid ? sm.hits[w][++kw][lane] : (++kw, 0u);
+                        hm = sm.hits[w][++kw][lane];
                         my_pairs32 += __popc(hm);
                     }
                     const bool act = hm != 0u;
@@ -346,12 +348,8 @@ __global__ void __launch_bounds__(256) gather_aux_kernel(bf_raxis ax, double2 *_
 // halos were diverted by the binning stage; they are applied on top of the gathered offsets with fp64
 // atomics (4 pixels each; order only matters if >= 3 of them share a pixel).
 #include "bf_pair.cuh"
-__global__ void tiny_kernel(bf_hpx h, bf_shell_halos S, bf_raxis ax, const int *__restrict__ tiny_list,
-                            const int *__restrict__ tiny_count, i64 pix_first, i64 pix_last, double *out, i64 pix_base,
-                            u64 *npairs) {
-    int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 2, k = threadIdx.x & 3;
-    if (i >= *tiny_count) return;
-    i64 j = tiny_list[i];
+__device__ __forceinline__ void tiny_one(const bf_hpx &h, const bf_shell_halos &S, const bf_raxis &ax, i64 j, int k,
+                                         i64 pix_first, i64 pix_last, double *out, i64 pix_base, u64 *npairs) {
     bf_halo_rec H;
     H.c[0] = S.vec[3 * j]; H.c[1] = S.vec[3 * j + 1]; H.c[2] = S.vec[3 * j + 2];
     H.D = S.D[j]; H.a = S.a[j]; H.cut = S.cut[j]; H.lnr_shift = S.lnr_shift[j];
@@ -363,6 +361,14 @@ __global__ void tiny_kernel(bf_hpx h, bf_shell_halos S, bf_raxis ax, const int *
     bf_pair_baryonify_shell(H, ax, v, off);
     for (int m = 0; m < 3; ++m) atomicAdd(out + 3 * (p[k] - pix_base) + m, off[m]);
     if (npairs) atomicAdd(npairs, 1ull);
+}
+
+__global__ void tiny_kernel(bf_hpx h, bf_shell_halos S, bf_raxis ax, const int *__restrict__ tiny_list,
+                            const int *__restrict__ tiny_count, i64 pix_first, i64 pix_last, double *out, i64 pix_base,
+                            u64 *npairs) {
+    const int k = threadIdx.x & 3, ntiny = *tiny_count;  // (few or none: the grid is small and strides over the list)
+    for (int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 2; i < ntiny; i += (gridDim.x * blockDim.x) >> 2)
+        tiny_one(h, S, ax, tiny_list[i], k, pix_first, pix_last, out, pix_base, npairs);
 }
 
 extern "C" int bf_shell_gather(int64_t nside, int mode, const bf_shell_halos *S, const bf_table *T, int64_t band_lo,
@@ -417,8 +423,9 @@ extern "C" int bf_shell_gather(int64_t nside, int mode, const bf_shell_halos *S,
         int64_t first = 0, last = 0;
         int rc = bf_shell_band_pixel_range(nside, band_lo, band_hi, &first, &last);
         if (rc) return rc;
-        tiny_kernel<<<(unsigned)((S->nh * 4 + 127) / 128), 128, 0, s>>>(A.h, *S, A.ax, w.tiny_list, w.tiny_count, first,
-                                                                         last, out, pix_base, npairs);
+        const i64 want = (S->nh * 4 + 127) / 128;
+        tiny_kernel<<<(unsigned)(want < 296 ? want : 296), 128, 0, s>>>(A.h, *S, A.ax, w.tiny_list, w.tiny_count, first, last,
+                                                                        out, pix_base, npairs);
         BF_LAUNCH_OK();
     }
     return BF_OK;

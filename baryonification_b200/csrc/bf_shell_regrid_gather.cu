@@ -168,7 +168,7 @@ __global__ void __launch_bounds__(256) rg_gather_kernel(bf_hpx h, int dr_min, in
             rg_scan(key, val, sp + (u32)lo, sp + (u32)hi, d, s, any);
         }
     }
-    if (any) out[d] += s;
+    out[d] = any ? s : 0.0;  // every destination of the range is written: the map needs no zero fill
 }
 
 extern "C" size_t bf_shell_regrid_gather_ws_bytes(int64_t nside) {
@@ -196,15 +196,32 @@ static int rg_layout(int64_t nside, void *ws, size_t ws_bytes, const char *who, 
 }
 
 // sources pix_first <= p < pix_last; orig_map / pix_offsets are that slice
+static int rg_emit(int64_t nside, int64_t pix_first, int64_t pix_last, const double *orig_map, const double *pix_offsets,
+                   void *ws, size_t ws_bytes, int *window_host, int margin_rings, void *stream);
+
 extern "C" int bf_shell_regrid_gather_emit_range(int64_t nside, int64_t pix_first, int64_t pix_last, const double *orig_map,
                                                  const double *pix_offsets, void *ws, size_t ws_bytes, int *window_host,
                                                  void *stream) {
+    return rg_emit(nside, pix_first, pix_last, orig_map, pix_offsets, ws, ws_bytes, window_host,
+                   BF_SHELL_GATHER_MARGIN_RINGS, stream);
+}
+
+// The pipelined form (engine: pair stage, emit, gather and read-back proceed ring-band group by group): the keys of the
+// group's own sources only -- the neighbouring groups' keys, already written, must survive.
+extern "C" int bf_shell_regrid_gather_emit_part(int64_t nside, int64_t pix_first, int64_t pix_last, const double *orig_map,
+                                                const double *pix_offsets, void *ws, size_t ws_bytes, int *window_host,
+                                                void *stream) {
+    return rg_emit(nside, pix_first, pix_last, orig_map, pix_offsets, ws, ws_bytes, window_host, 0, stream);
+}
+
+static int rg_emit(int64_t nside, int64_t pix_first, int64_t pix_last, const double *orig_map, const double *pix_offsets,
+                   void *ws, size_t ws_bytes, int *window_host, int margin_rings, void *stream) {
     BF_REQUIRE(orig_map && pix_offsets && window_host, "null argument");
     bf_hpx h; rg_window *win; uint4 *key; double *val;
     int rc = rg_layout(nside, ws, ws_bytes, "bf_shell_regrid_gather_emit", h, win, key, val);
     if (rc) return rc;
     BF_REQUIRE(pix_first >= 0 && pix_first <= pix_last && pix_last <= h.npix, "pixel range");
-    const i64 margin = (i64)BF_SHELL_GATHER_MARGIN_RINGS * 4 * nside;
+    const i64 margin = (i64)margin_rings * 4 * nside;
     const i64 e_first = (pix_first - margin > 0) ? pix_first - margin : 0;
     const i64 e_last = (pix_last + margin < h.npix) ? pix_last + margin : h.npix;
     cudaStream_t s = (cudaStream_t)stream;
@@ -225,7 +242,7 @@ extern "C" int bf_shell_regrid_gather_emit_range(int64_t nside, int64_t pix_firs
     window_host[0] = w.dr_min; window_host[1] = w.dr_max; window_host[2] = w.dj_max;
     const long long cost = (long long)(w.dr_max - w.dr_min + 1) * (2LL * w.dj_max + 1);
     const int reach = (w.dr_max > -w.dr_min ? w.dr_max : -w.dr_min) + 1;  // rings between a source and its destination
-    const bool part = pix_first > 0 || pix_last < h.npix;
+    const bool part = margin_rings > 0 && (pix_first > 0 || pix_last < h.npix);
     if (cost > BF_SHELL_GATHER_MAX_WINDOW || (part && 2 * reach > BF_SHELL_GATHER_MARGIN_RINGS)) {
         bf_set_error("bf_shell_regrid_gather: window of %d rings x %d pixels exceeds %d sources per destination",
                      w.dr_max - w.dr_min + 1, 2 * w.dj_max + 1, BF_SHELL_GATHER_MAX_WINDOW);
@@ -248,8 +265,12 @@ extern "C" int bf_shell_regrid_gather_range(int64_t nside, const void *ws, size_
     int rc = rg_layout(nside, const_cast<void *>(ws), ws_bytes, "bf_shell_regrid_gather_range", h, win, key, val);
     if (rc) return rc;
     BF_REQUIRE(dest_first >= 0 && dest_first <= dest_last && dest_last <= h.npix, "destination range");
-    if (dest_last == dest_first || window_host[1] < window_host[0]) return BF_OK;
+    if (dest_last == dest_first) return BF_OK;
     const i64 n = dest_last - dest_first;
+    if (window_host[1] < window_host[0]) {  // no deposits at all: the range is still written
+        BF_CUDA_OK(cudaMemsetAsync(new_map + dest_first, 0, sizeof(double) * (size_t)n, (cudaStream_t)stream));
+        return BF_OK;
+    }
     rg_gather_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
         h, window_host[0], window_host[1], window_host[2], dest_first, dest_last, key, val, new_map);
     BF_LAUNCH_OK();

@@ -207,6 +207,52 @@ def gather_slices(own, ranges, group=None, out=None):
     return out
 
 
+MARGIN_RINGS = 96  # = BF_SHELL_GATHER_MARGIN_RINGS / 2: the farthest the shard form of the destination gather deposits
+
+
+def margin_pixels(nside):
+    return MARGIN_RINGS * 4 * int(nside)
+
+
+def fixed_margins_ok(ranges, F):
+    """The fixed-width neighbour exchange applies when every rank's range is at least one margin long, so that what a
+    rank deposits beyond its range lands on the ADJACENT rank only.  Decided from the partition alone: every rank
+    takes the same branch."""
+    return len(ranges) > 1 and all(b - a >= F for a, b in ranges)
+
+
+def exchange_margins(local, ranges, F, group=None):
+    """Boundary mass exchange with FIXED margins: ``local`` holds this rank's partial sums over
+    [first - F, last + F) (without the side that has no neighbour); the two margins go to the adjacent ranks, the
+    margins received from them are added to the first / last F own pixels (each boundary region has exactly one
+    foreign contributor, so the order is fixed).  No size negotiation, no host read-back: four point-to-point messages
+    of F pixels.  Returns the finished own slice (a view of ``local``)."""
+    rank, world = _world(group)
+    first, last = ranges[rank]
+    lo_n, hi_n = rank > 0, rank < world - 1
+    off0 = F if lo_n else 0
+    own = local[off0:off0 + (last - first)]
+    if world == 1:
+        return own
+    peer = (lambda r: dist.get_global_rank(group, r)) if group is not None else (lambda r: r)
+    ops, r_lo, r_hi = [], None, None
+    if lo_n:
+        r_lo = torch.empty(F, dtype=local.dtype, device=local.device)
+        ops += [dist.P2POp(dist.isend, local[:F], peer(rank - 1), group=group),
+                dist.P2POp(dist.irecv, r_lo, peer(rank - 1), group=group)]
+    if hi_n:
+        r_hi = torch.empty(F, dtype=local.dtype, device=local.device)
+        ops += [dist.P2POp(dist.isend, local[local.numel() - F:], peer(rank + 1), group=group),
+                dist.P2POp(dist.irecv, r_hi, peer(rank + 1), group=group)]
+    for w in dist.batch_isend_irecv(ops):
+        w.wait()
+    if r_lo is not None:
+        own[:F] += r_lo
+    if r_hi is not None:
+        own[own.numel() - F:] += r_hi
+    return own
+
+
 # ----------------------------------------------------------------------------------------------------------
 # grid slabs
 # ----------------------------------------------------------------------------------------------------------
@@ -278,11 +324,74 @@ def _subset(scalars, keep):
             for k, v in scalars.items() if k != "_pinned"}  # (the page-locked slabs hold the WHOLE catalogue)
 
 
+class SharedHostArena:
+    """A host array that every rank of a one-box job maps (POSIX shared memory under /dev/shm) and page-locks
+    (``cudaHostRegister``), so that each rank's GPU writes ITS piece of a result straight into the caller-visible array
+    over its own PCIe link -- N links in parallel instead of one rank pulling the whole map through one.  Rank 0 names
+    and creates the segment, the others attach after a barrier; the file is unlinked as soon as everybody has it mapped
+    (the memory lives as long as the mappings).  Without CUDA (the gloo tests) the array is simply shared."""
+
+    def __init__(self, n, group=None, dtype=np.float64):
+        import os
+        import uuid
+        rank, world = _world(group)
+        self.n, self.registered, self._tensor = int(n), False, None
+        nbytes = max(self.n, 1) * np.dtype(dtype).itemsize
+        name = [None]
+        if rank == 0:
+            name[0] = "/dev/shm/bf200_%d_%s" % (os.getpid(), uuid.uuid4().hex[:12])
+            with open(name[0], "wb") as f:
+                f.truncate(nbytes)
+        if world > 1:
+            dist.broadcast_object_list(name, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        self.array = np.memmap(name[0], dtype=dtype, mode="r+", shape=(max(self.n, 1),))[:self.n]
+        if world > 1:
+            dist.barrier(group=group)
+        if rank == 0:
+            os.unlink(name[0])
+        if torch.cuda.is_available():
+            t = torch.from_numpy(self.array)
+            rc = torch.cuda.cudart().cudaHostRegister(t.data_ptr(), t.numel() * t.element_size(), 0)
+            self.registered = int(rc) == 0
+            self._tensor = t
+
+    @property
+    def tensor(self):
+        if self._tensor is None:
+            self._tensor = torch.from_numpy(self.array)
+        return self._tensor
+
+    def close(self):
+        if self.registered:
+            torch.cuda.cudart().cudaHostUnregister(self._tensor.data_ptr())
+            self.registered = False
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+_SHELL_KEYS = ("a", "D", "radius", "z_in", "M_in", "lon", "lat", "cut", "lnr_shift")
+
+
 class ShardedShell:
-    """Ring-band sharded BaryonifyShell / PaintProfilesShell.
+    """Ring-band sharded BaryonifyShell / PaintProfilesShell (one process per GPU of one box).
 
     ``runner`` is an (unprocessed) ``BaryonifyShell`` or ``PaintProfilesShell`` built identically on every rank.
-    ``process()`` returns the full map on every rank (numpy), exactly like the single-GPU runner."""
+    ``process()`` returns the full map on every rank, like the single-GPU runner -- as a view of a host array all ranks
+    share (``SharedHostArena``; two of them alternate, so a result stays valid until the second-next call):
+
+    * host set-up: every rank prepares the per-halo scalars of 1/N of the catalogue, one device all-gather (~100 B per
+      halo over NVLink) hands every rank the whole table, and each keeps the halos whose footprint can touch its bands
+      (catalogue order preserved: the per-pixel summation order -- and the bits -- equal the single-GPU run);
+    * pair stage on the rank's bands: no collective (pixel owners);
+    * BaryonifyShell re-binning: the rank's partial sums over its range widened by a fixed margin, the two margins go
+      to the adjacent ranks and are added there (``exchange_margins``: four messages, no negotiation) -- the boundary
+      mass exchange, the only data-path collective; small spheres whose bands are shorter than the margin take the
+      general ``exchange_boundary``;
+    * every rank copies ITS finished band to the shared host array over its own PCIe link."""
 
     def __init__(self, runner, group=None, device=None):
         from .Runners import shell as _shell
@@ -291,6 +400,8 @@ class ShardedShell:
         self.rank, self.world = _world(group)
         self.device = device
         self.npairs = None
+        self.timings = {}
+        self._arenas, self._turn = [None, None], 0
 
     def plan(self):
         nside = self.runner.LightconeShell.NSIDE
@@ -298,8 +409,58 @@ class ShardedShell:
         ranges = [band_pixel_range(nside, lo, hi) for lo, hi in bands]
         return bands, ranges
 
-    def process_device(self):
-        from . import _device as dv, engine, host
+    # ---- per-halo scalars: 1/N of the host work per rank, all-gathered on the device ------------------------
+    def scalars_device(self, dev, bands):
+        """dict of device tensors (the ``ShellEngine`` inputs) for the halos that can touch ``bands``."""
+        import copy
+        from . import host
+        r = self.runner
+        cat = r.HaloLightConeCatalog
+        n = len(cat.cat)
+        a, b = index_split(n, self.world)[self.rank]
+        part = copy.copy(cat)
+        part.cat = cat.cat[a:b]
+        s = host.shell_scalars(part, r.cosmo, r.mass_def, r.epsilon_max, r.model, self.baryonify)
+        ex = host.property_columns(part.cat, r.model)
+        nx = 0 if ex is None else ex.shape[1]
+        width = len(_SHELL_KEYS) + 3 + nx
+        chunk = -(-n // self.world) if n else 0  # equal pieces for one all_gather_into_tensor
+        mine = torch.zeros((chunk, width), dtype=torch.float64, pin_memory=torch.cuda.is_available())
+        m = mine.numpy()
+        for c, k in enumerate(_SHELL_KEYS):
+            m[:b - a, c] = s[k]
+        m[:b - a, len(_SHELL_KEYS):len(_SHELL_KEYS) + 3] = s["vec"]
+        if nx:
+            m[:b - a, len(_SHELL_KEYS) + 3:] = ex
+        mine_d = mine.to(dev, non_blocking=True)
+        if self.world > 1:
+            full = torch.empty((chunk * self.world, width), dtype=torch.float64, device=dev)
+            dist.all_gather_into_tensor(full, mine_d, group=self.group)
+            sizes = [hi - lo for lo, hi in index_split(n, self.world)]
+            if any(sz != chunk for sz in sizes):  # drop the padding rows of the shorter pieces
+                full = torch.cat([full[i * chunk:i * chunk + sz] for i, sz in enumerate(sizes)])
+        else:
+            full = mine_d[:n]
+        nside = r.LightconeShell.NSIDE
+        ci = {k: c for c, k in enumerate(_SHELL_KEYS)}
+        if self.world > 1:  # halos_touching_bands on the device (conservative by `margin_rings`, like the host form)
+            lo, hi = bands
+            theta0 = torch.acos(full[:, len(_SHELL_KEYS) + 2].clamp(-1.0, 1.0))
+            rad = full[:, ci["radius"]]
+            first_ring, last_ring = max(lo * 8 + 1 - 3, 0), min(hi * 8 + 3, 4 * nside)
+            t_lo, t_hi = float(ring_colatitude(nside, first_ring)), float(ring_colatitude(nside, last_ring))
+            keep = ((theta0 + rad >= t_lo) & (theta0 - rad <= t_hi)) | ~torch.isfinite(rad)
+            full = full[keep]
+        t = {k: full[:, ci[k]].contiguous() for k in _SHELL_KEYS}
+        t["vec"] = full[:, len(_SHELL_KEYS):len(_SHELL_KEYS) + 3].contiguous()
+        t["extras"] = full[:, len(_SHELL_KEYS) + 3:].contiguous() if nx else None
+        return t
+
+    def process_device(self, gather=False):
+        """Device part: returns (own slice [first, last) on the device -- or the whole map with ``gather=True`` --,
+        (sum new, sum old) or None, ranges)."""
+        import time
+        from . import _device as dv, engine
         from .tables import displacement_host_table, profile_host_table
         r = self.runner
         r._check_keys(self.baryonify)
@@ -307,36 +468,64 @@ class ShardedShell:
         nside = r.LightconeShell.NSIDE
         bands, ranges = self.plan()
         lo, hi = bands[self.rank]
-        s = host.shell_scalars(r.HaloLightConeCatalog, r.cosmo, r.mass_def, r.epsilon_max, r.model, self.baryonify)
-        s["extras"] = host.property_columns(r.HaloLightConeCatalog.cat, r.model)
-        keep = halos_touching_bands(s["vec"][:, 2], s["radius"], nside, lo, hi)
-        s = _subset(s, keep)
+        first, last = ranges[self.rank]
         mode = engine.BARYONIFY if self.baryonify else engine.PAINT
         htab = displacement_host_table(r.model) if self.baryonify else profile_host_table(r.model, "2D")
         with torch.cuda.device(dev):
-            eng = engine.ShellEngine(nside, mode, htab, s, dev, variant="gather", bands=(lo, hi)).upload().bin()
+            t0 = time.perf_counter()
+            up = None
+            if self.baryonify:  # this rank's slice of the map travels while the halos are prepared
+                orig = np.ascontiguousarray(r.LightconeShell.map, dtype=np.float64).reshape(-1)
+                up = dv.AsyncUpload(orig[first:last], dev)
+            t = self.scalars_device(dev, (lo, hi))
+            self.timings["host_setup"] = time.perf_counter() - t0
+            eng = engine.ShellEngine(nside, mode, htab, None, dev, variant="gather", bands=(lo, hi))
+            eng.upload_device(t).bin()
             acc = eng.accumulate()
-            pairs = torch.tensor([eng.pair_count()], dtype=torch.int64, device=dev)
-            dist.all_reduce(pairs, group=self.group)
-            self.npairs = int(pairs.item())
+            pairs = eng.cnt.clone()
+            if self.world > 1:
+                dist.all_reduce(pairs, group=self.group)
             if not self.baryonify:
-                return gather_slices(acc, ranges, self.group), None
-            first, last = ranges[self.rank]
-            orig = np.ascontiguousarray(r.LightconeShell.map, dtype=np.float64)
-            orig_d = dv.to_dev(orig[first:last], dev=dev, pinned=True)
-            new_full = eng.regrid(orig_d, acc, method=r.regrid)
-            own = exchange_boundary(new_full, ranges, self.group, window=64 * 4 * nside)
-            sums = torch.stack([own.sum(), orig_d.sum()])
-            dist.all_reduce(sums, group=self.group)  # the reference's mass check, HealpixRunner.py:344-346
-            return gather_slices(own, ranges, self.group), (float(sums[0]), float(sums[1]))
+                self.npairs = int(pairs.item())
+                return (gather_slices(acc, ranges, self.group) if gather else acc), None, ranges
+            orig_d = up.result()
+            F = margin_pixels(nside)
+            if fixed_margins_ok(ranges, F):
+                local, stray = eng.regrid_shard(orig_d, acc, F, self.rank > 0, self.rank < self.world - 1, method=r.regrid)
+                own = exchange_margins(local, ranges, F, self.group)
+            else:  # small spheres: bands shorter than the margin
+                stray = None
+                new_full = eng.regrid(orig_d, acc, method=r.regrid)
+                own = exchange_boundary(new_full, ranges, self.group, window=64 * 4 * nside)
+            sums = torch.stack([own.sum(), orig_d.sum(), (stray if stray is not None else own.new_zeros(())).to(own.dtype)])
+            if self.world > 1:
+                dist.all_reduce(sums, group=self.group)  # the reference's mass check, HealpixRunner.py:344-346
+            self.npairs = int(pairs.item())
+            sums = sums.tolist()
+            if sums[2] != 0:
+                raise _lib.BFError("ShardedShell: displaced mass landed more than %d rings outside a shard" % MARGIN_RINGS)
+            return (gather_slices(own, ranges, self.group) if gather else own), (sums[0], sums[1]), ranges
+
+    def _arena(self, n):
+        self._turn ^= 1
+        ar = self._arenas[self._turn]
+        if ar is None or ar.n != n:
+            ar = self._arenas[self._turn] = SharedHostArena(n, self.group)
+        return ar
 
     def process(self):
-        from . import _device as dv
-        out, sums = self.process_device()
+        out, sums, ranges = self.process_device(gather=False)
         if sums is not None:
             assert np.isclose(sums[0], sums[1]), \
                 "ERROR in pixel regridding, sum(new_map) [%0.14e] != sum(oldmap) [%0.14e]" % sums
-        return dv.to_host(out, True)
+        arena = self._arena(ranges[-1][1])
+        a, b = ranges[self.rank]
+        arena.tensor[a:b].copy_(out, non_blocking=arena.registered)  # every rank: its band, its own PCIe link
+        if out.is_cuda:
+            torch.cuda.current_stream(out.device).synchronize()
+        if self.world > 1:
+            dist.barrier(group=self.group)
+        return arena.array
 
 
 class ShardedSnapshot:
@@ -401,9 +590,14 @@ class ShardedGrid:
         local.HaloNDCatalog, local.rows, local.device, local.timings = cat, (a0, a1), self.device, {}
         return local
 
-    def process(self, gather=True):
-        import ctypes as C
-        from . import _device as dv, _lib
+    GHOST_ROWS = 4  # rows of the map uploaded either side of the slab before the displacement window is known
+
+    def upload(self, dev, ghost=None):
+        """Everything the device stages need, resident in HBM: the halos that can reach this rank's slab (set-up on the
+        host, table, collapsed rows), the slab's rows of the map plus ``ghost`` rows either side (more are fetched
+        when the displacement window turns out wider).  Returns the state dict the stage methods take."""
+        from . import _device as dv
+        from .tables import displacement_host_table, profile_host_table
         r = self.runner
         G = r.GriddedMap
         n, dim = G.Npix, (2 if G.is2D else 3)
@@ -411,41 +605,101 @@ class ShardedGrid:
         rows = index_split(n, self.world)
         a0, a1 = rows[self.rank]
         local = self._local_runner(a0, a1)
-        dev = dv.device(self.device)
+        ghost = self.GHOST_ROWS if ghost is None else int(ghost)
         with torch.cuda.device(dev):
-            if not self.baryonify:
-                out = local.paint_device(dev).view(n, rowlen)
-            else:
-                lib = _lib.load(require_cuda=True)
-                off = local.offsets_device(dev).view(n, rowlen * dim)
-                ws = torch.empty(lib.bf_grid_regrid_gather_ws_bytes(), dtype=torch.uint8, device=dev)
-                lohi = (C.c_int * 6)()
-                _lib.call("bf_grid_regrid_window", dim, n, dv.ptr(off), a0, a1, dv.ptr(ws), ws.numel(), lohi,
-                          dv.stream_ptr())
+            htab = displacement_host_table(r.model) if self.baryonify else profile_host_table(r.model, "2D" if G.is2D else "3D")
+            table, s, desc, bins, keep = local._prepare(htab, self.baryonify, dev)
+            st = dict(local=local, table=table, s=s, desc=desc, bins=bins, keep=keep, rows=rows, a0=a0, a1=a1, n=n, dim=dim,
+                      rowlen=rowlen, dev=dev, cnt=dv.pair_counter(dev), have=set())
+            if self.baryonify:
+                st["orig_h"] = np.ascontiguousarray(G.map, dtype=np.float64).reshape(n, rowlen)
+                st["orig"] = dv.zeros((n, rowlen), dev=dev) if self.world > 1 else None
+                self._fetch_rows(st, list(range(a0, a1)) + ghost_rows(rows, self.rank, ghost, ghost, n))
+                st["orig_slab"] = st["orig"][a0:a1]
+                st["off"] = dv.zeros((n, rowlen * dim), dev=dev)
+                st["out"] = dv.zeros((n, rowlen), dev=dev)
+        return st
+
+    def _fetch_rows(self, st, wanted):
+        """Upload the rows of the map in ``wanted`` that are not on the device yet (global row indexing)."""
+        from . import _device as dv
+        new = sorted(set(int(g) for g in wanted) - st["have"])
+        if st["orig"] is None:  # one rank: the whole map, one pinned copy
+            st["orig"] = dv.to_dev(st["orig_h"], dev=st["dev"], pinned=True)
+            st["have"] = set(range(st["n"]))
+            return
+        for g0, g1 in _runs(new):
+            st["orig"][g0:g1] = dv.to_dev(st["orig_h"][g0:g1], dev=st["dev"], pinned=True)
+        st["have"].update(new)
+
+    def pairs_device(self, st):
+        """The per-halo loop on this rank's slab (cell-owner gather, no collective): pixel offsets [n, rowlen * dim]
+        (global row indexing, only the slab's rows are written) or the painted rows."""
+        loc = st["local"]
+        a0, a1 = st["a0"], st["a1"]
+        out = st["off"] if self.baryonify else st.setdefault("paint", torch.zeros((st["n"], st["rowlen"]), dtype=torch.float64,
+                                                                                   device=st["dev"]))
+        out[a0:a1].zero_()
+        st["cnt"].zero_()
+        with torch.cuda.device(st["dev"]):
+            from .Runners.grid import GRID_BARYONIFY, GRID_PAINT
+            loc._accumulate(GRID_BARYONIFY if self.baryonify else GRID_PAINT, st["s"], st["desc"], st["bins"], st["table"],
+                            out.view(-1, st["dim"]) if self.baryonify else out.view(-1), st["cnt"], st["dev"])
+        self.local_pairs = loc.npairs
+        return out
+
+    def regrid_device(self, st, off):
+        """BaryonifyGrid re-binning of the slab: agree on the displacement window (MIN / MAX all-reduce of six integers),
+        exchange the ghost rows of the offsets, fetch missing ghost rows of the map, gather this rank's destination
+        rows.  Returns the slab's rows of the new map (device, [a1 - a0, rowlen])."""
+        import ctypes as C
+        from . import _device as dv, _lib
+        dev, n, dim, a0, a1, rows = st["dev"], st["n"], st["dim"], st["a0"], st["a1"], st["rows"]
+        with torch.cuda.device(dev):
+            lib = _lib.load(require_cuda=True)
+            if "rg_ws" not in st:
+                st["rg_ws"] = torch.empty(lib.bf_grid_regrid_gather_ws_bytes(), dtype=torch.uint8, device=dev)
+            ws = st["rg_ws"]
+            lohi = (C.c_int * 6)()
+            _lib.call("bf_grid_regrid_window", dim, n, dv.ptr(off), a0, a1, dv.ptr(ws), ws.numel(), lohi, dv.stream_ptr())
+            if self.world > 1:
                 lo_t = torch.tensor(list(lohi)[:3], dtype=torch.int64, device=dev)
                 hi_t = torch.tensor(list(lohi)[3:], dtype=torch.int64, device=dev)
                 dist.all_reduce(lo_t, op=dist.ReduceOp.MIN, group=self.group)
                 dist.all_reduce(hi_t, op=dist.ReduceOp.MAX, group=self.group)
                 lohi = (C.c_int * 6)(*[int(v) for v in lo_t.tolist() + hi_t.tolist()])
-                below, above = max(0, lohi[3] + 1), max(0, -lohi[0])  # source rows a0 - hi - 1 ... a1 - 1 - lo
-                exchange_rows(off, rows, below, above, self.group)
-                orig_h = np.ascontiguousarray(G.map, dtype=np.float64).reshape(n, rowlen)
-                orig = dv.zeros((n, rowlen), dev=dev)
-                mine = list(range(a0, a1)) + ghost_rows(rows, self.rank, below, above, n)
-                for g0, g1 in _runs(sorted(mine)):
-                    orig[g0:g1] = dv.to_dev(orig_h[g0:g1], dev=dev)
-                out = dv.zeros((n, rowlen), dev=dev)
-                win = (C.c_int * 3)()
-                _lib.call("bf_grid_regrid_gather_rows", dim, n, dv.ptr(off), dv.ptr(orig), dv.ptr(out), lohi, a0, a1,
-                          win, dv.stream_ptr())
-                self.regrid_window = tuple(win)
-            pairs = torch.tensor([local.npairs], dtype=torch.int64, device=dev)
-            dist.all_reduce(pairs, group=self.group)
+            below, above = max(0, lohi[3] + 1), max(0, -lohi[0])  # source rows a0 - hi - 1 ... a1 - 1 - lo
+            exchange_rows(off, rows, below, above, self.group)
+            self._fetch_rows(st, ghost_rows(rows, self.rank, below, above, n))
+            win = (C.c_int * 3)()
+            _lib.call("bf_grid_regrid_gather_rows", dim, n, dv.ptr(off), dv.ptr(st["orig"]), dv.ptr(st["out"]), lohi, a0, a1,
+                      win, dv.stream_ptr())
+            self.regrid_window = tuple(win)
+        return st["out"][a0:a1]
+
+    def process(self, gather=True):
+        from . import _device as dv
+        r = self.runner
+        G = r.GriddedMap
+        dev = dv.device(self.device)
+        with torch.cuda.device(dev):
+            st = self.upload(dev)
+            out = self.pairs_device(st)
+            own = self.regrid_device(st, out) if self.baryonify else out[st["a0"]:st["a1"]]
+            pairs = torch.tensor([self.local_pairs], dtype=torch.int64, device=dev)
+            if self.world > 1:
+                dist.all_reduce(pairs, group=self.group)
             self.npairs = int(pairs.item())
-            own = out[a0:a1]
             if not gather:
-                return own.cpu().numpy()
-            full = gather_slices(own.contiguous(), rows, self.group)
+                res = dv.to_host(own.contiguous(), True)
+                if self.baryonify:  # Map2DRunner.py:611-613, over all slabs
+                    sums = torch.stack([own.sum(), st["orig_slab"].sum()])
+                    if self.world > 1:
+                        dist.all_reduce(sums, group=self.group)
+                    assert np.isclose(float(sums[0]), float(sums[1])), \
+                        "ERROR in pixel regridding, sum(new_map) [%0.14e] != sum(oldmap) [%0.14e]" % (float(sums[0]), float(sums[1]))
+                return res
+            full = gather_slices(own.contiguous(), st["rows"], self.group)
             res = dv.to_host(full.reshape(-1), True).reshape(G.map.shape)
         if self.baryonify:  # Map2DRunner.py:611-613
             new_sum, old_sum = float(res.sum()), float(np.sum(G.map))

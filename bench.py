@@ -1,23 +1,29 @@
 #!/usr/bin/env python
-"""bench.py -- halo-pixel updates/s of BaryonifyShell on B200 (BASELINE.json metric).
+"""bench.py -- halo-pixel updates/s of the B200 hot path (BASELINE.json metric), one JSON line on stdout.
 
-    python bench.py --gpus N --steps K --warmup W            # our arm (N>1: launched by torchrun)
-    python bench.py --impl reference --gpus N --steps K ...   # the CPU arm (oracle port, all host threads)
+    python bench.py --gpus N --steps K --warmup W                 # our arm (N>1: launched by torchrun)
+    python bench.py --impl reference --gpus N --steps K ...       # the CPU arm (oracle port, all host threads)
+    python bench.py --workload paint|snapshot|grid3d ...          # the other BASELINE.json configurations
 
-Workload (config.workload): BaryonifyShell on a HEALPix NSIDE 4096 mass map with 1e6 synthetic halos,
-epsilon_max 20, 10x10x500 displacement table -- the configuration BASELINE.json's metric is quoted on; it
-fits one B200 (offsets 4.8 GB + maps 3.2 GB + collapsed rows 4 GB), so it is the N=1 workload too.
+Workloads (config.workload):
+  shell     BaryonifyShell, HEALPix NSIDE 4096 mass map, 1e6 synthetic halos, epsilon_max 20, 10x10x500 displacement
+            table -- the configuration BASELINE.json's metric is quoted on; it fits one B200, so it is the N=1 workload
+            too.  DEFAULT (what the driver's BENCH / SCALE runs measure).
+  paint     PaintProfilesShell (C3): same map size and catalogue, zero map, 10x10x500 profile table.
+  snapshot  BaryonifySnapshot (C4): 512^3 particles in a 500 Mpc/h box, 1e5 halos, epsilon_max 5.
+  grid3d    BaryonifyGrid 3-D 1024^3 + Delta P(k) of the result (C5): 1e5 halos, epsilon_max 20, slab-sharded.
 
-One "step" = one full pass of the hot path with inputs resident in HBM: (z,M) table collapse, halo binning
-into sky cells, pair evaluation (gather kernel), re-binning (+ the map all-reduce when N>1).  `value` =
-exact pair count / device time.  `e2e` = the same metric through BaryonifyShell(...).process() with HOST
-numpy inputs: host scalar set-up, pinned H2D, kernels, D2H of the new map, mass check.
-N>1 shards the sphere into ring-band ranges of equal pixel count (strong scaling: the same map and catalogue
-are split); each rank bins the replicated catalogue against its own bands only.
+One "step" = one full pass of the hot path with inputs resident in HBM: (z,M) table collapse, halo binning, pair
+evaluation, re-binning (+ the boundary mass exchange when N>1; the result stays sharded over its owners).  `value` =
+exact pair (particle) count / device time, max over ranks.  `e2e` = the same metric through the public Runner
+`.process()` with HOST numpy inputs and a host result: host scalar set-up, pinned H2D, kernels, D2H, mass check -- at N>1
+through `sharding.Sharded*` (every rank prepares 1/N of the halos and reads ITS piece back over its own PCIe link), the
+same quantity at every N.  N>1 is strong scaling: the same map and catalogue are split.
 """
 from __future__ import annotations
 
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -30,14 +36,16 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-B_PAIR = 48.0      # algorithmic bytes per pair: RMW of 3 f64 offset components
-B_PIXEL = 104.0    # algorithmic bytes per pixel: map read 8 + offsets 24 + 4-neighbour RMW 64 + zero-init 8
-B_PARTICLE = 88.0  # snapshot: read (M,x,y,z) 32 + offsets 24 + write 32 (SURVEY.md section 8d)
+# ALGORITHMIC bytes: the accumulator read-modify-write the reference performs per pair
+B_PAIR = {"shell": 48.0, "paint": 16.0}   # 3 / 1 f64 components x (8 B read + 8 B write)
+B_PIXEL = 104.0    # BaryonifyShell per pixel: map read 8 + offsets 24 + 4-neighbour RMW 64 + zero-init 8
+B_PARTICLE = 88.0  # snapshot: read (M,x,y,z) 32 + offsets 24 + write 32
 B_SNAP_PAIR = 72.0 # snapshot: 24 B particle xyz read + 48 B offsets RMW per pair
-# dram__bytes_read.sum + dram__bytes_write.sum of ONE gather_kernel<1> launch at the default workload, N = 1, from the
-# ncu --set full capture summarised in profiles/ (the kernel writes every pixel once; it never re-reads accumulators)
-GATHER_TRAFFIC_BYTES = 7.06e9
-SNAP_TRAFFIC_BYTES = 10.92e9
+B_GRID_PAIR = 48.0 # BaryonifyGrid 3-D: 16 * D bytes per pair
+B_GRID_CELL = 168.0
+# fp64 instructions per pair in the whole-strip loop of gather_kernel (counted in `cuobjdump -sass`: DADD/DMUL/DFMA/DSETP)
+FP64_PER_PAIR = {"shell": 39, "paint": 40}
+CPU_SAMPLE = 10_000  # halos of the seed-42 shuffle in the bounded CPU sample -- the SAME for cpu_baseline and the reference arm
 
 
 def parse():
@@ -46,19 +54,22 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="shell", choices=["shell", "snapshot"],
-                    help="shell = BaryonifyShell NSIDE 4096 / 1e6 halos (the metric's configuration, default); "
-                         "snapshot = BaryonifySnapshot 512^3 particles / 1e5 halos (north_star's second target)")
+    ap.add_argument("--workload", default="shell", choices=["shell", "paint", "snapshot", "grid3d"])
     ap.add_argument("--npart-side", type=int, default=512)
+    ap.add_argument("--ngrid", type=int, default=1024)
     ap.add_argument("--nside", type=int, default=4096)
-    ap.add_argument("--nhalo", type=int, default=1_000_000)
+    ap.add_argument("--nhalo", type=int, default=None, help="default: 1e6 (shell, paint), 1e5 (snapshot, grid3d)")
     ap.add_argument("--variant", default="gather", choices=["gather", "atomic"])
     ap.add_argument("--regrid", default="gather", choices=["gather", "sorted", "atomic"],
-                    help="re-binning: deterministic sort + in-order segmented sum (default) or fp64 atomics")
-    ap.add_argument("--cpu-sample", type=int, default=10_000, help="halos in the bounded CPU-baseline sample")
+                    help="re-binning: deterministic destination gather (default), counting sort, or fp64 atomics")
+    ap.add_argument("--cpu-sample", type=int, default=CPU_SAMPLE, help="halos in the bounded CPU sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
-    return ap.parse_args()
+    ap.add_argument("--no-n1-check", action="store_true", help="N>1: skip the comparison with a 1-GPU evaluation on rank 0")
+    a = ap.parse_args()
+    if a.nhalo is None:
+        a.nhalo = 1_000_000 if a.workload in ("shell", "paint") else 100_000
+    return a
 
 
 def peaks():
@@ -66,6 +77,19 @@ def peaks():
     if os.path.exists(p):
         return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
     return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def measured_traffic(kernel, source):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of `kernel`, from profiles/traffic.json (written by
+    scripts/ncu_traffic.py from an `ncu --set full` capture) -- only while the kernel's source file still has the
+    content it was profiled at; None (null) when the capture is stale or absent."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        rec = json.load(open(p))[kernel]
+        sha = hashlib.sha256(open(os.path.join(ROOT, "baryonification_b200", "csrc", source), "rb").read()).hexdigest()[:16]
+        return float(rec["bytes"]) if rec.get("src_sha16") == sha else None
+    except Exception:
+        return None
 
 
 class ClockSampler:
@@ -80,7 +104,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
@@ -109,128 +133,185 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
-def make_inputs(args):
-    from oracle import ref_shim  # registers the pyccl stand-in when the real one is absent (inputs only)
+def min_timed_seconds(step, barrier, steps, ev, world, dev, floor_s=1.2):
+    """Time `steps` steps with CUDA events between two barriers.  When that region is shorter than ~1 s the clock sampler
+    would see only a handful of samples, so the region is REPEATED (each repeat is exactly `steps` steps between
+    barriers; the number of repeats is agreed across ranks from the first region) until ~`floor_s` of load has been
+    observed; ms/step is the mean over all regions.  Returns (ms per step on this rank, repeats)."""
+    import math
+    import torch
+    import torch.distributed as dist
+
+    def region():
+        barrier()
+        a, b = ev(), ev()
+        a.record()
+        for _ in range(steps):
+            step(True)
+        b.record()
+        barrier()
+        return a.elapsed_time(b)
+
+    first = region()
+    t = torch.tensor([first], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    reps = int(min(200, max(1, math.ceil(floor_s * 1e3 / max(float(t[0]), 1e-3)))))
+    total = first + sum(region() for _ in range(reps - 1))
+    return total / (reps * steps), reps
+
+
+def fp64_peak(dev):
+    """Device fp64 rate measured live: G lane-instructions / s of independent DFMA chains (bf_probe_fp64)."""
+    import ctypes as C
+    import torch
+    from baryonification_b200 import _device as dv, _lib
+    blocks, iters = 148 * 8, 1 << 13
+    out = torch.empty(blocks * 256, dtype=torch.float64, device=dev)
+    n = C.c_ulonglong()
+    best = None
+    for _ in range(4):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        _lib.call("bf_probe_fp64", blocks, iters, dv.ptr(out), C.byref(n), dv.stream_ptr())
+        b.record()
+        torch.cuda.synchronize(dev)
+        ms = a.elapsed_time(b)
+        best = ms if best is None else min(best, ms)
+    return blocks * 256 * n.value / (best * 1e-3) / 1e9  # G DFMA (lane) / s
+
+
+# =====================================================================================================================
+# shell workloads: BaryonifyShell ("shell", the metric's configuration) and PaintProfilesShell ("paint", C3)
+# =====================================================================================================================
+def shell_inputs(args):
+    from baryonification_b200 import synthetic as syn  # (pyccl or the package's own flat-wCDM closed forms: _ccl.py)
+    return syn.config_shell(nside=args.nside, nhalo=args.nhalo, zero_map=(args.workload == "paint"))
+
+
+def workload_name(args, eps=20.0):
+    if args.workload == "shell":
+        return f"BaryonifyShell NSIDE={args.nside}, {args.nhalo} halos, epsilon_max={eps:g}, table 10x10x500"
+    if args.workload == "paint":
+        return f"PaintProfilesShell NSIDE={args.nside}, {args.nhalo} halos, epsilon_max={eps:g}, profile table 10x10x500"
+    if args.workload == "snapshot":
+        return (f"BaryonifySnapshot {args.npart_side}^3 particles, L=500 Mpc/h, {args.nhalo} halos, "
+                "epsilon_max=5, table 10x10x500")
+    return (f"BaryonifyGrid 3-D {args.ngrid}^3 cells, L=500 Mpc/h, {args.nhalo} halos, epsilon_max=20, table 10x10x500, "
+            "+ Delta P(k) of the result (Nk=180)")
+
+
+def cpu_shell_sample(cfg, args, nthreads, nsample):
+    """Oracle port (C, OpenMP over halos) on a bounded sample: the first `nsample` halos of the reference's own seed-42
+    shuffle (Parallelize.py:255); BaryonifyShell adds the serial re-binning of a pixel sub-range.  Scaled linearly."""
+    from oracle import ref_shim
     ref_shim.install()
-    from baryonification_b200 import synthetic as syn
-    return syn.config_shell(nside=args.nside, nhalo=args.nhalo)
-
-
-def cpu_baseline(cfg, args, nthreads):
-    """Oracle port (C, OpenMP over halos) on a bounded sample; regrid timed on a pixel sub-range; both scaled."""
     from oracle import runners as orc
     cat = cfg["catalog"]
     n = len(cat)
-    m = min(args.cpu_sample, n)
-    idx = np.random.default_rng(42).choice(n, size=n, replace=False)[:m]  # the reference's own shuffle (Parallelize.py:255)
+    m = min(nsample, n)
+    idx = np.random.default_rng(42).choice(n, size=n, replace=False)[:m]
     sub = cat[np.sort(idx)]
+    npix = cfg["field"].map.size
+    if args.workload == "paint":
+        r = orc.PaintProfilesShell(sub, cfg["field"], cfg["epsilon_max"], cfg["paint_model"], nthreads=nthreads)
+        t0 = time.perf_counter()
+        r.process()
+        return dict(pairs=r.npairs, t_loop=time.perf_counter() - t0, t_regrid_sample=0.0, regrid_pixels=npix, halos=m)
     r = orc.BaryonifyShell(sub, cfg["field"], cfg["epsilon_max"], cfg["model"], nthreads=nthreads)
     t0 = time.perf_counter()
     off = r.offsets()
     t_loop = time.perf_counter() - t0
-    npix = cfg["field"].map.size
     p1 = min(npix, 4_000_000)
     new_map = np.zeros(npix)
     t0 = time.perf_counter()
     orc._lib().bfo_regrid_shell_range(cfg["field"].NSIDE, 0, p1, np.ascontiguousarray(cfg["field"].map), off, new_map)
-    t_rg = time.perf_counter() - t0
-    return dict(pairs=r.npairs, t_loop=t_loop, t_regrid_sample=t_rg, regrid_pixels=p1, halos=m)
+    return dict(pairs=r.npairs, t_loop=t_loop, t_regrid_sample=time.perf_counter() - t0, regrid_pixels=p1, halos=m)
 
 
-def cpu_value(cb, nhalo, npix):
+def cpu_shell_value(cb, nhalo, npix):
     scale = nhalo / cb["halos"]
     t_full = cb["t_loop"] * scale + cb["t_regrid_sample"] * (npix / cb["regrid_pixels"])
     return cb["pairs"] * scale / t_full, t_full
 
 
-def run_reference(args, rank, world):
-    """CPU arm: the oracle port of the reference's BaryonifyShell loop with all host threads (the reference itself is
-    pure Python and needs pyccl + healpy, neither installable here)."""
-    if rank != 0:
-        return
-    cfg = make_inputs(args)
-    cores = os.cpu_count() or 1
-    npix = cfg["field"].map.size
-    vals, times = [], []
-    for i in range(args.warmup + args.steps):
-        a = argparse.Namespace(**vars(args))
-        a.cpu_sample = max(500, args.cpu_sample // 4)  # each step is a bounded sample
-        t0 = time.perf_counter()
-        cb = cpu_baseline(cfg, a, cores)
-        dt = time.perf_counter() - t0
-        if i >= args.warmup:
-            vals.append(cpu_value(cb, args.nhalo, npix)[0])
-            times.append(dt)
-    v = float(np.mean(vals))
-    sample = (f"{a.cpu_sample} halos of the seed-42 shuffle (offset loop, OpenMP x{cores}) + re-binning of the first "
-              f"{cb['regrid_pixels']} pixels (serial, as the reference's numba loop); scaled linearly to the full job")
-    emit({
-        "impl": "reference", "metric": "halo-pixel updates/sec", "value": v, "unit": "pairs/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": float(np.mean(times) * 1e3),
-        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"BaryonifyShell NSIDE={args.nside}, {args.nhalo} halos, epsilon_max=20, table 10x10x500"},
-        "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port", "sample": sample},
-        "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0})
+def cpu_shell_record(cb, args, npix, cores):
+    v, t_full = cpu_shell_value(cb, args.nhalo, npix)
+    txt = f"{cb['halos']} halos of the seed-42 shuffle (pair loop {cb['t_loop']:.1f} s, OpenMP x{cores})"
+    if args.workload == "shell":
+        txt += f" + re-binning of {cb['regrid_pixels']} pixels ({cb['t_regrid_sample']:.1f} s, serial as the reference's numba loop)"
+    return {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port",
+            "sample": txt + f"; scaled linearly to the full job (~{t_full:.0f} s)", "extrapolated": True}
 
 
-def run_ours(args, rank, local_rank, world):
+def run_shell(args, rank, local_rank, world):
+    import ctypes as C
     import torch
     import torch.distributed as dist
-    from baryonification_b200 import _device as dv, _lib, engine, host
-    from baryonification_b200._ccl import default_mass_def
-    from baryonification_b200.tables import displacement_host_table
     import baryonification_b200 as bf
+    from baryonification_b200 import _device as dv, _lib, engine, host, sharding as sh
+    from baryonification_b200._ccl import backend_name, default_mass_def
+    from baryonification_b200.tables import displacement_host_table, profile_host_table
 
-    _lib.load(require_cuda=True)  # no CPU fallback: fail loudly
+    lib = _lib.load(require_cuda=True)  # no CPU fallback: fail loudly
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    cfg = make_inputs(args)
+    baryonify = args.workload == "shell"
+    cfg = shell_inputs(args)
+    model = cfg["model"] if baryonify else cfg["paint_model"]
     nside, eps = args.nside, cfg["epsilon_max"]
     npix = 12 * nside * nside
-    from baryonification_b200 import sharding as sh
     all_bands = sh.band_split(nside, world)
     ranges = [sh.band_pixel_range(nside, lo, hi) for lo, hi in all_bands]
     bands = all_bands[rank] if world > 1 else None
     if world > 1 and args.variant != "gather":
         raise SystemExit("multi-GPU sharding needs the gather variant")
+    F = sh.margin_pixels(nside)
+    fast_x = world > 1 and sh.fixed_margins_ok(ranges, F)
 
-    # ---- inputs resident in HBM -------------------------------------------------------------------------
-    s = host.shell_scalars(cfg["catalog"], cfg["catalog"].cosmo, default_mass_def(), eps, cfg["model"], True)
+    # ---- inputs resident in HBM -----------------------------------------------------------------------------
+    s = host.shell_scalars(cfg["catalog"], cfg["catalog"].cosmo, default_mass_def(), eps, model, baryonify)
     if world > 1:  # halos replicated to every shard their footprint overlaps (catalogue order kept)
         keep = sh.halos_touching_bands(s["vec"][:, 2], s["radius"], nside, *bands)
         s = sh._subset(s, keep)
-    eng = engine.ShellEngine(nside, engine.BARYONIFY, displacement_host_table(cfg["model"]), s, dev,
+    htab = displacement_host_table(model) if baryonify else profile_host_table(model, "2D")
+    eng = engine.ShellEngine(nside, engine.BARYONIFY if baryonify else engine.PAINT, htab, s, dev,
                              variant=args.variant, bands=bands).upload()
     orig_host = np.ascontiguousarray(cfg["field"].map)
-    orig_d = dv.to_dev(orig_host[eng.pix_first:eng.pix_last], dev=dev)
-    nloc = eng.pix_last - eng.pix_first
-    off = dv.empty((nloc, 3), dev=dev)
-    new_d = dv.zeros(npix, dev=dev)
-    full_d = dv.zeros(npix, dev=dev) if world > 1 else new_d
+    first, last = eng.pix_first, eng.pix_last
+    nloc = last - first
+    orig_d = dv.to_dev(orig_host[first:last], dev=dev) if baryonify else None
+    acc = dv.empty((nloc, 3) if baryonify else (nloc,), dev=dev)
+    new_d = dv.empty(npix, dev=dev) if (baryonify and not fast_x) else None
+    state = {}
 
     ev = lambda: torch.cuda.Event(enable_timing=True)
-    acc_ms = []
-
-    rg_ms = []
+    acc_ms, rg_ms, x_ms = [], [], []
 
     def step(timed):
         eng.recollapse()
         eng.bin()
-        a, b, c = ev(), ev(), ev()
+        a, b, c, d = ev(), ev(), ev(), ev()
         a.record()
-        eng.accumulate(off)
+        eng.accumulate(acc)
         b.record()
-        eng.regrid(orig_d, off, new_d, method=args.regrid)
-        c.record()
-        if world > 1:  # boundary mass exchange + gather of the finished band slices (the only collectives)
-            own = sh.exchange_boundary(new_d, ranges, window=64 * 4 * nside)
-            sh.gather_slices(own, ranges, out=full_d)
+        if baryonify:
+            if fast_x:  # the shard's partial sums over its range + fixed margins, then the boundary mass exchange
+                local, _ = eng.regrid_shard(orig_d, acc, F, rank > 0, rank < world - 1, method=args.regrid)
+                c.record()
+                state["own"] = sh.exchange_margins(local, ranges, F)
+            else:
+                eng.regrid(orig_d, acc, new_d, method=args.regrid)
+                c.record()
+                state["own"] = sh.exchange_boundary(new_d, ranges, window=64 * 4 * nside) if world > 1 else new_d
+        else:
+            c.record()
+            state["own"] = acc
+        d.record()
         if timed:
-            acc_ms.append((a, b))
-            rg_ms.append((b, c))
+            acc_ms.append((a, b)), rg_ms.append((b, c)), x_ms.append((c, d))
 
     def barrier():
         torch.cuda.synchronize(dev)
@@ -240,154 +321,145 @@ def run_ours(args, rank, local_rank, world):
 
     for _ in range(args.warmup):
         step(False)
+    barrier()
+    launches0 = lib.bf_launch_count()
     sampler = ClockSampler(local_rank).start() if rank == 0 else None
-    barrier()
-    t_a, t_b = ev(), ev()
-    t_a.record()
-    for _ in range(args.steps):
-        step(True)
-    t_b.record()
-    barrier()
+    ms_step_local, reps = min_timed_seconds(step, barrier, args.steps, ev, world, dev)
     clocks = sampler.stop() if sampler else None
-    ms = torch.tensor([t_a.elapsed_time(t_b) / args.steps, float(np.mean([a.elapsed_time(b) for a, b in acc_ms]))],
-                      dtype=torch.float64, device=dev)
+    launches = int(lib.bf_launch_count() - launches0)
+    mean = lambda prs: float(np.mean([a.elapsed_time(b) for a, b in prs])) if prs else 0.0
+    ms = torch.tensor([ms_step_local, mean(acc_ms), mean(rg_ms), mean(x_ms)], dtype=torch.float64, device=dev)
     pairs = torch.tensor([eng.pair_count()], dtype=torch.int64, device=dev)
-    if os.environ.get("BF_STEP_BREAKDOWN"):  # diagnostic: per-phase wall time with a device sync after every phase
-        ph = {}
-
-        def tick(name, t0):
-            torch.cuda.synchronize(dev)
-            ph[name] = ph.get(name, 0.0) + (time.perf_counter() - t0) * 1e3 / 3
-            return time.perf_counter()
-
-        for _ in range(3):
-            barrier()
-            t0 = time.perf_counter()
-            eng.recollapse(); t0 = tick("collapse", t0)
-            eng.bin(); t0 = tick("bin", t0)
-            eng.accumulate(off); t0 = tick("accumulate", t0)
-            eng.regrid(orig_d, off, new_d, method=args.regrid); t0 = tick("regrid", t0)
-            if world > 1:
-                own = sh.exchange_boundary(new_d, ranges, window=64 * 4 * nside); t0 = tick("exchange", t0)
-                sh.gather_slices(own, ranges, out=full_d); t0 = tick("gather", t0)
-        print(f"[rank {rank}] step phases (ms): " + ", ".join(f"{k} {v:.2f}" for k, v in ph.items()), file=sys.stderr, flush=True)
+    own = state["own"]
+    sums = torch.stack([own.sum(), orig_d.sum() if baryonify else own.sum()])
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(pairs)
-    ms_step, ms_acc = float(ms[0]), float(ms[1])
+        dist.all_reduce(sums)
+    ms_step, ms_acc, ms_rg, ms_x = (float(v) for v in ms)
     npairs = int(pairs[0])
-    mass_err = abs(float(full_d.sum()) / float(orig_host.sum()) - 1.0)
-    ms_rg = float(np.mean([a.elapsed_time(b) for a, b in rg_ms]))
-    # the other re-binning variants, timed alongside (not part of `value`)
-    regrid_used = eng.regrid_used
-    rg_all = {regrid_used: ms_rg}
-    alt_diff = {}
-    new_alt = dv.zeros(npix, dev=dev)
-    for other in ("gather", "sorted", "atomic"):
-        if other == regrid_used or (other == "gather" and world > 1):
-            continue
-        oa, ob = ev(), ev()
-        eng.regrid(orig_d, off, new_alt, method=other)
-        oa.record()
-        eng.regrid(orig_d, off, new_alt, method=other)
-        ob.record()
-        torch.cuda.synchronize(dev)
-        rg_all[eng.regrid_used] = oa.elapsed_time(ob)
-        if world == 1:  # (sharded: new_d holds ghosts)
-            alt_diff[eng.regrid_used] = float((new_alt - new_d).abs().max() / new_d.abs().max())
-    del new_alt
+    mass_err = abs(float(sums[0]) / float(sums[1]) - 1.0) if baryonify else None
 
-    # ---- e2e through the public API: host buffers in, host map out ---------------------------------------------
-    e2e = None
-    if not args.no_e2e and world == 1:
-        runner = bf.BaryonifyShell(cfg["catalog"], cfg["field"], eps, cfg["model"], verbose=False, device=local_rank,
-                                   variant=args.variant, regrid=args.regrid)
-        for _ in range(max(3, min(args.warmup, 4))):  # warm-up: page-in, allocator, and BOTH pinned result buffers
-            out = runner.process()                     # (the caller still holds result k while call k+1 runs)
-        ts = []
-        for _ in range(max(1, min(args.steps, 3))):
-            t0 = time.perf_counter()
-            out = runner.process()
+    # the other re-binning variants, timed alongside (not part of `value`): N = 1 only
+    regrid_used = getattr(eng, "regrid_used", None)
+    rg_all, alt_diff = ({regrid_used: ms_rg} if baryonify else {}), {}
+    if baryonify and world == 1:
+        new_alt = dv.zeros(npix, dev=dev)
+        for other in ("gather", "sorted", "atomic"):
+            if other == regrid_used:
+                continue
+            oa, ob = ev(), ev()
+            eng.regrid(orig_d, acc, new_alt, method=other)
+            oa.record()
+            eng.regrid(orig_d, acc, new_alt, method=other)
+            ob.record()
             torch.cuda.synchronize(dev)
+            rg_all[eng.regrid_used] = oa.elapsed_time(ob)
+            alt_diff[eng.regrid_used] = float((new_alt - new_d).abs().max() / new_d.abs().max())
+        del new_alt
+    fp64_rate = fp64_peak(dev) if rank == 0 else None
+
+    # ---- e2e through the public API: host buffers in, host map out -- the same quantity at every N ----------------
+    e2e, n1 = None, {}
+    if not args.no_e2e:
+        del acc, new_d, orig_d, eng, own, state  # (the engine's 10-20 GB of workspaces are not needed any more)
+        torch.cuda.empty_cache()
+        cls = bf.BaryonifyShell if baryonify else bf.PaintProfilesShell
+        runner = cls(cfg["catalog"], cfg["field"], eps, model, verbose=False, device=local_rank,
+                     variant=args.variant, regrid=args.regrid)
+        call = sh.ShardedShell(runner, device=local_rank) if world > 1 else runner
+        for _ in range(3):  # warm-up: page-in, allocator, BOTH result buffers (the caller holds result k during call k+1)
+            out = call.process()
+        ts = []
+        for _ in range(max(2, min(args.steps, 5))):
+            barrier()
+            t0 = time.perf_counter()
+            out = call.process()
+            barrier()
             ts.append(time.perf_counter() - t0)
         t_e2e = float(np.mean(ts))
-        h2d = sum(np.asarray(v).nbytes for v in s.values()) + cfg["model"].raw_input_d.nbytes + orig_host.nbytes
-        e2e = {"value": runner.npairs / t_e2e, "unit": "pairs/s", "h2d_bytes_per_step": int(h2d),
-               "d2h_bytes_per_step": int(out.nbytes), "ms": t_e2e * 1e3, "stages_ms":
-                   {k: round(v * 1e3, 2) for k, v in runner.timings.items()}}
-    elif not args.no_e2e:
-        # sharded e2e: every step also moves this rank's map slice H2D and rank 0 reads the reduced map back
-        pin_in = torch.from_numpy(orig_host[eng.pix_first:eng.pix_last]).pin_memory()
-        pin_out = torch.empty(npix, dtype=torch.float64).pin_memory() if rank == 0 else None
-        ts = []
-        for i in range(1 + max(1, min(args.steps, 3))):
-            barrier()
-            t0 = time.perf_counter()
-            orig_d.copy_(pin_in, non_blocking=True)
-            eng.upload()
-            step(False)
+        a, b = ranges[rank]
+        halo_bytes = 13 * 8 * (args.nhalo // world)  # 9 scalars + vec + radius... per halo prepared by this rank
+        e2e = {"value": (call.npairs if world > 1 else runner.npairs) / t_e2e, "unit": "pairs/s",
+               "h2d_bytes_per_step": int(halo_bytes + htab.values.nbytes + ((b - a) * 8 if baryonify else 0)),
+               "d2h_bytes_per_step": int((b - a) * 8), "ms": t_e2e * 1e3,
+               "bytes_are": "per rank (every rank moves its own band over its own PCIe link)" if world > 1 else "whole job",
+               "stages_ms": {k: (round(v * 1e3, 2) if not isinstance(v, bool) else v)
+                             for k, v in (call.timings if world > 1 else runner.timings).items()},
+               "includes": "host scalar set-up, H2D, kernels, D2H of the result, mass check"}
+        if world > 1 and not args.no_n1_check:  # outside every timed region: the N-GPU product vs ONE GPU, on rank 0
             if rank == 0:
-                pin_out.copy_(full_d, non_blocking=True)
+                single = cls(cfg["catalog"], cfg["field"], eps, model, verbose=False, device=local_rank,
+                             variant=args.variant, regrid=args.regrid).process()
+                diff = float(np.max(np.abs(single - out)))
+                scale = float(np.max(np.abs(single))) or 1.0
+                n1 = {"n1_max_abs_diff_over_scale": diff / scale,
+                      "n1_equal": bool(np.array_equal(single, out)) if not baryonify else bool(diff <= 1e-13 * scale),
+                      "n1_criterion": "bitwise (pixel owners)" if not baryonify else "max |N-GPU - 1-GPU| <= 1e-13 max|map| "
+                                      "(boundary mass is added in another order)"}
             barrier()
-            if i > 0:
-                ts.append(time.perf_counter() - t0)
-        t_e2e = float(np.mean(ts))
-        e2e = {"value": npairs / t_e2e, "unit": "pairs/s", "h2d_bytes_per_step": int(pin_in.numel() * 8),
-               "d2h_bytes_per_step": int(npix * 8) if rank == 0 else 0, "ms": t_e2e * 1e3,
-               "note": "host scalar set-up excluded (replicated catalogue prepared once); slice H2D + result D2H included"}
 
     if rank == 0:
         peak, peak_src = peaks()
-        alg_bytes = npairs / world * B_PAIR  # per launch (per rank)
+        kname = "gather_kernel<%d>" % (1 if baryonify else 0) if args.variant == "gather" else "shell_atomic_kernel"
+        alg_bytes = npairs / world * B_PAIR[args.workload]  # per launch (per rank)
         ach = alg_bytes / (ms_acc * 1e-3) / 1e9
+        traffic = measured_traffic(kname, "bf_shell_gather.cu") if (world == 1 and nside == 4096 and args.nhalo == 1_000_000) else None
+        fp64_ach = npairs / world * FP64_PER_PAIR[args.workload] / (ms_acc * 1e-3) / 1e9
         res = {
             "metric": "halo-pixel updates/sec", "value": npairs / (ms_step * 1e-3), "unit": "pairs/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"BaryonifyShell NSIDE={nside}, {args.nhalo} halos, epsilon_max={eps:g}, table 10x10x500",
-                       "variant": args.variant, "parallelism": f"ring-band x{world}", "pairs": npairs,
-                       "l2": "working set (offsets 24 B/pixel + maps) far exceeds the 126 MB L2",
-                       "mass_conservation_relerr": mass_err, "bin_entries": eng.nentries,
-                       "regrid": regrid_used, "regrid_ms": rg_all,
-                       "regrid_variants_max_reldiff": alt_diff},
-            "roofline": {"bound": "hbm", "kernel": "gather_kernel<1>" if args.variant == "gather" else "shell_atomic_kernel<1>",
-                         "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                         "traffic": (GATHER_TRAFFIC_BYTES if (world == 1 and args.variant == "gather" and nside == 4096
-                                                              and args.nhalo == 1_000_000) else None),
-                         "traffic_unit": "bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum, profiles/)",
-                         "peak_source": peak_src, "algorithmic_bytes_per_pair": B_PAIR, "kernel_ms": ms_acc,
-                         "note": "pairs are summed in registers: the kernel is fp64-issue bound, HBM traffic is one 24 B write per pixel"},
-            "e2e": e2e, "gpu_launches": {"gather": 8, "sorted": 9, "atomic": 6}[regrid_used] * args.steps, "clocks": clocks}
+            "config": dict({"workload": workload_name(args, eps), "variant": args.variant,
+                            "parallelism": f"ring-band x{world}", "pairs": npairs,
+                            "l2": "working set (offsets 24 B/pixel + maps + 4 GB of collapsed rows) far exceeds the 126 MB L2",
+                            "timed_region_repeats": reps,
+                            "output": "whole map in HBM" if world == 1 else "band-sharded: every rank holds its finished band in HBM",
+                            "stages_ms_max_over_ranks": {"pair_kernel": ms_acc, "regrid": ms_rg, "exchange": ms_x},
+                            "mass_conservation_relerr": mass_err, "bin_entries": None,
+                            "regrid": regrid_used, "regrid_ms": rg_all, "regrid_variants_max_reldiff": alt_diff,
+                            "cosmology_backend": backend_name(), "healpix_oracle": "restated (healpy not installable)"}, **n1),
+            "roofline": {"bound": "fp64", "kernel": kname, "kernel_ms": ms_acc,
+                         "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "peak_source": peak_src,
+                         "achieved_is": "ALGORITHMIC-equivalent bytes (SURVEY 8d: %g B/pair accumulator read-modify-write of the "
+                                        "reference) / kernel time; the kernel sums pairs in registers and never performs that "
+                                        "traffic, so this may exceed 1 -- the binding resource is `fp64`" % B_PAIR[args.workload],
+                         "traffic": traffic,
+                         "traffic_unit": "bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum; null = no capture "
+                                         "of the current kernel source, see profiles/traffic.json)",
+                         "dram": None if traffic is None else {"gbs": traffic / (ms_acc * 1e-3) / 1e9,
+                                                                "frac": traffic / (ms_acc * 1e-3) / 1e9 / peak},
+                         "fp64": {"instr_per_pair": FP64_PER_PAIR[args.workload], "achieved_ginstr_s": fp64_ach,
+                                  "peak_ginstr_s": fp64_rate, "frac": fp64_ach / fp64_rate if fp64_rate else None,
+                                  "peak_source": "measured live: bf_probe_fp64 (8 independent DFMA chains per thread)"}},
+            "e2e": e2e, "gpu_launches": launches, "gpu_launches_are": "counted by the library (bf_launch_count) over the timed region, this rank",
+            "clocks": clocks}
         if not args.no_cpu:
             cores = os.cpu_count() or 1
-            cb = cpu_baseline(cfg, args, cores)
-            v, t_full = cpu_value(cb, args.nhalo, npix)
-            res["cpu_baseline"] = {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port",
-                                   "sample": f"{cb['halos']} halos of the seed-42 shuffle (offset loop {cb['t_loop']:.1f} s, OpenMP x{cores}) "
-                                             f"+ re-binning of {cb['regrid_pixels']} pixels ({cb['t_regrid_sample']:.1f} s, serial); "
-                                             f"scaled linearly: full job ~{t_full:.0f} s", "extrapolated": True}
+            res["cpu_baseline"] = cpu_shell_record(cpu_shell_sample(cfg, args, cores, args.cpu_sample), args, npix, cores)
         emit(res)
     if world > 1:
         dist.destroy_process_group()
 
 
+# =====================================================================================================================
+# snapshot workload (C4)
+# =====================================================================================================================
 def run_snapshot(args, rank, local_rank, world):
     """BaryonifySnapshot: `npart_side`^3 particles in a 500 Mpc/h box, 1e5 halos, epsilon_max 5.  N > 1 splits the
-    particle array by index (weak in nothing: the same snapshot is divided, strong scaling); the halo grid is
-    replicated; there is no collective on the data path."""
+    particle array by index (strong scaling: the same snapshot is divided); the halo grid is replicated; there is no
+    collective on the data path."""
     import ctypes as C
     import torch
     import torch.distributed as dist
     import baryonification_b200 as bf
     from baryonification_b200 import _device as dv, _lib, sharding as sh, synthetic as syn
-    from oracle import ref_shim
-    ref_shim.install()
-    _lib.load(require_cuda=True)
+    lib = _lib.load(require_cuda=True)
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    nh = 100_000
+    nh = args.nhalo
     cfg = syn.config_snapshot(npart_side=args.npart_side, nhalo=nh, dim=3)
     cat = cfg["field"].cat
     a0, b0 = sh.index_split(cat.size, world)[rank]
@@ -398,7 +470,6 @@ def run_snapshot(args, rank, local_rank, world):
     cnt = dv.pair_counter(dev)
     ev = lambda: torch.cuda.Event(enable_timing=True)
     kms = []
-
     st = runner._upload(dev)  # per-halo scalars and the table are resident in HBM before the timed region, like the shell's
 
     def step(timed):
@@ -412,7 +483,6 @@ def run_snapshot(args, rank, local_rank, world):
         b.record()
         if timed:
             kms.append((a, b))
-        return st
 
     def barrier():
         torch.cuda.synchronize(dev)
@@ -422,31 +492,29 @@ def run_snapshot(args, rank, local_rank, world):
 
     for _ in range(args.warmup):
         step(False)
+    barrier()
+    launches0 = lib.bf_launch_count()
     sampler = ClockSampler(local_rank).start() if rank == 0 else None
-    barrier()
-    t_a, t_b = ev(), ev()
-    t_a.record()
-    for _ in range(args.steps):
-        step(True)
-    t_b.record()
-    barrier()
+    ms_local, reps = min_timed_seconds(step, barrier, args.steps, ev, world, dev)
     clocks = sampler.stop() if sampler else None
-    ms = torch.tensor([t_a.elapsed_time(t_b) / args.steps, float(np.mean([a.elapsed_time(b) for a, b in kms]))],
-                      dtype=torch.float64, device=dev)
+    launches = int(lib.bf_launch_count() - launches0)
+    ms = torch.tensor([ms_local, float(np.mean([a.elapsed_time(b) for a, b in kms]))], dtype=torch.float64, device=dev)
     pairs = cnt.clone()
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(pairs)
     ms_step, ms_k, npairs = float(ms[0]), float(ms[1]), int(pairs[0])
     # e2e: process() with host records in, host records out (pinned staging inside)
-    e2e = None
+    e2e, n1 = None, {}
     if not args.no_e2e:
+        del rec, out
+        torch.cuda.empty_cache()
         local = runner if world == 1 else sh.ShardedSnapshot(runner, device=local_rank)
         call = (lambda: local.process()) if world == 1 else (lambda: local.process(gather=False))
         for _ in range(3):  # warm-up incl. both pinned result buffers (result k is alive while call k+1 runs)
             res = call()
         ts = []
-        for _ in range(max(1, min(args.steps, 3))):
+        for _ in range(max(2, min(args.steps, 5))):
             barrier()
             t0 = time.perf_counter()
             res = call()
@@ -454,38 +522,253 @@ def run_snapshot(args, rank, local_rank, world):
             ts.append(time.perf_counter() - t0)
         t_e2e = float(np.mean(ts))
         e2e = {"value": cat.size / t_e2e, "unit": "particles/s", "h2d_bytes_per_step": int((b0 - a0) * 32),
-               "d2h_bytes_per_step": int(res.nbytes), "ms": t_e2e * 1e3}
+               "d2h_bytes_per_step": int(res.nbytes), "ms": t_e2e * 1e3,
+               "bytes_are": "per rank (every rank moves its own particle slice over its own PCIe link)" if world > 1 else "whole job",
+               "includes": "host scalar set-up, halo binning, H2D of the records, kernel, D2H of the displaced records"}
+        if world > 1 and not args.no_n1_check:
+            if rank == 0:  # rank 0's slice against a 1-GPU evaluation of the same slice's particles (particle-centric)
+                single = bf.BaryonifySnapshot(cfg["catalog"], cfg["field"], cfg["epsilon_max"], cfg["model"], verbose=False,
+                                              device=local_rank).process()
+                n1 = {"n1_equal": bool(all(np.array_equal(single[k][a0:b0], res[k]) for k in res.dtype.names)),
+                      "n1_criterion": "bitwise, rank 0's particle slice (no collective on the data path)"}
+            barrier()
     if rank == 0:
         peak, peak_src = peaks()
         alg = (cat.size * B_PARTICLE + npairs * B_SNAP_PAIR) / world
         ach = alg / (ms_k * 1e-3) / 1e9
+        traffic = measured_traffic("snap_gather_kernel<3,true>", "bf_snapshot.cu") if (world == 1 and args.npart_side == 512) else None
         out_j = {"metric": "particle updates/sec", "value": cat.size / (ms_step * 1e-3), "unit": "particles/s",
                  "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
                  "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                 "config": {"workload": f"BaryonifySnapshot {args.npart_side}^3 particles, L=500 Mpc/h, {nh} halos, "
-                                        "epsilon_max=5, table 10x10x500", "parallelism": f"particle-index x{world}",
-                            "pairs": npairs, "l2": "particle records (64 B/particle in+out) far exceed the 126 MB L2"},
+                 "config": dict({"workload": workload_name(args), "parallelism": f"particle-index x{world}",
+                                 "pairs": npairs, "timed_region_repeats": reps,
+                                 "l2": "particle records (64 B/particle in+out) far exceed the 126 MB L2"}, **n1),
                  "roofline": {"bound": "hbm", "kernel": "snap_gather_kernel<3,true>", "achieved": ach, "peak": peak,
                               "unit": "GB/s", "frac": ach / peak, "peak_source": peak_src, "kernel_ms": ms_k,
-                              "traffic": SNAP_TRAFFIC_BYTES if (world == 1 and args.npart_side == 512) else None,
+                              "traffic": traffic,
+                              "dram": None if traffic is None else {"gbs": traffic / (ms_k * 1e-3) / 1e9,
+                                                                     "frac": traffic / (ms_k * 1e-3) / 1e9 / peak},
+                              "compulsory_bytes": cat.size / world * 64.0,
                               "algorithmic_bytes": {"per_particle": B_PARTICLE, "per_pair": B_SNAP_PAIR}},
-                 "e2e": e2e, "gpu_launches": 8 * args.steps, "clocks": clocks}
+                 "e2e": e2e, "gpu_launches": launches, "clocks": clocks}
         if not args.no_cpu:
-            from oracle import runners as orc
-            cores = os.cpu_count() or 1
-            m = 2_000_000  # bounded sample: the first 2e6 particles against the full halo catalogue
-            sub = syn.ParticleSnapshot(x=cat["x"][:m], y=cat["y"][:m], z=cat["z"][:m], M=1.0, L=cfg["field"].L,
-                                       redshift=cfg["field"].redshift, cosmo=cfg["field"].cosmo)
-            r = orc.BaryonifySnapshot(cfg["catalog"], sub, cfg["epsilon_max"], cfg["model"], nthreads=cores)
-            t0 = time.perf_counter()
-            r.process()
-            dt = time.perf_counter() - t0
-            out_j["cpu_baseline"] = {"value": m / dt, "unit": "particles/s", "cores": cores, "kind": "port",
-                                     "sample": f"first {m} particles x all {nh} halos, cell-list ball query + displacement "
-                                               f"(OpenMP x{cores}) + apply, {dt:.1f} s", "extrapolated": False}
+            out_j["cpu_baseline"] = cpu_snapshot_record(cfg, args)
         emit(out_j)
     if world > 1:
         dist.destroy_process_group()
+
+
+def cpu_snapshot_record(cfg, args):
+    from oracle import ref_shim
+    ref_shim.install()
+    from oracle import runners as orc
+    from baryonification_b200 import synthetic as syn
+    cat = cfg["field"].cat
+    cores = os.cpu_count() or 1
+    m = min(2_000_000, cat.size)  # bounded sample: the first 2e6 particles against the full halo catalogue
+    sub = syn.ParticleSnapshot(x=cat["x"][:m], y=cat["y"][:m], z=cat["z"][:m], M=1.0, L=cfg["field"].L,
+                               redshift=cfg["field"].redshift, cosmo=cfg["field"].cosmo)
+    r = orc.BaryonifySnapshot(cfg["catalog"], sub, cfg["epsilon_max"], cfg["model"], nthreads=cores)
+    t0 = time.perf_counter()
+    r.process()
+    dt = time.perf_counter() - t0
+    return {"value": m / dt, "unit": "particles/s", "cores": cores, "kind": "port",
+            "sample": f"first {m} particles x all {args.nhalo} halos, cell-list ball query + displacement "
+                      f"(OpenMP x{cores}) + apply, {dt:.1f} s", "extrapolated": False}
+
+
+# =====================================================================================================================
+# grid3d workload (C5): BaryonifyGrid 3-D + Delta P(k)
+# =====================================================================================================================
+def grid_inputs(args):
+    from baryonification_b200 import synthetic as syn
+    return syn.config_grid(npix=args.ngrid, nhalo=args.nhalo, dim=3, L=500.0 / 0.7, epsilon_max=20.0)
+
+
+def run_grid3d(args, rank, local_rank, world):
+    """BaryonifyGrid 3-D on an `ngrid`^3 mass grid (row slabs of the first axis over the ranks) followed by the Delta P(k)
+    summary of the result: P(k) of the baryonified and of the original grid, S = P_bary / P_dmo.  Every stage goes through
+    the product's own classes (`BaryonifyGrid` / `sharding.ShardedGrid`, `PowerSpectrumGrid` / `ShardedPowerSpectrum`);
+    `value` is cell-halo pairs per second of the whole pass with the map resident in HBM."""
+    import torch
+    import torch.distributed as dist
+    import baryonification_b200 as bf
+    from baryonification_b200 import _device as dv, _lib, sharding as sh
+    lib = _lib.load(require_cuda=True)
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    cfg = grid_inputs(args)
+    G = cfg["field"]
+    n = G.Npix
+    runner = bf.BaryonifyGrid(cfg["catalog"], G, 20.0, cfg["model"], verbose=False, device=local_rank)
+    plan = sh.ShardedGrid(runner, device=local_rank)
+    pk = sh.ShardedPowerSpectrum(n, 500.0 / 0.7, Nk=180, device=local_rank)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    stage = {"pairs": [], "regrid": [], "pk": []}
+    res = plan.upload(dev)  # halos, table, this rank's slab (+ ghost rows) of the map: resident before the timed region
+    state = {}
+
+    def step(timed):
+        a, b, c, d = ev(), ev(), ev(), ev()
+        a.record()
+        off = plan.pairs_device(res)
+        b.record()
+        new = plan.regrid_device(res, off)
+        c.record()
+        kb, Pb, _ = pk.power_of_slab(new.reshape(-1, n, n))
+        kd, Pd, _ = pk.power_of_slab(res["orig_slab"].reshape(-1, n, n))
+        d.record()
+        state.update(k=kb, S=Pb / Pd, new=new)
+        if timed:
+            stage["pairs"].append((a, b)), stage["regrid"].append((b, c)), stage["pk"].append((c, d))
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    for _ in range(max(1, min(args.warmup, 3))):
+        step(False)
+    barrier()
+    launches0 = lib.bf_launch_count()
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    ms_local, reps = min_timed_seconds(step, barrier, args.steps, ev, world, dev)
+    clocks = sampler.stop() if sampler else None
+    launches = int(lib.bf_launch_count() - launches0)
+    mean = lambda prs: float(np.mean([a.elapsed_time(b) for a, b in prs]))
+    ms = torch.tensor([ms_local, mean(stage["pairs"]), mean(stage["regrid"]), mean(stage["pk"])], dtype=torch.float64, device=dev)
+    pairs = torch.tensor([plan.local_pairs], dtype=torch.int64, device=dev)
+    sums = torch.stack([state["new"].sum(), res["orig_slab"].sum()])
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(pairs)
+        dist.all_reduce(sums)
+    ms_step, ms_pairs, ms_rg, ms_pk = (float(v) for v in ms)
+    npairs = int(pairs[0])
+    S = state["S"]
+    e2e = None
+    if not args.no_e2e:
+        del res, state
+        torch.cuda.empty_cache()
+        ts = []
+        for i in range(1 + max(1, min(args.steps, 2))):
+            barrier()
+            t0 = time.perf_counter()
+            out = plan.process(gather=False) if world > 1 else runner.process()
+            barrier()
+            if i > 0:
+                ts.append(time.perf_counter() - t0)
+        t_e2e = float(np.mean(ts))
+        e2e = {"value": npairs / t_e2e, "unit": "pairs/s", "ms": t_e2e * 1e3,
+               "h2d_bytes_per_step": int(G.map.nbytes // world), "d2h_bytes_per_step": int(out.nbytes),
+               "bytes_are": "per rank (row slab)" if world > 1 else "whole job",
+               "includes": "BaryonifyGrid.process(): host scalar set-up, H2D of the map, kernels, D2H of the new map, mass check "
+                           "(the Delta P(k) summary is part of `value`, not of this call)"}
+    if rank == 0:
+        peak, peak_src = peaks()
+        alg = (npairs * B_GRID_PAIR + float(n) ** 3 * B_GRID_CELL) / world
+        ach = alg / ((ms_pairs + ms_rg) * 1e-3) / 1e9
+        ok = np.isfinite(S)
+        out_j = {"metric": "halo-cell updates/sec", "value": npairs / (ms_step * 1e-3), "unit": "pairs/s",
+                 "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                 "config": {"workload": workload_name(args), "parallelism": f"row-slab x{world}", "pairs": npairs,
+                            "timed_region_repeats": reps,
+                            "stages_ms_max_over_ranks": {"pair_stage": ms_pairs, "regrid": ms_rg, "delta_pk": ms_pk},
+                            "mass_conservation_relerr": abs(float(sums[0]) / float(sums[1]) - 1.0),
+                            "delta_pk": {"nk": 180, "S_min": float(np.min(S[ok])), "S_max": float(np.max(S[ok])),
+                                         "S_at_k_nyquist_over_4": float(S[ok][len(S[ok]) // 4])},
+                            "l2": f"{n}^3 cells x (8 + 24) B far exceed the 126 MB L2"},
+                 "roofline": {"bound": "hbm", "kernel": "grid_gather_kernel + grid_regrid_gather_kernel", "achieved": ach,
+                              "peak": peak, "unit": "GB/s", "frac": ach / peak, "peak_source": peak_src,
+                              "kernel_ms": ms_pairs + ms_rg, "traffic": None,
+                              "algorithmic_bytes": {"per_pair": B_GRID_PAIR, "per_cell": B_GRID_CELL}},
+                 "e2e": e2e, "gpu_launches": launches, "clocks": clocks}
+        if not args.no_cpu:
+            out_j["cpu_baseline"] = cpu_grid_record(cfg, args)
+        emit(out_j)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_grid_record(cfg, args, nsample=2000):
+    """Oracle port of BaryonifyGrid's per-halo loop on the first `nsample` halos of the seed-42 shuffle (OpenMP over
+    halos); the serial re-binning is not part of the sample.  Scaled linearly in halos."""
+    import copy
+    from oracle import ref_shim
+    ref_shim.install()
+    from oracle import runners as orc
+    cores = os.cpu_count() or 1
+    cat = cfg["catalog"]
+    nh = len(cat.cat)
+    m = min(nsample, nh)
+    idx = np.sort(np.random.default_rng(42).choice(nh, size=nh, replace=False)[:m])
+    sub = copy.copy(cat)
+    sub.cat = cat.cat[idx]
+    r = orc.BaryonifyGrid(sub, cfg["field"], 20.0, cfg["model"], nthreads=cores)
+    t0 = time.perf_counter()
+    r.offsets()
+    dt = time.perf_counter() - t0
+    return {"value": r.npairs / dt, "unit": "pairs/s", "cores": cores, "kind": "port",
+            "sample": f"pair loop of {m} halos of the seed-42 shuffle (OpenMP x{cores}), {dt:.1f} s; the serial re-binning "
+                      "is not included", "extrapolated": True}
+
+
+# =====================================================================================================================
+# reference arm
+# =====================================================================================================================
+def run_reference(args, rank, world):
+    """CPU arm: the oracle port of the reference's loop with all host threads (the reference itself is pure Python and
+    needs pyccl + healpy, neither installable here).  Each step is the SAME bounded sample as the repo
+    arm's cpu_baseline."""
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    vals, times, rec = [], [], None
+    if args.workload in ("shell", "paint"):
+        cfg = shell_inputs(args)
+        npix = cfg["field"].map.size
+        for i in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            cb = cpu_shell_sample(cfg, args, cores, args.cpu_sample)
+            dt = time.perf_counter() - t0
+            if i >= args.warmup:
+                vals.append(cpu_shell_value(cb, args.nhalo, npix)[0])
+                times.append(dt)
+        rec = cpu_shell_record(cb, args, npix, cores)
+        metric, unit = "halo-pixel updates/sec", "pairs/s"
+    elif args.workload == "snapshot":
+        from baryonification_b200 import synthetic as syn
+        cfg = syn.config_snapshot(npart_side=args.npart_side, nhalo=args.nhalo, dim=3)
+        for i in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            rec = cpu_snapshot_record(cfg, args)
+            if i >= args.warmup:
+                vals.append(rec["value"])
+                times.append(time.perf_counter() - t0)
+        metric, unit = "particle updates/sec", "particles/s"
+    else:
+        cfg = grid_inputs(args)
+        for i in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            rec = cpu_grid_record(cfg, args)
+            if i >= args.warmup:
+                vals.append(rec["value"])
+                times.append(time.perf_counter() - t0)
+        metric, unit = "halo-cell updates/sec", "pairs/s"
+    v = float(np.mean(vals))
+    rec = dict(rec, value=v)
+    emit({"impl": "reference", "metric": metric, "value": v, "unit": unit, "n_gpus": args.gpus,
+          "steps": args.steps, "warmup": args.warmup, "ms_per_step": float(np.mean(times) * 1e3),
+          "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+          "extrapolated": bool(rec.get("extrapolated")),
+          "config": {"workload": workload_name(args)},
+          "cpu_baseline": rec,
+          "e2e": {"value": v, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+          "gpu_launches": 0})
 
 
 _REAL_STDOUT = None
@@ -515,8 +798,10 @@ def main():
         run_reference(args, rank, world)
     elif args.workload == "snapshot":
         run_snapshot(args, rank, local_rank, world)
+    elif args.workload == "grid3d":
+        run_grid3d(args, rank, local_rank, world)
     else:
-        run_ours(args, rank, local_rank, world)
+        run_shell(args, rank, local_rank, world)
 
 
 if __name__ == "__main__":

@@ -29,9 +29,22 @@ extern "C" {
 #define BF_E_CAPACITY (-4)  /* bf_snap_bin_halos: >= 2^25 (cell, halo) entries at this `ng`; call again with fewer cells */
 #define BF_E_WINDOW (-3)    /* bf_{grid,shell}_regrid_gather: displacement window too wide, use the _sorted variant */
 
+/* `mode` of the pair entry points.  The two runner families historically number it differently -- use the names:
+ * shell entries (bf_shell_bin_halos, bf_shell_gather): 0 = paint, 1 = baryonify;
+ * grid entries (bf_grid_gather, bf_grid_gather_rows):  0 = baryonify, 1 = paint. */
+#define BF_SHELL_MODE_PAINT 0
+#define BF_SHELL_MODE_BARYONIFY 1
+#define BF_GRID_MODE_BARYONIFY 0
+#define BF_GRID_MODE_PAINT 1
+
 const char *bf_last_error(void);
 int bf_version(void);
 int bf_device_sm_count(int *sm_count_host);
+/* Kernel launches of this library since it was loaded (CUB's internal kernels not included). */
+unsigned long long bf_launch_count(void);
+/* Throughput probe: `blocks` CTAs of 256 threads, each thread runs 8 independent chains of `iters` fused multiply-adds
+ * in fp64; out is [blocks * 256] doubles (scratch), *dfma_per_thread_host = 8 * iters.  Time it with events. */
+int bf_probe_fp64(int blocks, int iters, double *out, unsigned long long *dfma_per_thread_host, void *stream);
 
 /* A (ln(1+z), ln M, ln r) table resident on the device.  `values` holds d (displacement,
  * Profiles/BaryonCorrection.py:315) or ln(profile) (utils/Tabulate.py:237-238). */
@@ -145,7 +158,8 @@ int bf_shell_regrid_sorted(int64_t nside, int64_t pix_first, int64_t pix_last, c
  * sources inside that window.  No sort, no atomics on the map, 48 B of workspace per pixel.  Destinations within
  * BF_SHELL_GATHER_POLAR rings of a pole scan whole source rings.  window_host[3] (may be NULL) receives
  * (dr_min, dr_max, dj_max).  BF_E_WINDOW when a destination would have to scan more than BF_SHELL_GATHER_MAX_WINDOW
- * sources (fall back to bf_shell_regrid_sorted).  new_map is += (zero it first).  Synchronises `stream` once. */
+ * sources (fall back to bf_shell_regrid_sorted).  Every pixel of new_map is WRITTEN (0 where nothing lands): no zero
+ * fill is needed.  Synchronises `stream` once. */
 #define BF_SHELL_GATHER_POLAR 8
 #define BF_SHELL_GATHER_MAX_WINDOW 165
 size_t bf_shell_regrid_gather_ws_bytes(int64_t nside);
@@ -154,7 +168,7 @@ int bf_shell_regrid_gather(int64_t nside, const double *orig_map, const double *
 /* The two passes on their own, so that a caller can produce the map in destination ranges and start reading each
  * range back while the next one is computed: _emit writes the deposits into ws and returns the window in
  * window_host[3] (an empty field gives dr_min > dr_max; BF_E_WINDOW as above; synchronises `stream` once), _range
- * adds the deposits of destinations dest_first <= d < dest_last to new_map (+=), given that window. */
+ * writes the sums of destinations dest_first <= d < dest_last to new_map (=; 0 where nothing lands), given that window. */
 int bf_shell_regrid_gather_emit(int64_t nside, const double *orig_map, const double *pix_offsets, void *ws,
                                 size_t ws_bytes, int *window_host, void *stream);
 int bf_shell_regrid_gather_range(int64_t nside, const void *ws, size_t ws_bytes, const int *window_host,
@@ -168,6 +182,13 @@ int bf_shell_regrid_gather_range(int64_t nside, const void *ws, size_t ws_bytes,
 int bf_shell_regrid_gather_emit_range(int64_t nside, int64_t pix_first, int64_t pix_last, const double *orig_map,
                                       const double *pix_offsets, void *ws, size_t ws_bytes, int *window_host,
                                       void *stream);
+/* _emit for one GROUP of a pipelined whole-sphere run: only the keys of pix_first <= p < pix_last are written (the other
+ * groups' keys, already there, survive) and window_host[3] is the window of THIS group's sources.  The caller emits the
+ * groups in ascending pixel order and may run _range over destinations all of whose possible sources -- the rings
+ * r_d - dr_max ... r_d - dr_min of the UNION of the windows so far -- have been emitted.  Only BF_E_WINDOW for cost. */
+int bf_shell_regrid_gather_emit_part(int64_t nside, int64_t pix_first, int64_t pix_last, const double *orig_map,
+                                     const double *pix_offsets, void *ws, size_t ws_bytes, int *window_host,
+                                     void *stream);
 
 /* ---- Grid runners (Map2DRunner.py) ---- */
 typedef struct {

@@ -289,3 +289,48 @@ def _slab_fft_ranks(rank, world, N, Nk):
 @pytest.mark.parametrize("world,N,Nk", [(2, 16, 7), (3, 10, 5), (3, 9, 4), (2, 2, 1)])
 def test_slab_decomposed_rfftn_and_piecewise_binning(world, N, Nk):
     _run(_slab_fft_ranks, world, N, Nk)
+
+
+# ------------------------------------------------------------------ round 2: fixed-margin exchange, shared host arena
+def _margin_ranks(rank, world, n, F):
+    """Every rank deposits random mass over its range widened by F; the fixed-margin exchange must give every owner the
+    sum of all deposits on its pixels (what exchange_boundary gives with its negotiated extents)."""
+    rng = np.random.default_rng(5)
+    ranges = sh.index_split(n, world)
+    assert sh.fixed_margins_ok(ranges, F)
+    want = np.zeros(n)
+    locals_ = []
+    for r, (a, b) in enumerate(ranges):
+        w0, w1 = a - (F if r > 0 else 0), b + (F if r < world - 1 else 0)
+        dep = rng.random(w1 - w0)
+        dep[rng.random(w1 - w0) < 0.5] = 0.0
+        want[w0:w1] += dep
+        locals_.append(dep)
+    own = sh.exchange_margins(torch.from_numpy(locals_[rank].copy()), ranges, F)
+    a, b = ranges[rank]
+    assert own.numel() == b - a
+    assert np.allclose(own.numpy(), want[a:b], rtol=1e-15, atol=0)
+    # ... and the shared host arena: every rank writes its piece, every rank sees the whole array
+    arena = sh.SharedHostArena(n)
+    arena.tensor[a:b].copy_(own)
+    dist.barrier()
+    assert np.allclose(arena.array, want, rtol=1e-15, atol=0)
+    again = sh.SharedHostArena(n)  # a second arena is a different segment
+    again.array[a:b] = -1.0
+    dist.barrier()
+    assert np.allclose(arena.array, want, rtol=1e-15, atol=0) and np.all(again.array == -1.0)
+
+
+@pytest.mark.parametrize("world,n,F", [(2, 1000, 100), (3, 999, 333), (3, 40, 7)])
+def test_fixed_margin_exchange_and_shared_host_arena(world, n, F):
+    _run(_margin_ranks, world, n, F)
+
+
+def test_fixed_margins_need_bands_longer_than_the_margin():
+    assert not sh.fixed_margins_ok([(0, 100)], 10)                   # one rank: nothing to exchange
+    assert not sh.fixed_margins_ok([(0, 100), (100, 105)], 10)       # a range shorter than the margin
+    assert sh.fixed_margins_ok([(0, 100), (100, 110)], 10)
+    ranges = [sh.band_pixel_range(4096, *b) for b in sh.band_split(4096, 8)]
+    assert sh.fixed_margins_ok(ranges, sh.margin_pixels(4096))       # the benchmark partition takes the fast path
+    small = [sh.band_pixel_range(16, *b) for b in sh.band_split(16, 2)]
+    assert not sh.fixed_margins_ok(small, sh.margin_pixels(16))      # small spheres: the general exchange
