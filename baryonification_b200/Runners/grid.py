@@ -48,7 +48,15 @@ class DefaultRunnerGrid:
                 assert "c_ell" in names, "The 'c_ell' column is missing, but you set use_ellipticity = True"
             assert "A_ell" in names, "The 'A_ell' column is missing, but you set use_ellipticity = True"
 
+    def _progress(self, what):
+        """Per-stage progress lines under the reference's ``verbose`` flag (its tqdm bar over halos, Map2DRunner.py:476 /
+        :714, has no per-halo counterpart here: the loop is a handful of kernel launches)."""
+        if self.verbose:
+            import sys
+            print("[%s] %s" % (type(self).__name__, what), file=sys.stderr, flush=True)
+
     def _prepare(self, table_host, baryonify, dev):
+        self._progress("host set-up of %d halos, table upload, (z, M) collapse" % len(self.HaloNDCatalog.cat))
         keys = vars(self.model).get("p_keys", [])
         if len(keys) > 0:  # Map2DRunner.py:469-474 / :707-712
             txt = (f"You asked to use {keys} properties in Baryonification. You must pass a ParamTabulatedProfile"
@@ -78,6 +86,7 @@ class DefaultRunnerGrid:
         G = self.GriddedMap
         lib = _lib.load(require_cuda=True)
         dim, nh = s["dim"], s["cut"].size
+        self._progress("halo binning into grid tiles + pair stage (%s)" % self.variant)
         self.variant_used = self.variant
         if self.variant == "gather" and nh > 0 and int(np.max(s["Nsize"])) > G.Npix:
             self.variant_used = "atomic"  # a cut-out wider than the grid: numpy's duplicate-dropping += semantics
@@ -137,6 +146,7 @@ class BaryonifyGrid(DefaultRunnerGrid):
             orig_d = up.result()
             new_d = dv.zeros(orig.size, dev=dev)
             dim = 2 if G.is2D else 3
+            self._progress("re-binning (%s) + read-back" % self.regrid)
             lib = _lib.load(require_cuda=True)
             mode = self.regrid
             new_map = None

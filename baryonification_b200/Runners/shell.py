@@ -74,7 +74,11 @@ class DefaultRunner:
             after()
         t0 = time.perf_counter()
         eng = engine.ShellEngine(self.LightconeShell.NSIDE, mode, htab, s, dev, variant=self.variant, bands=bands)
+        # a repeated process() sizes the key list from the previous call and skips the counting pass of the binning
+        eng.max_entries = getattr(self, "_bin_hint", {}).get((mode, bands, len(self.HaloLightConeCatalog.cat)), 0)
         eng.upload().bin()
+        if eng.nentries is not None:
+            self._bin_hint = {(mode, bands, len(self.HaloLightConeCatalog.cat)): eng.nentries + eng.nentries // 16 + 1024}
         self._tick("upload_bin", t0, dev)
         return eng
 

@@ -107,6 +107,14 @@ class DefaultRunnerSnapshot:
         self.timings = {}
 
 
+    def _progress(self, what):
+        """Per-stage progress lines under the reference's ``verbose`` flag (its tqdm bar over halos,
+        SnapshotRunner.py:205, has no per-halo counterpart here)."""
+        if self.verbose:
+            import sys
+            print("[%s] %s" % (type(self).__name__, what), file=sys.stderr, flush=True)
+
+
 class BaryonifySnapshot(DefaultRunnerSnapshot):
     """``process()`` returns a displaced copy of ``ParticleSnapshot.cat`` (SnapshotRunner.py:250-262)."""
 
@@ -204,7 +212,9 @@ class BaryonifySnapshot(DefaultRunnerSnapshot):
             cat = S.cat
             fast = self._is_reference_layout(cat)
             pipe = _RecordPipeline(cat.view(np.float64).reshape(-1, 4), dev) if fast else None  # travels during set-up
+            self._progress("host set-up of %d halos, halo binning into the periodic grid" % len(self.HaloNDCatalog.cat))
             st = self._setup(dev)
+            self._progress("ball query + displacement of %d particles (upload / kernel / read-back in chunks)" % cat.size)
             dim, s = st["dim"], st["s"]
             cnt = dv.pair_counter(dev)
             self.timings["setup"] = time.perf_counter() - t0

@@ -10,7 +10,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(HERE, "libbaryonification_b200.so")
+# BF_LIB_PATH: a differently-compiled build of the same library (kernel tuning experiments, scripts/build_variant.py)
+SO_PATH = os.environ.get("BF_LIB_PATH") or os.path.join(HERE, "libbaryonification_b200.so")
 
 _dbl_p = C.c_void_p  # raw device pointers
 _i64 = C.c_int64

@@ -211,8 +211,21 @@ __device__ __forceinline__ void bfh_ang2vec_lonlat(double lon, double lat, doubl
 
 // get_interpol(pointing(theta, phi)) with phi already normalised to [0, 2pi)
 // (ir1 = ring above the point, 0 at the north pole: pix[0..1] lie on ring max(ir1, 1), pix[2..3] on min(ir1 + 1, 4N - 1))
+// `theta_tab` (optional): co-latitudes of rings 0 .. 4 nside as bfh_ring_info2 computes them (filled by calling it, so
+// the values are the same bits); the two acos / atan2 per point become two loads.  The integer ring data of
+// bfh_ring_info_small equal bfh_ring_info2's.
+__device__ __forceinline__ void bfh_ring_info2_tab(const bf_hpx &h, i64 ring, i64 &startpix, i64 &ringpix, double &theta,
+                                                   bool &shifted, const double *__restrict__ theta_tab) {
+    if (theta_tab) {
+        bfh_ring_info_small(h, ring, startpix, ringpix, shifted);
+        theta = __ldg(theta_tab + ring);
+    } else {
+        bfh_ring_info2(h, ring, startpix, ringpix, theta, shifted);
+    }
+}
+
 __device__ __forceinline__ void bfh_get_interpol_r(const bf_hpx &h, double theta, double phi, i64 pix[4],
-                                                   double wgt[4], i64 &ir1) {
+                                                   double wgt[4], i64 &ir1, const double *__restrict__ theta_tab = nullptr) {
     double z = cos(theta);
     ir1 = bfh_ring_above(h, z);
     i64 ir2 = ir1 + 1;
@@ -220,7 +233,7 @@ __device__ __forceinline__ void bfh_get_interpol_r(const bf_hpx &h, double theta
     i64 sp, nr, i1, i2;
     bool shift;
     if (ir1 > 0) {
-        bfh_ring_info2(h, ir1, sp, nr, theta1, shift);
+        bfh_ring_info2_tab(h, ir1, sp, nr, theta1, shift, theta_tab);
         dphi = BFH_TWOPI / (double)nr;
         tmp = (phi / dphi - 0.5 * (shift ? 1.0 : 0.0));
         i1 = (tmp < 0) ? (i64)tmp - 1 : (i64)tmp;
@@ -232,7 +245,7 @@ __device__ __forceinline__ void bfh_get_interpol_r(const bf_hpx &h, double theta
         wgt[0] = 1 - w1;  wgt[1] = w1;
     }
     if (ir2 < 4 * h.nside) {
-        bfh_ring_info2(h, ir2, sp, nr, theta2, shift);
+        bfh_ring_info2_tab(h, ir2, sp, nr, theta2, shift, theta_tab);
         dphi = BFH_TWOPI / (double)nr;
         tmp = (phi / dphi - 0.5 * (shift ? 1.0 : 0.0));
         i1 = (tmp < 0) ? (i64)tmp - 1 : (i64)tmp;
@@ -271,10 +284,10 @@ __device__ __forceinline__ void bfh_get_interpol(const bf_hpx &h, double theta, 
 }
 
 __device__ __forceinline__ void bfh_interp_lonlat_r(const bf_hpx &h, double lon, double lat, i64 pix[4],
-                                                    double wgt[4], i64 &ir1) {
+                                                    double wgt[4], i64 &ir1, const double *__restrict__ theta_tab = nullptr) {
     double theta = BFH_PI / 2.0 - lat * BFH_DEG2RAD;
     double phi = bfh_fmodulo(lon * BFH_DEG2RAD, BFH_TWOPI);
-    bfh_get_interpol_r(h, theta, phi, pix, wgt, ir1);
+    bfh_get_interpol_r(h, theta, phi, pix, wgt, ir1, theta_tab);
 }
 
 __device__ __forceinline__ void bfh_interp_lonlat(const bf_hpx &h, double lon, double lat, i64 pix[4],
@@ -287,7 +300,8 @@ __device__ __forceinline__ void bfh_interp_lonlat(const bf_hpx &h, double lon, d
 // vec2ang(lonlat=True) in DEGREES -> get_interp_weights(lonlat=True).  One definition for every re-binning variant,
 // so that their deposits are the same bits.
 __device__ __forceinline__ void bfh_displaced_deposits_r(const bf_hpx &h, i64 p, const double off[3], i64 cp[4],
-                                                         double w[4], i64 &ir1) {
+                                                         double w[4], i64 &ir1,
+                                                         const double *__restrict__ theta_tab = nullptr) {
     double v[3];
     bfh_pix2vec(h, p, v);
     double x = v[0] + off[0], y = v[1] + off[1], z = v[2] + off[2];
@@ -295,7 +309,7 @@ __device__ __forceinline__ void bfh_displaced_deposits_r(const bf_hpx &h, i64 p,
     double theta = acos(z / dnorm);
     double phi = atan2(y, x);
     if (phi < 0) phi += BFH_TWOPI;
-    bfh_interp_lonlat_r(h, phi * BFH_RAD2DEG, 90.0 - theta * BFH_RAD2DEG, cp, w, ir1);
+    bfh_interp_lonlat_r(h, phi * BFH_RAD2DEG, 90.0 - theta * BFH_RAD2DEG, cp, w, ir1, theta_tab);
 }
 
 __device__ __forceinline__ void bfh_displaced_deposits(const bf_hpx &h, i64 p, const double off[3], i64 cp[4],

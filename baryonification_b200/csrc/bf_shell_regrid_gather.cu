@@ -54,10 +54,24 @@ __global__ void __launch_bounds__(256) rg_init_kernel(rg_window *w) {
 
 // Sources p_first <= p < p_last (orig / off are that slice); pixels of the margin e_first <= p < e_last around it only
 // get the "no deposit" key, so that a ring-band shard can gather its partial sums without reading stale keys.
+// co-latitudes of rings 1 .. 4 nside - 1 exactly as the interpolation routine computes them (it is the routine that
+// fills the table), so that the emit pass reads two doubles per pixel instead of evaluating two acos / atan2
+__global__ void __launch_bounds__(256) rg_theta_kernel(bf_hpx h, double *__restrict__ theta_tab) {
+    const i64 ring = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (ring > 4 * h.nside) return;
+    double theta = 0.0;
+    if (ring >= 1 && ring < 4 * h.nside) {
+        i64 sp, nr; bool sh;
+        bfh_ring_info2(h, ring, sp, nr, theta, sh);
+    }
+    theta_tab[ring] = theta;
+}
+
 __global__ void __launch_bounds__(256) rg_emit_kernel(bf_hpx h, i64 p_first, i64 p_last, i64 e_first, i64 e_last,
                                                       const double *__restrict__ orig_s,
                                                       const double *__restrict__ off_s, uint4 *__restrict__ key,
-                                                      double *__restrict__ val, rg_window *__restrict__ win) {
+                                                      double *__restrict__ val, rg_window *__restrict__ win,
+                                                      const double *__restrict__ theta_tab) {
     const i64 p = e_first + (i64)blockIdx.x * blockDim.x + threadIdx.x;
     int dr_min = 0x7fffffff, dr_max = -0x7fffffff, dj_max = 0;
     if (p < e_last && (p < p_first || p >= p_last)) {
@@ -70,7 +84,7 @@ __global__ void __launch_bounds__(256) rg_emit_kernel(bf_hpx h, i64 p_first, i64
         if (m > 0) {  // HealpixRunner.py:335
             const double o3[3] = {off[3 * p], off[3 * p + 1], off[3 * p + 2]};
             i64 cp[4], ir1; double w[4];
-            bfh_displaced_deposits_r(h, p, o3, cp, w, ir1);
+            bfh_displaced_deposits_r(h, p, o3, cp, w, ir1, theta_tab);
             kk = make_uint4((u32)cp[0], (u32)cp[1], (u32)cp[2], (u32)cp[3]);
 #pragma unroll
             for (int k = 0; k < 4; ++k) vv[k] = w[k] * m;
@@ -119,22 +133,39 @@ __global__ void __launch_bounds__(256) rg_emit_kernel(bf_hpx h, i64 p_first, i64
     }
 }
 
-// the deposits of sources q0 .. q1 (one ring segment, ascending) that name destination d
-__device__ __forceinline__ void rg_scan(const uint4 *__restrict__ key, const double *__restrict__ val, u32 q0, u32 q1,
-                                        u32 d, double &s, bool &any) {
-    for (u32 q = q0; q <= q1; ++q) {
-        const uint4 k = __ldg(key + q);
-        if (k.x == d || k.y == d || k.z == d || k.w == d) {  // (about one source in six)
-            const double *v = val + 4 * (size_t)q;
-            if (k.x == d) { s = any ? s + v[0] : v[0]; any = true; }
-            if (k.y == d) { s = any ? s + v[1] : v[1]; any = true; }
-            if (k.z == d) { s = any ? s + v[2] : v[2]; any = true; }
-            if (k.w == d) { s = any ? s + v[3] : v[3]; any = true; }
-        }
+// the deposits of sources q0 .. q1 (one ring segment, ascending) that name destination d.  Keys are fetched four at a
+// time before any of them is looked at, so that the loads of a segment (5 keys for the usual +-2 pixel window) are in
+// flight together instead of one behind the other; the order of the additions is unchanged.
+__device__ __forceinline__ void rg_take(const uint4 k, const double *__restrict__ val, u32 q, u32 d, double &s, bool &any) {
+    if (k.x == d || k.y == d || k.z == d || k.w == d) {  // (about one source in six)
+        const double *v = val + 4 * (size_t)q;
+        if (k.x == d) { s = any ? s + v[0] : v[0]; any = true; }
+        if (k.y == d) { s = any ? s + v[1] : v[1]; any = true; }
+        if (k.z == d) { s = any ? s + v[2] : v[2]; any = true; }
+        if (k.w == d) { s = any ? s + v[3] : v[3]; any = true; }
     }
 }
 
-__global__ void __launch_bounds__(256) rg_gather_kernel(bf_hpx h, int dr_min, int dr_max, int P, i64 d_first,
+__device__ __forceinline__ void rg_scan(const uint4 *__restrict__ key, const double *__restrict__ val, u32 q0, u32 q1,
+                                        u32 d, double &s, bool &any) {
+    u32 q = q0;
+    for (; q + 3 <= q1; q += 4) {
+        const uint4 k0 = __ldg(key + q), k1 = __ldg(key + q + 1), k2 = __ldg(key + q + 2), k3 = __ldg(key + q + 3);
+        rg_take(k0, val, q, d, s, any);
+        rg_take(k1, val, q + 1, d, s, any);
+        rg_take(k2, val, q + 2, d, s, any);
+        rg_take(k3, val, q + 3, d, s, any);
+    }
+    if (q <= q1) {  // 1..3 left
+        const u32 n = q1 - q;
+        const uint4 k0 = __ldg(key + q), k1 = __ldg(key + min(q + 1, q1)), k2 = __ldg(key + min(q + 2, q1));
+        rg_take(k0, val, q, d, s, any);
+        if (n >= 1) rg_take(k1, val, q + 1, d, s, any);
+        if (n >= 2) rg_take(k2, val, q + 2, d, s, any);
+    }
+}
+
+__global__ void __launch_bounds__(256, 4) rg_gather_kernel(bf_hpx h, int dr_min, int dr_max, int P, i64 d_first,
                                                         i64 d_last, const uint4 *__restrict__ key,
                                                         const double *__restrict__ val, double *__restrict__ out) {
     const i64 d64 = d_first + (i64)blockIdx.x * blockDim.x + threadIdx.x;
@@ -173,10 +204,10 @@ __global__ void __launch_bounds__(256) rg_gather_kernel(bf_hpx h, int dr_min, in
 
 extern "C" size_t bf_shell_regrid_gather_ws_bytes(int64_t nside) {
     if (nside <= 0) return 0;
-    return (size_t)(12 * nside * nside) * 48 + 512;
+    return (size_t)(12 * nside * nside) * 48 + 512 + 8 * (size_t)(4 * nside + 2);
 }
 
-// workspace layout: [window | keys uint4[npix] | values double[4 npix]]
+// workspace layout: [window | keys uint4[npix] | values double[4 npix] | ring co-latitudes double[4 nside + 1]]
 static int rg_layout(int64_t nside, void *ws, size_t ws_bytes, const char *who, bf_hpx &h, rg_window *&win, uint4 *&key,
                      double *&val) {
     BF_REQUIRE(nside > 0, "nside");
@@ -194,6 +225,9 @@ static int rg_layout(int64_t nside, void *ws, size_t ws_bytes, const char *who, 
     val = (double *)(base + 256 + (size_t)h.npix * 16);
     return BF_OK;
 }
+
+// ring co-latitude table: behind the values, [4 nside + 1] doubles
+static double *rg_theta_tab(const bf_hpx &h, void *ws) { return (double *)((char *)ws + 512 + (size_t)h.npix * 48); }
 
 // sources pix_first <= p < pix_last; orig_map / pix_offsets are that slice
 static int rg_emit(int64_t nside, int64_t pix_first, int64_t pix_last, const double *orig_map, const double *pix_offsets,
@@ -227,9 +261,13 @@ static int rg_emit(int64_t nside, int64_t pix_first, int64_t pix_last, const dou
     cudaStream_t s = (cudaStream_t)stream;
     rg_init_kernel<<<1, 1, 0, s>>>(win);
     BF_LAUNCH_OK();
+    double *theta_tab = rg_theta_tab(h, ws);
+    rg_theta_kernel<<<(unsigned)((4 * nside + 1 + 255) / 256), 256, 0, s>>>(h, theta_tab);
+    BF_LAUNCH_OK();
     if (e_last > e_first) {
         rg_emit_kernel<<<(unsigned)((e_last - e_first + 255) / 256), 256, 0, s>>>(h, pix_first, pix_last, e_first, e_last,
-                                                                                 orig_map, pix_offsets, key, val, win);
+                                                                                 orig_map, pix_offsets, key, val, win,
+                                                                                 theta_tab);
         BF_LAUNCH_OK();
     }
     rg_window w;

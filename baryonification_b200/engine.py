@@ -55,6 +55,7 @@ class ShellEngine:
         self.nh = int(np.asarray(scalars["a"]).size) if scalars is not None else 0  # (upload_device sets it)
         self.table = None
         self.ws = None
+        self.max_entries = 0  # size hint of the (cell, halo) key list: 0 = find out with a counting pass
         self.nentries = None
         self.npairs = None
 
@@ -104,8 +105,6 @@ class ShellEngine:
             return self
         # first call: a counting pass with a key-less workspace returns the exact number of (cell, halo) entries
         # (BF_E_WORKSPACE + *nentries_host), the second call is sized for it; later calls reuse the workspace
-        if self.ws is None:
-            self.max_entries = 0
         for _ in range(2):
             need = self.lib.bf_shell_bin_ws_bytes(self.nside, self.nh, self.max_entries)
             if self.ws is None or self.ws.numel() < need:

@@ -480,7 +480,10 @@ class ShardedShell:
             t = self.scalars_device(dev, (lo, hi))
             self.timings["host_setup"] = time.perf_counter() - t0
             eng = engine.ShellEngine(nside, mode, htab, None, dev, variant="gather", bands=(lo, hi))
+            eng.max_entries = getattr(self, "_bin_hint", 0)  # (a repeated call skips the counting pass of the binning)
             eng.upload_device(t).bin()
+            if eng.nentries is not None:
+                self._bin_hint = eng.nentries + eng.nentries // 16 + 1024
             acc = eng.accumulate()
             pairs = eng.cnt.clone()
             if self.world > 1:
@@ -672,6 +675,7 @@ class ShardedGrid:
             exchange_rows(off, rows, below, above, self.group)
             self._fetch_rows(st, ghost_rows(rows, self.rank, below, above, n))
             win = (C.c_int * 3)()
+            st["out"][a0:a1].zero_()  # (the gather adds into its destination rows)
             _lib.call("bf_grid_regrid_gather_rows", dim, n, dv.ptr(off), dv.ptr(st["orig"]), dv.ptr(st["out"]), lohi, a0, a1,
                       win, dv.stream_ptr())
             self.regrid_window = tuple(win)

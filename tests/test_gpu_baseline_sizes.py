@@ -214,7 +214,8 @@ def test_healpix_ang2vec_lonlat_kernel(gpu):
     lon, lat = rng.uniform(0, 360, n), np.degrees(np.arcsin(rng.uniform(-1, 1, n)))
     lon[:4], lat[:4] = [0.0, 360.0, 180.0, 90.0], [90.0, -90.0, 0.0, 0.0]
     out = dv.empty((n, 3))
-    _lib.call("bf_healpix_ang2vec_lonlat", n, dv.ptr(dv.to_dev(lon)), dv.ptr(dv.to_dev(lat)), dv.ptr(out), dv.stream_ptr())
+    lon_d, lat_d = dv.to_dev(lon), dv.to_dev(lat)
+    _lib.call("bf_healpix_ang2vec_lonlat", n, dv.ptr(lon_d), dv.ptr(lat_d), dv.ptr(out), dv.stream_ptr())
     got = out.cpu().numpy()
     assert np.max(np.abs(got - host.ang2vec_lonlat(lon, lat))) < 4e-16
     assert np.max(np.abs(got - np.asarray(ohp.ang2vec(lon, lat, lonlat=True)).reshape(n, 3))) < 4e-16
@@ -229,7 +230,7 @@ def test_snapshot_pair_list_128cubed(gpu):
     got_r = bf.BaryonifySnapshot(cfg["catalog"], cfg["field"], 5.0, cfg["model"], verbose=False)
     ref_r = orc.BaryonifySnapshot(cfg["catalog"], cfg["field"], 5.0, cfg["model"], nthreads=_threads())
     got_pairs, ref_pairs = got_r.pair_list(), ref_r.pair_list()
-    assert ref_pairs.size > 1_000_000
+    assert ref_pairs.size > 300_000
     assert np.array_equal(got_pairs, ref_pairs)  # (particle, halo) ids, bit-exact
     got, ref = got_r.process(), ref_r.process()
     assert got_r.npairs == ref_r.npairs == ref_pairs.size
