@@ -47,6 +47,8 @@ class DefaultRunner:
         if use_ellipticity:  # HealpixRunner.py:164-165
             raise NotImplementedError("You have set use_ellipticity = True, but this not yet implemented for HealpixRunner")
 
+    SETUP_RUNS, SETUP_RUNS_MIN_HALOS = 4, 200_000
+
     # -- helpers -----------------------------------------------------------------------------
     def _check_keys(self, baryonify=False):
         """HealpixRunner.py:282-287 / :407-412: models with property keys must be ParamTabulatedProfile tables."""
@@ -62,23 +64,39 @@ class DefaultRunner:
         baryonify = mode == engine.BARYONIFY
         self._check_keys(baryonify)
         t0 = time.perf_counter()
-        self._progress("host set-up of %d halos" % len(self.HaloLightConeCatalog.cat))
+        nh = len(self.HaloLightConeCatalog.cat)
+        self._progress("host set-up of %d halos" % nh)
         htab = displacement_host_table(self.model) if baryonify else profile_host_table(self.model, "2D")
-        s = host.shell_scalars(self.HaloLightConeCatalog, self.cosmo, self.mass_def, self.epsilon_max, self.model,
-                               baryonify)
+        key = (mode, bands, nh)
+        hint = getattr(self, "_bin_hint", {}).get(key, 0)
+        extras_needed = len(vars(self.model).get("p_keys", []) or []) > 0 if self.model is not None else False
+        eng = engine.ShellEngine(self.LightconeShell.NSIDE, mode, htab, None, dev, variant=self.variant, bands=bands)
+        eng.max_entries = hint  # a repeated process() sizes the key list from the previous call: no counting pass ...
+        if hint > 0 and self.variant == "gather" and nh >= self.SETUP_RUNS_MIN_HALOS and not extras_needed and not htab.extra:
+            # ... and the catalogue goes to the device in runs of consecutive halos: upload, (z, M) collapse and binning of
+            # a finished run overlap the host set-up of the next one
+            eng.begin_runs(nh)
+            s = host.shell_scalars(self.HaloLightConeCatalog, self.cosmo, self.mass_def, self.epsilon_max, self.model,
+                                   baryonify, runs=self.SETUP_RUNS, on_run=eng.add_run)
+            streamed = "_pinned" in s  # (small catalogues / no page-locked memory: nothing was sent yet)
+        else:
+            s = host.shell_scalars(self.HaloLightConeCatalog, self.cosmo, self.mass_def, self.epsilon_max, self.model,
+                                   baryonify)
+            streamed = False
         s["extras"] = host.property_columns(self.HaloLightConeCatalog.cat, self.model)
+        eng.s, eng.nh = s, nh
         self.timings["host_setup"] = time.perf_counter() - t0
-        self._progress("upload, (z, M) table collapse, halo binning into sky cells")
         after = getattr(self, "_after_host", None)
         if after is not None:  # e.g. start the map upload now: the host cores are free while the GPU works
             after()
         t0 = time.perf_counter()
-        eng = engine.ShellEngine(self.LightconeShell.NSIDE, mode, htab, s, dev, variant=self.variant, bands=bands)
-        # a repeated process() sizes the key list from the previous call and skips the counting pass of the binning
-        eng.max_entries = getattr(self, "_bin_hint", {}).get((mode, bands, len(self.HaloLightConeCatalog.cat)), 0)
-        eng.upload().bin()
+        self._progress("upload, (z, M) table collapse, halo binning into sky cells")
+        if streamed:
+            eng.end_runs()
+        else:
+            eng.upload().bin()
         if eng.nentries is not None:
-            self._bin_hint = {(mode, bands, len(self.HaloLightConeCatalog.cat)): eng.nentries + eng.nentries // 16 + 1024}
+            self._bin_hint = {key: eng.nentries + eng.nentries // 16 + 1024}
         self._tick("upload_bin", t0, dev)
         return eng
 

@@ -75,6 +75,11 @@ _SIGS = {
     "bf_shell_bin_ws_bytes": (C.c_size_t, [_i64, _i64, _i64]),
     "bf_shell_bin_halos": (C.c_int, [_i64, C.c_int, _P(ShellHalos), _i64, _i64, _i64, C.c_void_p, C.c_size_t,
                                      _P(_i64), C.c_void_p]),
+    "bf_shell_bin_begin": (C.c_int, [_i64, C.c_int, _P(ShellHalos), _i64, _i64, _i64, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "bf_shell_bin_add": (C.c_int, [_i64, C.c_int, _P(ShellHalos), _i64, _i64, _i64, _i64, _i64, C.c_void_p, C.c_size_t,
+                                   C.c_void_p]),
+    "bf_shell_bin_end": (C.c_int, [_i64, C.c_int, _P(ShellHalos), _i64, _i64, _i64, C.c_void_p, C.c_size_t, _P(_i64),
+                                   C.c_void_p]),
     "bf_shell_gather": (C.c_int, [_i64, C.c_int, _P(ShellHalos), _P(Table), _i64, _i64, C.c_void_p, _dbl_p, _i64,
                                   C.c_int, _dbl_p, C.c_void_p]),
     "bf_shell_regrid": (C.c_int, [_i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p]),

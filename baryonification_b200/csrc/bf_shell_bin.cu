@@ -30,13 +30,13 @@ __device__ __forceinline__ u64 seg_mask(int s, int e, int wc) {  // columns touc
 // not.  Blocks that would pass `max_entries` are counted but not written: the caller learns the exact size from the
 // cursor and comes back with a larger workspace.  "Tiny" halos (baryonify mode, < 4 pixel centres in the disc,
 // HealpixRunner.py:309-310) emit no keys and are appended to tiny_list instead.
-__global__ void __launch_bounds__(128) bin_kernel(bf_hpx h, bf_cells cg, int mode, bf_shell_halos S, i64 band_lo,
-                                                  i64 band_hi, double resol, i64 max_entries,
+__global__ void __launch_bounds__(128) bin_kernel(bf_hpx h, bf_cells cg, int mode, bf_shell_halos S, i64 j_first,
+                                                  i64 j_last, i64 band_lo, i64 band_hi, double resol, i64 max_entries,
                                                   unsigned long long *__restrict__ cursor, u64 *__restrict__ keys,
                                                   int *__restrict__ tiny_list, int *__restrict__ tiny_count) {
-    i64 j = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    i64 j = j_first + (((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     int lane = threadIdx.x & 31;
-    if (j >= S.nh) return;
+    if (j >= j_last) return;
     double v[3] = {S.vec[3 * j], S.vec[3 * j + 1], S.vec[3 * j + 2]};
     double radius = S.radius[j];
     bf_disc d = bfh_disc_setup(h, v, radius);
@@ -126,41 +126,72 @@ extern "C" size_t bf_shell_bin_ws_bytes(int64_t nside, int64_t nh, int64_t max_e
     return bf_bin_ws_layout(nullptr, nside, nh, max_entries).total;
 }
 
-extern "C" int bf_shell_bin_halos(int64_t nside, int mode, const bf_shell_halos *S, int64_t band_lo, int64_t band_hi,
-                                  int64_t max_entries, void *ws, size_t ws_bytes, int64_t *nentries_host,
-                                  void *stream) {
+static int bin_check(int64_t nside, int mode, const bf_shell_halos *S, int64_t band_lo, int64_t band_hi,
+                     int64_t max_entries, void *ws, size_t ws_bytes, bf_bin_ws &w) {
     BF_REQUIRE(nside > 0 && (mode == 0 || mode == 1), "nside / mode");
     BF_REQUIRE(S && S->nh >= 0 && S->nh < (1ll << 31), "halo record");
     BF_REQUIRE(S->nh == 0 || (S->vec && S->radius), "null per-halo array");
-    BF_REQUIRE(nentries_host && ws, "null outputs");
+    BF_REQUIRE(ws, "null workspace");
     bf_cells cg = bf_cells_make(nside);
     BF_REQUIRE(band_lo >= 0 && band_lo <= band_hi && band_hi <= cg.nbands, "band range");
     BF_REQUIRE(max_entries >= 0 && max_entries < (1ll << 31), "max_entries must fit int32");
-    bf_bin_ws w = bf_bin_ws_layout(ws, nside, S->nh, max_entries);
+    w = bf_bin_ws_layout(ws, nside, S->nh, max_entries);
     if (ws_bytes < w.total) {
-        bf_set_error("bf_shell_bin_halos: workspace %zu < %zu bytes", ws_bytes, w.total);
+        bf_set_error("bf_shell_bin: workspace %zu < %zu bytes", ws_bytes, w.total);
         return BF_E_WORKSPACE;
     }
+    return BF_OK;
+}
+
+// The binning in three steps, so that a caller whose per-halo arrays arrive piece by piece (the host prepares the
+// catalogue in runs of consecutive halos) can bin every run as soon as it is on the device: _begin resets the key
+// cursor, _add emits the keys of halos j_first <= j < j_last (the arrays of `S` are the whole catalogue's; entries beyond
+// j_last need not be valid yet), _end sorts and marks the cell boundaries.  bf_shell_bin_halos = begin, add(0, nh), end.
+extern "C" int bf_shell_bin_begin(int64_t nside, int mode, const bf_shell_halos *S, int64_t band_lo, int64_t band_hi,
+                                  int64_t max_entries, void *ws, size_t ws_bytes, void *stream) {
+    bf_bin_ws w;
+    int rc = bin_check(nside, mode, S, band_lo, band_hi, max_entries, ws, ws_bytes, w);
+    if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
-    bf_hpx h = bf_hpx_make(nside);
-    double resol = sqrt(4.0 * BFH_PI / (double)h.npix);
     BF_CUDA_OK(cudaMemsetAsync(w.cell_begin, 0, sizeof(int) * (size_t)w.ncells, s));
     BF_CUDA_OK(cudaMemsetAsync(w.cell_end, 0, sizeof(int) * (size_t)w.ncells, s));
     BF_CUDA_OK(cudaMemsetAsync(w.tiny_count, 0, sizeof(int), s));
-    unsigned long long *cursor = (unsigned long long *)w.counts;  // counts[0] holds the key cursor
-    BF_CUDA_OK(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), s));
-    *nentries_host = 0;
-    if (S->nh == 0) return BF_OK;
-    unsigned blocks = (unsigned)((S->nh * 32 + 127) / 128);
-    bin_kernel<<<blocks, 128, 0, s>>>(h, cg, mode, *S, band_lo, band_hi, resol, max_entries, cursor, w.keys, w.tiny_list,
-                                      w.tiny_count);
+    BF_CUDA_OK(cudaMemsetAsync(w.counts, 0, sizeof(unsigned long long), s));  // counts[0] holds the key cursor
+    return BF_OK;
+}
+
+extern "C" int bf_shell_bin_add(int64_t nside, int mode, const bf_shell_halos *S, int64_t j_first, int64_t j_last,
+                                int64_t band_lo, int64_t band_hi, int64_t max_entries, void *ws, size_t ws_bytes,
+                                void *stream) {
+    bf_bin_ws w;
+    int rc = bin_check(nside, mode, S, band_lo, band_hi, max_entries, ws, ws_bytes, w);
+    if (rc) return rc;
+    BF_REQUIRE(j_first >= 0 && j_first <= j_last && j_last <= S->nh, "halo range");
+    if (j_last == j_first) return BF_OK;
+    bf_hpx h = bf_hpx_make(nside);
+    const double resol = sqrt(4.0 * BFH_PI / (double)h.npix);
+    const unsigned blocks = (unsigned)(((j_last - j_first) * 32 + 127) / 128);
+    bin_kernel<<<blocks, 128, 0, (cudaStream_t)stream>>>(h, bf_cells_make(nside), mode, *S, j_first, j_last, band_lo,
+                                                        band_hi, resol, max_entries, (unsigned long long *)w.counts,
+                                                        w.keys, w.tiny_list, w.tiny_count);
     BF_LAUNCH_OK();
+    return BF_OK;
+}
+
+extern "C" int bf_shell_bin_end(int64_t nside, int mode, const bf_shell_halos *S, int64_t band_lo, int64_t band_hi,
+                                int64_t max_entries, void *ws, size_t ws_bytes, int64_t *nentries_host, void *stream) {
+    BF_REQUIRE(nentries_host, "null outputs");
+    bf_bin_ws w;
+    int rc = bin_check(nside, mode, S, band_lo, band_hi, max_entries, ws, ws_bytes, w);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    *nentries_host = 0;
     i64 total = 0;
-    BF_CUDA_OK(cudaMemcpyAsync(&total, cursor, sizeof(i64), cudaMemcpyDeviceToHost, s));
+    BF_CUDA_OK(cudaMemcpyAsync(&total, w.counts, sizeof(i64), cudaMemcpyDeviceToHost, s));
     BF_CUDA_OK(cudaStreamSynchronize(s));
     *nentries_host = total;
     if (total > max_entries) {
-        bf_set_error("bf_shell_bin_halos: %lld entries exceed max_entries %lld", (long long)total, (long long)max_entries);
+        bf_set_error("bf_shell_bin: %lld entries exceed max_entries %lld", (long long)total, (long long)max_entries);
         return BF_E_WORKSPACE;
     }
     if (total == 0) return BF_OK;
@@ -174,4 +205,15 @@ extern "C" int bf_shell_bin_halos(int64_t nside, int mode, const bf_shell_halos 
     cell_bounds_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(total, w.keys, w.cell_begin, w.cell_end);
     BF_LAUNCH_OK();
     return BF_OK;
+}
+
+extern "C" int bf_shell_bin_halos(int64_t nside, int mode, const bf_shell_halos *S, int64_t band_lo, int64_t band_hi,
+                                  int64_t max_entries, void *ws, size_t ws_bytes, int64_t *nentries_host,
+                                  void *stream) {
+    BF_REQUIRE(nentries_host && ws, "null outputs");
+    int rc = bf_shell_bin_begin(nside, mode, S, band_lo, band_hi, max_entries, ws, ws_bytes, stream);
+    if (rc) return rc;
+    rc = bf_shell_bin_add(nside, mode, S, 0, S->nh, band_lo, band_hi, max_entries, ws, ws_bytes, stream);
+    if (rc) return rc;
+    return bf_shell_bin_end(nside, mode, S, band_lo, band_hi, max_entries, ws, ws_bytes, nentries_host, stream);
 }

@@ -31,6 +31,9 @@
 #ifndef GT_MINBLOCKS
 #define GT_MINBLOCKS 4
 #endif
+#ifndef GT_FAST_NP
+#define GT_FAST_NP 1  // pairs evaluated side by side in the whole-strip loop (2: more registers)
+#endif
 
 struct gather_args {
     const void *aux;     // [ln table | (g, 1/dg) pairs | g] prepared once per call (gather_aux_kernel)
@@ -111,58 +114,103 @@ __device__ __forceinline__ double gather_log(const double2 *__restrict__ tab, do
 // sum e (1 + g) delta (one FMA per component) -- the pixel's shift is acc[0..2] + v acc[3], formed once at the end.
 // fp64 instructions are what bounds this kernel, so tests that do not need fp64 arithmetic (finite?, |q| > 1e-3,
 // 0 <= t < 1 - 2^-50) look at the bit patterns with integer instructions instead.
+// NP pairs of the same pixel at once (NP = 2 in the whole-strip loop): the pairs' dependent fp64 chains (ln series,
+// reciprocal square root, (1+q)^-1/2 series) are independent of each other, so writing them side by side lets the
+// scheduler fill one chain's latency with the other's instructions; the rare exact-search and |q| > 1e-3 routes are
+// taken once for the group.
+template <int MODE, int NP>
+__device__ __forceinline__ void gather_pairs(const gather_smem &sm, const int c[NP], const double v[3], const bf_raxis &ax,
+                                             const double2 *__restrict__ gi_s, const double2 *__restrict__ logtab,
+                                             double acc[4]) {
+    const double2 *__restrict__ cq[NP];
+    double dx[NP], dy[NP], dz[NP], d2[NP], x[NP], tt[NP];
+    int k[NP];
+    bool inr[NP];
+    bool fast = true;
+#pragma unroll
+    for (int u = 0; u < NP; ++u) {
+        cq[u] = reinterpret_cast<const double2 *>(sm.cand[c[u]]);
+        const double2 q0 = cq[u][0], q1 = cq[u][1];  // (c0, c1), (c2, ln(D/a))
+        dx[u] = v[0] - q0.x; dy[u] = v[1] - q0.y; dz[u] = v[2] - q1.x;
+        d2[u] = fma(dz[u], dz[u], fma(dy[u], dy[u], dx[u] * dx[u]));
+        x[u] = fma(0.5, gather_log(logtab, d2[u]), q1.y);
+        // Table cell: uniform-grid guess, accepted when 0 <= tt < 1 - 2^-50, which PROVES g[k] <= x < g[k+1] (tt >= 0 iff
+        // x >= g[k]; x >= g[k+1] would give tt >= 1 - 4 ulp) and with it that x lies inside the table.  For tt >= 0 the
+        // order of doubles is the order of their bit patterns; negative tt and NaN have larger patterns, so one
+        // unsigned compare decides.  Everything else -- rounding at a node, a non-uniform axis, x == glast, x outside
+        // the table (fill_value NaN) -- takes the exact route.
+        k[u] = (int)((x[u] - ax.g0) * ax.inv_dx);
+        k[u] = max(0, min(k[u], ax.nr - 2));
+        const double2 gi = gi_s[k[u]];
+        tt[u] = (x[u] - gi.x) * gi.y;
+        inr[u] = true;
+        fast = fast && (u64)__double_as_longlong(tt[u]) < 0x3feffffffffffff8ull;  // (bits of 1 - 2^-50)
+    }
+    if (!fast) {
+#pragma unroll
+        for (int u = 0; u < NP; ++u)
+            if ((u64)__double_as_longlong(tt[u]) >= 0x3feffffffffffff8ull) {
+                inr[u] = x[u] >= ax.g0 && x[u] <= ax.glast;
+                if (inr[u]) {
+                    k[u] = bf_find_cell(ax, x[u]);
+                    const double2 gi = gi_s[k[u]];
+                    tt[u] = (x[u] - gi.x) * gi.y;
+                }
+            }
+    }
+    double r0[NP], r1[NP];
+#pragma unroll
+    for (int u = 0; u < NP; ++u) {
+        const double *row = reinterpret_cast<const double *>(__double_as_longlong(cq[u][3].x)) + k[u];
+        r0[u] = __ldg(row);
+        r1[u] = __ldg(row + 1);
+    }
+    if (MODE == 0) {
+#pragma unroll
+        for (int u = 0; u < NP; ++u) {
+            // the two-product form keeps scipy's propagation through zero weights (0 * -inf = NaN -> 0, Tabulate.py:237)
+            const double val = fma(r1[u], tt[u], r0[u] * (1.0 - tt[u]));
+            const double P = exp(inr[u] ? val : nan(""));
+            if ((__double2hiint(P) & 0x7ff00000) != 0x7ff00000) acc[0] += P;  // finite (HealpixRunner.py:442)
+        }
+    } else {
+        double e[NP], q[NP], gg[NP];
+        bool big = false;
+#pragma unroll
+        for (int u = 0; u < NP; ++u) {
+            const double2 q2 = cq[u][2];  // (cut^2, a/D)
+            const double sc = q2.y * bf_rsqrt(d2[u]);
+            const bool use = inr[u] && d2[u] < q2.x;  // NaN fill / BaryonCorrection.py:381-382: both end as 0
+            // (an inf or NaN anywhere in the cell gives a non-finite e in either form of the lerp, which ends as 0 below)
+            e[u] = fma(tt[u], r1[u] - r0[u], r0[u]) * sc;
+            if (!use || (__double2hiint(e[u]) & 0x7ff00000) == 0x7ff00000) e[u] = 0.0;  // HealpixRunner.py:323
+            const double ed = e[u] * d2[u];
+            q[u] = fma(e[u], ed, ed);  // e d2 (1 + e)
+            gg[u] = q[u] * fma(q[u], fma(q[u], fma(q[u], bf_kc[5], bf_kc[6]), bf_kc[4]), -0.5);  // (1+q)^-1/2 - 1
+            big = big || (__double2hiint(q[u]) & 0x7fffffff) > 0x3f50624d;
+        }
+        if (big) {  // |q| > 1e-3: pixel (almost) on a halo centre
+#pragma unroll
+            for (int u = 0; u < NP; ++u)
+                if ((__double2hiint(q[u]) & 0x7fffffff) > 0x3f50624d) gg[u] = rsqrt(1.0 + q[u]) - 1.0;
+        }
+#pragma unroll
+        for (int u = 0; u < NP; ++u) {  // (pair u before pair u + 1: the candidates' order)
+            const double ef = fma(e[u], gg[u], e[u]);
+            acc[3] += gg[u];
+            acc[0] = fma(ef, dx[u], acc[0]);
+            acc[1] = fma(ef, dy[u], acc[1]);
+            acc[2] = fma(ef, dz[u], acc[2]);
+        }
+    }
+}
+
 template <int MODE>
 __device__ __forceinline__ void gather_pair(const gather_smem &sm, int c, const double v[3], const bf_raxis &ax,
                                             const double2 *__restrict__ gi_s, const double2 *__restrict__ logtab,
                                             double acc[4]) {
-    const double2 *__restrict__ cq = reinterpret_cast<const double2 *>(sm.cand[c]);
-    const double2 q0 = cq[0], q1 = cq[1];  // (c0, c1), (c2, ln(D/a))
-    const double dx = v[0] - q0.x, dy = v[1] - q0.y, dz = v[2] - q1.x;
-    const double d2 = fma(dz, dz, fma(dy, dy, dx * dx));
-    const double x = fma(0.5, gather_log(logtab, d2), q1.y);
-    // Table cell: uniform-grid guess, accepted when 0 <= tt < 1 - 2^-50, which PROVES g[k] <= x < g[k+1] (tt >= 0 iff
-    // x >= g[k]; x >= g[k+1] would give tt >= 1 - 4 ulp) and with it that x lies inside the table.  For tt >= 0 the
-    // order of doubles is the order of their bit patterns; negative tt and NaN have larger patterns, so one unsigned
-    // compare decides.  Everything else -- rounding at a node, a non-uniform axis, x == glast, x outside the table
-    // (fill_value NaN) -- takes the exact route.
-    int k = (int)((x - ax.g0) * ax.inv_dx);
-    k = max(0, min(k, ax.nr - 2));
-    double2 gi = gi_s[k];
-    double tt = (x - gi.x) * gi.y;
-    bool inr = true;
-    if ((u64)__double_as_longlong(tt) >= 0x3feffffffffffff8ull) {  // (bits of 1 - 2^-50)
-        inr = x >= ax.g0 && x <= ax.glast;
-        if (inr) {
-            k = bf_find_cell(ax, x);
-            gi = gi_s[k];
-            tt = (x - gi.x) * gi.y;
-        }
-    }
-    const double2 q3 = cq[3];
-    const double *row = reinterpret_cast<const double *>(__double_as_longlong(q3.x)) + k;
-    const double r0 = __ldg(row), r1 = __ldg(row + 1);
-    if (MODE == 0) {
-        // the two-product form keeps scipy's propagation through zero weights (0 * -inf = NaN -> 0, Tabulate.py:237)
-        const double val = fma(r1, tt, r0 * (1.0 - tt));
-        const double P = exp(inr ? val : nan(""));
-        if ((__double2hiint(P) & 0x7ff00000) != 0x7ff00000) acc[0] += P;  // finite (HealpixRunner.py:442)
-    } else {
-        const double2 q2 = cq[2];  // (cut^2, a/D)
-        const double sc = q2.y * bf_rsqrt(d2);
-        const bool use = inr && d2 < q2.x;  // NaN fill / BaryonCorrection.py:381-382: both end as 0
-        // (an inf or NaN anywhere in the cell gives a non-finite e in either form of the lerp, which ends as 0 below)
-        double e = fma(tt, r1 - r0, r0) * sc;
-        if (!use || (__double2hiint(e) & 0x7ff00000) == 0x7ff00000) e = 0.0;  // HealpixRunner.py:323
-        const double ed = e * d2;
-        const double q = fma(e, ed, ed);  // e d2 (1 + e)
-        double gg = q * fma(q, fma(q, fma(q, bf_kc[5], bf_kc[6]), bf_kc[4]), -0.5);  // (1+q)^-1/2 - 1
-        if ((__double2hiint(q) & 0x7fffffff) > 0x3f50624d) gg = rsqrt(1.0 + q) - 1.0;  // |q| > 1e-3: pixel (almost) on the centre
-        const double ef = fma(e, gg, e);
-        acc[3] += gg;
-        acc[0] = fma(ef, dx, acc[0]);
-        acc[1] = fma(ef, dy, acc[1]);
-        acc[2] = fma(ef, dz, acc[2]);
-    }
+    const int cc[1] = {c};
+    gather_pairs<MODE, 1>(sm, cc, v, ax, gi_s, logtab, acc);
 }
 
 template <int MODE>
@@ -282,6 +330,16 @@ __global__ void __launch_bounds__(GT_THREADS, GT_MINBLOCKS) gather_kernel(gather
                 for (int kw = 0; kw < nw; ++kw) {
                     unsigned fm = sm.full[w][kw];
                     my_pairs32 += __popc(fm);
+#if GT_FAST_NP == 2
+                    while (fm & (fm - 1u)) {  // two or more left: a group of two
+                        int cc[2];
+                        cc[0] = kw * 32 + __ffs((int)fm) - 1;
+                        fm &= fm - 1u;
+                        cc[1] = kw * 32 + __ffs((int)fm) - 1;
+                        fm &= fm - 1u;
+                        gather_pairs<MODE, 2>(sm, cc, v, ax, gi_s, logtab, acc);
+                    }
+#endif
                     while (fm) {
                         const int c = kw * 32 + __ffs((int)fm) - 1;
                         fm &= fm - 1u;

@@ -78,6 +78,58 @@ class ShellEngine:
         self.cnt = dv.pair_counter(dev)
         return self
 
+    # ---- stage 0 + 1 for a catalogue that arrives in runs of consecutive halos (host.chunked, runs > 1) -----------------
+    RUN_KEYS = ("vec", "lon", "lat", "radius", "D", "a", "cut", "lnr_shift", "z_in", "M_in")
+
+    def begin_runs(self, nh):
+        """Device arrays for ``nh`` halos, table, binning workspace for ``self.max_entries`` keys (a size hint from an
+        earlier call: without one the key list cannot be sized before the halos are known, use upload() + bin())."""
+        assert self.variant == "gather" and self.max_entries > 0
+        dev = self.dev
+        self.nh = int(nh)
+        self.table = dv.DeviceTable(self.host_table, dev=dev)
+        self.t = {k: dv.empty((self.nh, 3) if k == "vec" else (self.nh,), dev=dev) for k in self.RUN_KEYS}
+        self.t["extras"] = None
+        self.rows = dv.empty((self.nh, self.table.nr), dev=dev)
+        self.order = None
+        t = self.t
+        self.desc = _lib.ShellHalos(t["vec"].data_ptr(), t["lon"].data_ptr(), t["lat"].data_ptr(),
+                                    t["radius"].data_ptr(), t["D"].data_ptr(), t["a"].data_ptr(),
+                                    t["cut"].data_ptr(), t["lnr_shift"].data_ptr(), self.rows.data_ptr(), None, self.nh)
+        self.cnt = dv.pair_counter(dev)
+        need = self.lib.bf_shell_bin_ws_bytes(self.nside, self.nh, self.max_entries)
+        if self.ws is None or self.ws.numel() < need:
+            self.ws = None
+            self.ws = torch.empty(need, dtype=torch.uint8, device=dev)
+        _lib.call("bf_shell_bin_begin", self.nside, self.mode, C.byref(self.desc), self.bands[0], self.bands[1],
+                  self.max_entries, dv.ptr(self.ws), self.ws.numel(), dv.stream_ptr())
+        return self
+
+    def add_run(self, j0, j1, pins):
+        """Halos j0 <= j < j1 are ready in the page-locked tensors ``pins``: upload them, collapse their table rows, emit
+        their (cell, halo) keys -- all asynchronous, the host goes on with the next run."""
+        if j1 <= j0:
+            return
+        with torch.cuda.device(self.dev):
+            for k in self.RUN_KEYS:
+                self.t[k][j0:j1].copy_(pins[k][j0:j1], non_blocking=True)
+            _lib.call("bf_table_collapse_zM", C.byref(self.table.desc), j1 - j0, dv.ptr(self.t["z_in"][j0:j1]),
+                      dv.ptr(self.t["M_in"][j0:j1]), dv.ptr(self.rows[j0:j1]), dv.stream_ptr())
+            _lib.call("bf_shell_bin_add", self.nside, self.mode, C.byref(self.desc), j0, j1, self.bands[0], self.bands[1],
+                      self.max_entries, dv.ptr(self.ws), self.ws.numel(), dv.stream_ptr())
+
+    def end_runs(self):
+        """Sort the keys and mark the cell boundaries; a key list that outgrew the hint is redone with the exact size."""
+        n = C.c_int64()
+        rc = self.lib.bf_shell_bin_end(self.nside, self.mode, C.byref(self.desc), self.bands[0], self.bands[1],
+                                       self.max_entries, dv.ptr(self.ws), self.ws.numel(), C.byref(n), dv.stream_ptr())
+        if rc == -2 and n.value > self.max_entries:
+            self.max_entries = n.value
+            return self.bin()
+        _lib.check(rc, "bf_shell_bin_end")
+        self.nentries = n.value
+        return self
+
     def upload_device(self, t, order=None):
         """``upload()`` for per-halo arrays that are already on the device (``sharding.ShardedShell``: prepared 1/N per
         rank, all-gathered over NVLink).  ``t``: dict of float64 tensors with the keys of ``upload()`` (+ "extras")."""

@@ -23,15 +23,25 @@ _PAR_MIN = 100_000
 _pool = None
 
 
-def _threads():
-    env = os.environ.get("BF_HOST_THREADS")
-    if env:
-        return max(1, int(env))
+def host_cores():
+    """Host cores this process may use: its affinity mask, shared evenly with the other ranks of a one-box job
+    (LOCAL_WORLD_SIZE, set by torchrun)."""
     try:
         n = len(os.sched_getaffinity(0))
     except AttributeError:
         n = os.cpu_count() or 1
-    return max(1, min(16, n))
+    try:
+        n //= max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
+    except ValueError:
+        pass
+    return max(1, n)
+
+
+def _threads():
+    env = os.environ.get("BF_HOST_THREADS")
+    if env:
+        return max(1, int(env))
+    return max(1, min(16, host_cores()))
 
 
 def spline_eval(cs, x):
@@ -60,22 +70,25 @@ def _pinned_outputs(schema, n):
     return pins
 
 
-def chunked(fn, n, schema=None):
+def chunked(fn, n, schema=None, runs=1, on_run=None):
     """Evaluate ``fn(slice) -> dict of arrays`` over [0, n) in parallel chunks and join them along axis 0.
 
     With ``schema`` = {key: trailing shape} (all float64) every chunk writes its slice straight into page-locked
     output arrays -- no serial concatenate, and the upload that follows is one asynchronous copy per array at PCIe
-    speed instead of a pageable one.  The backing tensors travel under the key ``"_pinned"``."""
+    speed instead of a pageable one.  The backing tensors travel under the key ``"_pinned"``.
+    ``runs`` > 1 with ``on_run``: the catalogue is worked through in that many runs of consecutive halos (each run
+    spread over all threads) and ``on_run(j0, j1, pinned tensors)`` is called after each, so that the caller can send a
+    finished run to the device (upload, table collapse, binning) while the host prepares the next one."""
     global _pool
     nt = _threads()
     if n < _PAR_MIN or nt == 1:
         return fn(slice(0, n))
     if _pool is None:
         _pool = ThreadPoolExecutor(max_workers=nt, thread_name_prefix="bf-host")
-    edges = np.linspace(0, n, nt + 1).astype(np.int64)
-    slices = [slice(int(edges[i]), int(edges[i + 1])) for i in range(nt)]
     pins = _pinned_outputs(schema, n) if schema else None
     if pins is None:
+        edges = np.linspace(0, n, nt + 1).astype(np.int64)
+        slices = [slice(int(edges[i]), int(edges[i + 1])) for i in range(nt)]
         parts = list(_pool.map(fn, slices))
         return {k: np.concatenate([p[k] for p in parts], axis=0) for k in parts[0]}
     out = {k: t.numpy() for k, t in pins.items()}
@@ -85,7 +98,13 @@ def chunked(fn, n, schema=None):
         for k in out:
             out[k][sl] = r[k]
 
-    list(_pool.map(run, slices))
+    nruns = max(1, int(runs)) if on_run is not None else 1
+    bounds = np.linspace(0, n, nruns + 1).astype(np.int64)
+    for r0, r1 in zip(bounds[:-1], bounds[1:]):
+        edges = np.linspace(int(r0), int(r1), nt + 1).astype(np.int64)
+        list(_pool.map(run, [slice(int(edges[i]), int(edges[i + 1])) for i in range(nt) if edges[i + 1] > edges[i]]))
+        if on_run is not None:
+            on_run(int(r0), int(r1), pins)
     out["_pinned"] = pins
     return out
 
@@ -152,7 +171,8 @@ def ang2vec_lonlat(lon, lat):
     return np.ascontiguousarray(np.stack([st * np.cos(phi), st * np.sin(phi), np.cos(theta)], axis=1))
 
 
-def shell_scalars(catalog, cosmo_dict, mass_def, epsilon_max, model, baryonify: bool):
+def shell_scalars(catalog, cosmo_dict, mass_def, epsilon_max, model, baryonify: bool, runs=1, on_run=None):
+    """Per-halo inputs of the shell kernels.  ``runs`` / ``on_run``: see :func:`chunked` (large catalogues only)."""
     ccl = get_ccl()
     cosmo = runner_cosmology(cosmo_dict, with_w0=True)
     z_t = np.linspace(0, 30, 1000)  # HealpixRunner.py:279-280
@@ -177,7 +197,7 @@ def shell_scalars(catalog, cosmo_dict, mass_def, epsilon_max, model, baryonify: 
 
     schema = {k: () for k in ("a", "D", "radius", "z_in", "M_in", "lon", "lat", "cut", "lnr_shift")}
     schema["vec"] = (3,)
-    return chunked(part, len(cat), schema)
+    return chunked(part, len(cat), schema, runs, on_run)
 
 
 def _native(a):

@@ -373,6 +373,17 @@ class SharedHostArena:
             pass
 
 
+def claim_host_threads():
+    """torchrun starts every rank with OMP_NUM_THREADS=1, which makes torch's pageable -> page-locked staging copies (the
+    map slice, the particle records: GBs per call) single-threaded.  The sharded runners give torch this rank's share of
+    the host cores instead (never fewer threads than it already has)."""
+    from .host import host_cores
+    n = host_cores()
+    if torch.get_num_threads() < n:
+        torch.set_num_threads(n)
+    return n
+
+
 _SHELL_KEYS = ("a", "D", "radius", "z_in", "M_in", "lon", "lat", "cut", "lnr_shift")
 
 
@@ -402,6 +413,7 @@ class ShardedShell:
         self.npairs = None
         self.timings = {}
         self._arenas, self._turn = [None, None], 0
+        claim_host_threads()
 
     def plan(self):
         nside = self.runner.LightconeShell.NSIDE
@@ -478,19 +490,22 @@ class ShardedShell:
                 orig = np.ascontiguousarray(r.LightconeShell.map, dtype=np.float64).reshape(-1)
                 up = dv.AsyncUpload(orig[first:last], dev)
             t = self.scalars_device(dev, (lo, hi))
-            self.timings["host_setup"] = time.perf_counter() - t0
+            t0 = self._tick("host_setup_allgather", t0, dev)
             eng = engine.ShellEngine(nside, mode, htab, None, dev, variant="gather", bands=(lo, hi))
             eng.max_entries = getattr(self, "_bin_hint", 0)  # (a repeated call skips the counting pass of the binning)
             eng.upload_device(t).bin()
             if eng.nentries is not None:
                 self._bin_hint = eng.nentries + eng.nentries // 16 + 1024
+            t0 = self._tick("collapse_bin", t0, dev)
             acc = eng.accumulate()
             pairs = eng.cnt.clone()
             if self.world > 1:
                 dist.all_reduce(pairs, group=self.group)
             if not self.baryonify:
                 self.npairs = int(pairs.item())
+                self._tick("pairs", t0, dev)
                 return (gather_slices(acc, ranges, self.group) if gather else acc), None, ranges
+            t0 = self._tick("pairs", t0, dev)
             orig_d = up.result()
             F = margin_pixels(nside)
             if fixed_margins_ok(ranges, F):
@@ -505,9 +520,16 @@ class ShardedShell:
                 dist.all_reduce(sums, group=self.group)  # the reference's mass check, HealpixRunner.py:344-346
             self.npairs = int(pairs.item())
             sums = sums.tolist()
+            self._tick("regrid_exchange", t0, dev)
             if sums[2] != 0:
                 raise _lib.BFError("ShardedShell: displaced mass landed more than %d rings outside a shard" % MARGIN_RINGS)
             return (gather_slices(own, ranges, self.group) if gather else own), (sums[0], sums[1]), ranges
+
+    def _tick(self, name, t0, dev):
+        import time
+        torch.cuda.synchronize(dev)
+        self.timings[name] = time.perf_counter() - t0
+        return time.perf_counter()
 
     def _arena(self, n):
         self._turn ^= 1
@@ -517,7 +539,9 @@ class ShardedShell:
         return ar
 
     def process(self):
+        import time
         out, sums, ranges = self.process_device(gather=False)
+        t0 = time.perf_counter()
         if sums is not None:
             assert np.isclose(sums[0], sums[1]), \
                 "ERROR in pixel regridding, sum(new_map) [%0.14e] != sum(oldmap) [%0.14e]" % sums
@@ -528,6 +552,7 @@ class ShardedShell:
             torch.cuda.current_stream(out.device).synchronize()
         if self.world > 1:
             dist.barrier(group=self.group)
+        self.timings["d2h_barrier"] = time.perf_counter() - t0
         return arena.array
 
 
@@ -539,6 +564,7 @@ class ShardedSnapshot:
         self.runner, self.group, self.device = runner, group, device
         self.rank, self.world = _world(group)
         self.npairs = None
+        claim_host_threads()
 
     def process(self, gather=True):
         import copy
@@ -579,6 +605,7 @@ class ShardedGrid:
         self.baryonify = isinstance(runner, _grid.BaryonifyGrid)
         self.rank, self.world = _world(group)
         self.npairs = None
+        claim_host_threads()
 
     def _local_runner(self, a0, a1):
         import copy

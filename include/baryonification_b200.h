@@ -129,6 +129,17 @@ size_t bf_shell_bin_ws_bytes(int64_t nside, int64_t nh, int64_t max_entries);
  * (call again with a workspace sized for *nentries_host).  Synchronises `stream` once. */
 int bf_shell_bin_halos(int64_t nside, int mode, const bf_shell_halos *h_host, int64_t band_lo, int64_t band_hi,
                        int64_t max_entries, void *ws, size_t ws_bytes, int64_t *nentries_host, void *stream);
+/* The same in three steps, for per-halo arrays that arrive on the device piece by piece (the host prepares the catalogue
+ * in runs of consecutive halos): _begin resets the key cursor, _add emits the keys of halos j_first <= j < j_last (the
+ * arrays of `h_host` are the whole catalogue's; entries at and beyond j_last need not be valid yet), _end reads the count
+ * back (synchronises `stream`), sorts and marks the cell boundaries.  bf_shell_bin_halos = begin, add(0, nh), end; the
+ * same workspace and max_entries in all three calls. */
+int bf_shell_bin_begin(int64_t nside, int mode, const bf_shell_halos *h_host, int64_t band_lo, int64_t band_hi,
+                       int64_t max_entries, void *ws, size_t ws_bytes, void *stream);
+int bf_shell_bin_add(int64_t nside, int mode, const bf_shell_halos *h_host, int64_t j_first, int64_t j_last,
+                     int64_t band_lo, int64_t band_hi, int64_t max_entries, void *ws, size_t ws_bytes, void *stream);
+int bf_shell_bin_end(int64_t nside, int mode, const bf_shell_halos *h_host, int64_t band_lo, int64_t band_hi,
+                     int64_t max_entries, void *ws, size_t ws_bytes, int64_t *nentries_host, void *stream);
 /* out: paint -> map[npix]; baryonify -> pix_offsets[npix][3]; both indexed by GLOBAL pixel number minus
  * `pix_base` (the first pixel of band_lo when sharded, else 0).  Pixels of the evaluated bands are
  * OVERWRITTEN (+= when accumulate != 0). */

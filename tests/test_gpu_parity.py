@@ -882,3 +882,30 @@ def test_paint_split_join_sum_equals_one_pass(gpu):
     assert pairs == runner.npairs
     assert np.array_equal(got != 0, want != 0)
     assert relmax(got, want) < 1e-13
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cls", ["BaryonifyShell", "PaintProfilesShell"])
+def test_shell_setup_in_runs_equals_one_piece(gpu, cls, monkeypatch):
+    """A repeated process() knows the size of the (cell, halo) key list from the previous call: the catalogue is then
+    prepared on the host in runs of consecutive halos, and the upload, (z, M) collapse and binning of a finished run
+    overlap the set-up of the next (bf_shell_bin_begin / _add / _end).  Same keys after the sort, hence the same bits."""
+    import baryonification_b200 as bf
+    from baryonification_b200 import host, synthetic as syn
+    monkeypatch.setattr(host, "_PAR_MIN", 500)
+    monkeypatch.setenv("BF_HOST_THREADS", "3")
+    cfg = syn.config_shell(nside=128, nhalo=3001, zero_map=(cls == "PaintProfilesShell"))
+    model = cfg["paint_model"] if cls == "PaintProfilesShell" else cfg["model"]
+    r = getattr(bf, cls)(cfg["catalog"], cfg["field"], 20.0, model, verbose=False)
+    r.SETUP_RUNS_MIN_HALOS, r.SETUP_RUNS = 1000, 4
+    seen = []
+    from baryonification_b200 import engine
+    orig_add = engine.ShellEngine.add_run
+    monkeypatch.setattr(engine.ShellEngine, "add_run", lambda self, j0, j1, pins: (seen.append((j0, j1)), orig_add(self, j0, j1, pins))[1])
+    first = r.process()
+    assert seen == []  # no size hint yet: one piece, with the counting pass
+    second = r.process()
+    assert [b - a for a, b in seen] and seen[0][0] == 0 and seen[-1][1] == 3001 and len(seen) == 4
+    assert np.array_equal(first, second)
+    r._bin_hint = {k: 10 for k in r._bin_hint}  # a hint that is too small: the binning is redone with the exact size
+    assert np.array_equal(r.process(), first)
