@@ -133,6 +133,9 @@ _SIGS = {
     "bf_pk_bin_ws_bytes": (C.c_size_t, [_i64, _i64]),
     "bf_pk_bin": (C.c_int, [_i64, C.c_void_p, _P(_i64), C.c_double, C.c_double, C.c_double, _i64, _dbl_p, C.c_void_p,
                             C.c_size_t, C.c_void_p]),
+    "bf_pk_bin_static_max_bytes": (C.c_size_t, []),
+    "bf_pk_bin_static": (C.c_int, [_i64, C.c_void_p, _P(_i64), C.c_double, C.c_double, C.c_double, _i64, _dbl_p,
+                                   C.c_void_p]),
     "bf_pk_bin_part_ws_bytes": (C.c_size_t, [_P(_i64), _i64]),
     "bf_pk_bin_part": (C.c_int, [_i64, C.c_void_p, _P(_i64), _P(_i64), _P(_i64), C.c_double, C.c_double, C.c_double,
                                  _i64, _dbl_p, C.c_void_p, C.c_size_t, C.c_void_p]),

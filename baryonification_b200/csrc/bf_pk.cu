@@ -228,3 +228,48 @@ extern "C" int bf_pk_bin(int64_t ngrid, const void *spectrum, const int64_t *str
     const int64_t ext[3] = {ngrid, ngrid, ngrid / 2 + 1}, off[3] = {0, 0, 0};
     return bf_pk_bin_part(ngrid, spectrum, strides_host, ext, off, val, k0, dk, nk, out, ws, ws_bytes, stream);
 }
+
+// ---------------------------------------------------------------------------------------------------
+// bf_pk_bin without a caller workspace and without any allocation (no counterpart in the reference; added
+// for callers that cannot allocate: CUDA graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc).  The per-block partial sums [blocks][3][nk] that bf_pk_bin keeps in the caller's workspace live in a
+// file-scope device array of fixed size instead; every GPU that loads the library holds these 8 MiB until exit.
+// In HOST code the array's name is only a stand-in for the symbol, not a device address: the address is asked for once per
+// device, with that device current (cudaGetSymbolAddress), and that pointer is what the kernels get.
+// All calls on a device share the array: calls that overlap on the GPU (different streams) race.  Nothing in it has to
+// start at zero -- every block writes all of its 3 * nk partial sums before the finishing kernel reads them -- so a call
+// does not depend on what the previous one left behind.
+// ---------------------------------------------------------------------------------------------------
+#define PK_STATIC_DOUBLES (1 << 20)  // 8 MiB
+#define PK_STATIC_MAX_NK 256
+#define PK_STATIC_MAX_DEVICES 64
+static __device__ __align__(256) double pk_static_scratch[PK_STATIC_DOUBLES];
+static double *pk_static_ptr[PK_STATIC_MAX_DEVICES];  // device address of the array, per device (0 = not asked yet)
+
+extern "C" size_t bf_pk_bin_static_max_bytes(void) { return sizeof(double) * (size_t)PK_STATIC_DOUBLES; }
+
+extern "C" int bf_pk_bin_static(int64_t ngrid, const void *spectrum, const int64_t *strides_host, double val, double k0,
+                                double dk, int64_t nk, double *out /* [3][nk] */, void *stream) {
+    BF_REQUIRE(ngrid >= 2 && ngrid <= 4096 && spectrum && out, "ngrid / spectrum / out");
+    if (nk < 1 || nk > PK_STATIC_MAX_NK) {
+        bf_set_error("bf_pk_bin_static: nk = %lld is outside [1, %d], the most the built-in scratch array is sized for; "
+                     "use bf_pk_bin with a workspace", (long long)nk, PK_STATIC_MAX_NK);
+        return BF_E_INVALID;
+    }
+    const size_t need = bf_pk_bin_ws_bytes(ngrid, nk), have = bf_pk_bin_static_max_bytes();
+    if (need == 0 || need > have) {
+        bf_set_error("bf_pk_bin_static: ngrid = %lld, nk = %lld need %zu bytes of scratch on this device, the built-in array "
+                     "holds %zu; use bf_pk_bin with a workspace", (long long)ngrid, (long long)nk, need, have);
+        return BF_E_WORKSPACE;
+    }
+    int dev = 0;
+    BF_CUDA_OK(cudaGetDevice(&dev));
+    BF_REQUIRE(dev >= 0 && dev < PK_STATIC_MAX_DEVICES, "device ordinal beyond the per-device table");
+    if (!pk_static_ptr[dev]) {  // set-up, once per device, with that device current
+        double *p = nullptr;
+        BF_CUDA_OK(cudaGetSymbolAddress((void **)&p, pk_static_scratch));
+        BF_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned NULL");
+        pk_static_ptr[dev] = p;
+    }
+    return bf_pk_bin(ngrid, spectrum, strides_host, val, k0, dk, nk, out, pk_static_ptr[dev], have, stream);
+}

@@ -318,6 +318,17 @@ int bf_pk_ngp_deposit(int64_t np, const double *x, const double *y, const double
 size_t bf_pk_bin_ws_bytes(int64_t ngrid, int64_t nk);
 int bf_pk_bin(int64_t ngrid, const void *spectrum, const int64_t *strides_host, double val, double k0, double dk,
               int64_t nk, double *out, void *ws, size_t ws_bytes, void *stream);
+/* bf_pk_bin for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * NO counterpart in the reference.  The scratch bf_pk_bin takes as a
+ * workspace lives in a file-scope device array of bf_pk_bin_static_max_bytes() = 8 MiB that every GPU loading the library
+ * holds until exit; the call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine).  Limits: nk <= 256
+ * and bf_pk_bin_ws_bytes(ngrid, nk) <= 8 MiB (true for every ngrid on a GPU of up to 170 SMs) -- BF_E_INVALID /
+ * BF_E_WORKSPACE with a message otherwise.  All calls on a device SHARE the array: calls that overlap on the GPU
+ * (different streams) race; consecutive calls do not depend on each other (nothing in the array has to start at zero).
+ * Same arguments and results as bf_pk_bin (bit-identical on the same device). */
+size_t bf_pk_bin_static_max_bytes(void);
+int bf_pk_bin_static(int64_t ngrid, const void *spectrum, const int64_t *strides_host, double val, double k0, double dk,
+                     int64_t nk, double *out, void *stream);
 /* The same over a rectangular PIECE of the spectrum, for the slab-decomposed transform of the N-GPU path (SURVEY.md
  * 8(e), last row): ext_host[3] = logical extents of the piece (axes i, j, l), off_host[3] = global index of its first
  * element, strides_host as above (NULL = C order of the piece).  The [3][nk] sums of all pieces add up to bf_pk_bin's
