@@ -23,6 +23,7 @@
 // separate offsets array); the randomly accessed tables (4 B / cell, 4 B / entry, 32 B / halo) are kept small
 // enough to live in L2 and the records are streamed with evict-first hints.
 #include <cub/cub.cuh>
+#include <stdlib.h>
 
 #include "bf_common.cuh"
 
@@ -48,7 +49,7 @@ static snap_grid make_grid(int dim, double L, i64 ng) {
 }
 
 __device__ __forceinline__ int snap_cell_coord(double x, const snap_grid &G) {
-    int g = (int)floor(x * G.inv_cs);  // x = L (allowed by the single wrap, :259-260) lands in cell 0
+    int g = __double2int_rd(x * G.inv_cs);  // floor; x = L (allowed by the single wrap, :259-260) lands in cell 0
     if ((unsigned)g >= (unsigned)G.ng) { g %= G.ng; if (g < 0) g += G.ng; }
     return g;
 }
@@ -233,6 +234,7 @@ struct snap_args {
     u64 *pair_list;    // optional (bf_snap_pair_list): (particle << 32 | halo) of every pair, in arrival order
     u64 *pair_cursor;
     i64 pair_cap;
+    int wide;          // records in and out are 32-byte aligned: one 256-bit store per record (STG.256, sm_100)
 };
 
 struct __align__(16) snap_q {  // one queued pair: min-image separation in, displacement vector out (in place)
@@ -269,19 +271,40 @@ __device__ __forceinline__ bool snap_member(const double P[3], const double4 h, 
 template <int DIM, bool REC>
 __device__ __forceinline__ void snap_store(const snap_args &A, i64 p, double M, double nx, double ny, double nz) {
     if (REC) {
-        double2 *o = reinterpret_cast<double2 *>(A.rec_out + p);
-        __stcs(o, make_double2(M, nx));
-        __stcs(o + 1, make_double2(ny, nz));
+        if (A.wide) {  // one full 32-byte sector per lane, evict-first
+            asm volatile("st.global.cs.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(A.rec_out + p), "d"(M), "d"(nx), "d"(ny), "d"(nz)
+                         : "memory");
+        } else {
+            double2 *o = reinterpret_cast<double2 *>(A.rec_out + p);
+            __stcs(o, make_double2(M, nx));
+            __stcs(o + 1, make_double2(ny, nz));
+        }
     } else {
         __stcs(A.xo + p, nx); __stcs(A.yo + p, ny);
         if (DIM == 3) __stcs(A.zo + p, nz);
     }
 }
 
+// snap_act::idx -> particle index.  The chunked kernel numbers a warp's particles from the start of its chunk; the
+// streaming kernel numbers them along the warp's own sequence of tiles (tile n of warp gw is tile
+// (gw + (n / SS_CHUNK_TILES) W) SS_CHUNK_TILES + n % SS_CHUNK_TILES of the array: chunks are dealt round robin).
+#define SS_CHUNK_TILES 16
+struct snap_map_chunk {
+    i64 chunk0;
+    __device__ __forceinline__ i64 operator()(int idx) const { return chunk0 + idx; }
+};
+struct snap_map_stream {
+    i64 gw, W;
+    __device__ __forceinline__ i64 tile(int n) const {
+        return (gw + (i64)(n / SS_CHUNK_TILES) * W) * SS_CHUNK_TILES + (n % SS_CHUNK_TILES);
+    }
+    __device__ __forceinline__ i64 operator()(int idx) const { return tile(idx >> 5) * 32 + (idx & 31); }
+};
+
 // Process the first `nact` (<= 32) parked particles of this warp, one per lane.  Returns the number of pairs.
-template <int DIM, bool REC>
+template <int DIM, bool REC, class MAP>
 __device__ __forceinline__ int snap_drain(const snap_args &A, const int *__restrict__ entj, const snap_act *act,
-                                          snap_q *wq, int nact, i64 chunk0, int lane) {
+                                          snap_q *wq, int nact, const MAP &mp, int lane) {
     const double L = A.G.L;
     const bool on = lane < nact;
     double P[3] = {0.0, 0.0, 0.0}, M = 0.0;
@@ -363,7 +386,7 @@ __device__ __forceinline__ int snap_drain(const snap_args &A, const int *__restr
             const int j = e.j;
             if (A.pair_list) {  // the KD-tree's answer, for the parity tests: which particle met which halo
                 const u64 slot = atomicAdd(A.pair_cursor, 1ull);
-                if ((i64)slot < A.pair_cap) A.pair_list[slot] = ((u64)(chunk0 + act[e.src].idx) << 32) | (u64)j;
+                if ((i64)slot < A.pair_cap) A.pair_list[slot] = ((u64)mp(act[e.src].idx) << 32) | (u64)j;
             }
             double dx[3] = {e.v[0], e.v[1], e.v[2]};
             double dsq = dx[0] * dx[0] + dx[1] * dx[1];
@@ -387,7 +410,7 @@ __device__ __forceinline__ int snap_drain(const snap_args &A, const int *__restr
         __syncwarp();
     }
     if (on)
-        snap_store<DIM, REC>(A, chunk0 + idx, M, wrap_box(P[0] + tot[0], L), wrap_box(P[1] + tot[1], L),
+        snap_store<DIM, REC>(A, mp(idx), M, wrap_box(P[0] + tot[0], L), wrap_box(P[1] + tot[1], L),
                              (DIM == 3) ? wrap_box(P[2] + tot[2], L) : P[2]);
     return nq;
 }
@@ -458,7 +481,7 @@ __global__ void __launch_bounds__(SN_THREADS, SN_MINBLOCKS) snap_gather_kernel(s
         const bool flush = t0 + 2 >= SN_TILES;
         while (nwait >= 32 || (flush && nwait > 0)) {
             const int take = min(nwait, 32);
-            npairs += snap_drain<DIM, REC>(A, entj, act, wq, take, chunk0, lane);
+            npairs += snap_drain<DIM, REC>(A, entj, act, wq, take, snap_map_chunk{chunk0}, lane);
             __syncwarp();
             snap_act keep[2];
             const int left = nwait - take;
@@ -474,6 +497,174 @@ __global__ void __launch_bounds__(SN_THREADS, SN_MINBLOCKS) snap_gather_kernel(s
         }
     }
     if (lane == 0 && A.npairs && npairs) atomicAdd(A.npairs, (u64)npairs);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// streaming particle kernel for (M, x, y, z) records: the same per-warp pipeline (stream / park / drain), fed by TMA.
+//
+// The chunked kernel above is latency bound (ncu: long scoreboard 10 cycles per issue, 35 % of the warp slots
+// active, 3.2 TB/s of DRAM traffic): a warp's record loads, the dependent cell-table word and the dependent halo
+// record are three round trips to L2 / HBM in a row, and nothing is in flight for the warp while it drains its
+// parked particles.  Here every warp owns a ring of SS_D shared-memory tiles of 32 records (1 KB each) that lane 0
+// keeps full with bulk asynchronous copies (cp.async.bulk global -> shared, completion counted in bytes on one
+// mbarrier per slot, L2 evict-first hint): SS_D KB per warp are in flight at all times, also while the warp is
+// draining, and they hold no registers.  The dependent loads are software-pipelined over the ring:
+//     A(n + 2)  wait for tile n + 2, read its coordinates from shared memory, issue the cell-table load
+//     B(n + 1)  cell-table word of tile n + 1 has arrived: issue the load of the one halo record of single-halo cells
+//     C(n)      membership, write-through of the particles no halo reaches (one 256-bit store per record), parking
+//               of the others, re-issue of the slot with tile n + SS_D, drains
+// so a load is consumed one loop iteration after it was issued.  Warps take chunks of SS_CHUNK_TILES tiles round
+// robin over the whole grid (persistent CTAs, one wave), which keeps the DRAM front compact and balances the
+// halo-rich regions over all warps.  Results are the chunked kernel's bit for bit: the same membership test, the
+// same drain, the same summation order.
+// ---------------------------------------------------------------------------------------------------
+#define SS_WARPS 4
+#define SS_THREADS (32 * SS_WARPS)
+#ifndef SS_D
+#define SS_D 6
+#endif
+#ifndef SS_MINBLOCKS
+#define SS_MINBLOCKS 4
+#endif
+#define SS_AQ 64  // parked particles per warp: <= 31 left over + one tile
+
+struct __align__(128) ss_smem {
+    double4 ring[SS_WARPS][SS_D][32];
+    snap_act act[SS_WARPS][SS_AQ];
+    snap_q q[SS_WARPS][SN_WQ];
+    u64 bar[SS_WARPS][SS_D];
+};
+
+__device__ __forceinline__ void ss_tma_load(void *dst_smem, const void *src_gmem, unsigned bytes, u64 *bar, u64 policy) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bf_smem_u32(bar)), "r"(bytes) : "memory");
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+            bf_smem_u32(dst_smem)),
+        "l"(src_gmem), "r"(bytes), "r"(bf_smem_u32(bar)), "l"(policy)
+        : "memory");
+}
+
+template <int DIM>
+__global__ void __launch_bounds__(SS_THREADS, SS_MINBLOCKS) snap_stream_kernel(snap_args A) {
+    __shared__ ss_smem sm;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const snap_map_stream mp{(i64)blockIdx.x * SS_WARPS + wid, (i64)gridDim.x * SS_WARPS};
+    const i64 ntiles = (A.np + 31) >> 5;
+    if (mp.tile(0) >= ntiles) return;
+    double4(*ring)[32] = sm.ring[wid];
+    u64 *bar = sm.bar[wid];
+    snap_act *act = sm.act[wid];
+    snap_q *wq = sm.q[wid];
+    const int *__restrict__ entj = A.hdr->entj;
+    const double L = A.G.L;
+    u64 policy;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+    if (lane == 0)
+        for (int s = 0; s < SS_D; ++s) bf_mbar_init(&bar[s], 1);
+    __syncwarp();
+
+    // tile T of the array is tile n of this warp's sequence; the tile `ahead` places further on is T + ahead inside the
+    // chunk and one round of chunks later beyond it (ahead <= SS_CHUNK_TILES)
+    const i64 round_skip = (mp.W - 1) * SS_CHUNK_TILES;
+    auto tile_ahead = [&](i64 T, int r, int ahead) -> i64 { return T + ahead + ((r + ahead >= SS_CHUNK_TILES) ? round_skip : 0); };
+    auto issue = [&](i64 T, int slot) {  // lane 0: bulk copy of tile T into a ring slot
+        if (lane == 0 && T < ntiles) {
+            const i64 left = A.np - T * 32;
+            ss_tma_load(ring[slot], A.rec + T * 32, (unsigned)(left < 32 ? left : 32) * 32u, &bar[slot], policy);
+        }
+    };
+    auto stage_a = [&](i64 T, int slot, unsigned phase) -> int {  // cell-table word of this lane's particle of tile T
+        if (T >= ntiles) return 0;
+        bf_mbar_wait(&bar[slot], phase);
+        if (T * 32 + lane >= A.np) return 0;
+        const double2 *r = reinterpret_cast<const double2 *>(&ring[slot][lane]);
+        const double2 r0 = r[0], r1 = r[1];
+        int c = snap_cell_coord(r0.y, A.G) * A.G.ng + snap_cell_coord(r1.x, A.G);
+        if (DIM == 3) c = c * A.G.ng + snap_cell_coord(r1.y, A.G);
+        return __ldg(A.cell_tab + c);  // (ld.global.nc.L1::no_allocate here measured SLOWER: 4.19 vs 3.27 ms, the words then miss L2)
+    };
+
+    i64 T = mp.tile(0);  // tile of stage C
+    int r = 0;           // its place in the chunk
+    static_assert(SS_D >= 3 && SS_D <= SS_CHUNK_TILES, "ring depth");
+    for (int n = 0; n < SS_D; ++n) issue(tile_ahead(T, 0, n), n);
+    int tab_a = stage_a(T, 0, 0u), tab_b = tab_a;
+    double4 h_b = make_double4(0.0, 0.0, 0.0, 0.0);
+    if (tab_b < 0) h_b = ldg_rec(A.hrec + (-tab_b - 1));
+    tab_a = stage_a(tile_ahead(T, 0, 1), 1, 0u);
+    int slot = 0, slot_a = 2;        // ring slots of stage C and of stage A (two tiles ahead)
+    unsigned phase_a = 0u;           // parity of stage A's slot: flips every time slot_a wraps
+    int nwait = 0, npairs = 0;
+    for (int n = 0; T < ntiles; ++n) {
+        int tab = tab_b;
+        const double4 h = h_b;
+        tab_b = tab_a;  // B(n + 1)
+        if (tab_b < 0) h_b = ldg_rec(A.hrec + (-tab_b - 1));
+        tab_a = stage_a(tile_ahead(T, r, 2), slot_a, phase_a);  // A(n + 2)
+        // C(n)
+        const i64 p = T * 32 + lane;
+        const bool valid = p < A.np;
+        double P[3] = {0.0, 0.0, 0.0}, M = 0.0;
+        if (valid) {
+            const double2 *rr = reinterpret_cast<const double2 *>(&ring[slot][lane]);
+            const double2 r0 = rr[0], r1 = rr[1];
+            M = r0.x; P[0] = r0.y; P[1] = r1.x; P[2] = r1.y;
+        }
+        if (tab < 0) {  // single-halo cell: decided here, only particles that do move are parked
+            double dx[3];
+            if (!snap_member<DIM>(P, h, L, dx)) tab = 0;
+        }
+        const bool park = tab != 0;
+        if (valid && !park) {
+            // the single wrap (:259-260) only ever acts on a coordinate outside [0, L]: one test for the three of them
+            const double lo = fmin(fmin(P[0], P[1]), (DIM == 3) ? P[2] : P[0]), hi = fmax(fmax(P[0], P[1]), (DIM == 3) ? P[2] : P[0]);
+            if (lo < 0.0 || hi > L) {
+                P[0] = wrap_box(P[0], L); P[1] = wrap_box(P[1], L);
+                if (DIM == 3) P[2] = wrap_box(P[2], L);
+            }
+            snap_store<DIM, true>(A, p, M, P[0], P[1], P[2]);
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, park);
+        if (park) {
+            snap_act &e = act[nwait + __popc(bal & ((1u << lane) - 1u))];
+            e.M = M; e.x = P[0]; e.y = P[1]; e.z = P[2];
+            e.tab = tab; e.idx = n * 32 + lane;
+        }
+        nwait += __popc(bal);
+        __syncwarp();                              // every lane has consumed its record of the slot (stored or parked)
+        issue(tile_ahead(T, r, SS_D), slot);       // ... so the slot can take the tile SS_D ahead
+        // advance the cursors
+        T = tile_ahead(T, r, 1);
+        r = (r + 1 == SS_CHUNK_TILES) ? 0 : r + 1;
+        slot = (slot + 1 == SS_D) ? 0 : slot + 1;
+        if (++slot_a == SS_D) { slot_a = 0; phase_a ^= 1u; }
+        const bool flush = T >= ntiles;
+        while (nwait >= 32 || (flush && nwait > 0)) {
+            const int take = min(nwait, 32);
+            npairs += snap_drain<DIM, true>(A, entj, act, wq, take, mp, lane);
+            __syncwarp();
+            const int left = nwait - take;  // <= 31
+            snap_act keep;
+            if (lane < left) keep = act[take + lane];
+            __syncwarp();
+            if (lane < left) act[lane] = keep;
+            nwait = left;
+            __syncwarp();
+        }
+    }
+    if (lane == 0 && A.npairs && npairs) atomicAdd(A.npairs, (u64)npairs);
+}
+
+static int ss_resident_blocks(int dim) {  // CTAs of the streaming kernel one SM holds (queried once per process)
+    static int nb[2] = {0, 0};
+    int &v = nb[dim - 2];
+    if (v == 0) {
+        int n = 0;
+        cudaError_t e = (dim == 2) ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, snap_stream_kernel<2>, SS_THREADS, 0)
+                                   : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, snap_stream_kernel<3>, SS_THREADS, 0);
+        v = (e == cudaSuccess && n > 0) ? n : SS_MINBLOCKS;
+    }
+    return v;
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -571,6 +762,18 @@ static int snap_launch(int dim, int64_t np, snap_args &A, double L, int64_t ng, 
     A.hdr = w.hdr;
     unsigned pb = (unsigned)((np + SN_TILE - 1) / SN_TILE);
     cudaStream_t s = (cudaStream_t)stream;
+    A.wide = rec && ((((uintptr_t)A.rec | (uintptr_t)A.rec_out) & 31) == 0);
+    static const bool chunked = getenv("BF_SNAP_CHUNKED") != nullptr;  // tuning / cross-check: the round-1 kernel
+    if (rec && !chunked && !A.pair_list) {
+        const i64 nchunks = (np + 32 * SS_CHUNK_TILES - 1) / (32 * SS_CHUNK_TILES);
+        i64 blocks = (nchunks + SS_WARPS - 1) / SS_WARPS;
+        const i64 wave = (i64)bf_sm_count() * ss_resident_blocks(dim);  // persistent CTAs: one wave
+        if (blocks > wave) blocks = wave;
+        if (dim == 2) snap_stream_kernel<2><<<(unsigned)blocks, SS_THREADS, 0, s>>>(A);
+        else snap_stream_kernel<3><<<(unsigned)blocks, SS_THREADS, 0, s>>>(A);
+        BF_LAUNCH_OK();
+        return BF_OK;
+    }
     if (dim == 2) {
         if (rec) snap_gather_kernel<2, true><<<pb, SN_THREADS, 0, s>>>(A);
         else snap_gather_kernel<2, false><<<pb, SN_THREADS, 0, s>>>(A);

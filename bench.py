@@ -535,15 +535,16 @@ def run_snapshot(args, rank, local_rank, world):
     if rank == 0:
         peak, peak_src = peaks()
         alg = (cat.size * B_PARTICLE + npairs * B_SNAP_PAIR) / world
+        kname = "snap_gather_kernel<3,1>" if os.environ.get("BF_SNAP_CHUNKED") else "snap_stream_kernel<3>"
         ach = alg / (ms_k * 1e-3) / 1e9
-        traffic = measured_traffic("snap_gather_kernel<3,true>", "bf_snapshot.cu") if (world == 1 and args.npart_side == 512) else None
+        traffic = measured_traffic(kname, "bf_snapshot.cu") if (world == 1 and args.npart_side == 512) else None
         out_j = {"metric": "particle updates/sec", "value": cat.size / (ms_step * 1e-3), "unit": "particles/s",
                  "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
                  "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                  "config": dict({"workload": workload_name(args), "parallelism": f"particle-index x{world}",
                                  "pairs": npairs, "timed_region_repeats": reps,
                                  "l2": "particle records (64 B/particle in+out) far exceed the 126 MB L2"}, **n1),
-                 "roofline": {"bound": "hbm", "kernel": "snap_gather_kernel<3,true>", "achieved": ach, "peak": peak,
+                 "roofline": {"bound": "hbm", "kernel": kname, "achieved": ach, "peak": peak,
                               "unit": "GB/s", "frac": ach / peak, "peak_source": peak_src, "kernel_ms": ms_k,
                               "traffic": traffic,
                               "dram": None if traffic is None else {"gbs": traffic / (ms_k * 1e-3) / 1e9,
