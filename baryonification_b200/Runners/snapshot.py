@@ -46,10 +46,20 @@ class _RecordPipeline:
     def _upload(self):
         try:
             import warnings
+            dv.thread_budget()  # (a helper thread does not inherit the main thread's torch.set_num_threads)
             with warnings.catch_warnings():  # a read-only input is only ever read here
                 warnings.simplefilter("ignore")
                 src = torch.from_numpy(self.rec)
             with torch.cuda.device(self.dev):
+                if dv.pin_in_place(self.rec):  # page-locked where it lies (a repeated input): no staging copy
+                    for i, (a, b) in enumerate(self.bounds):
+                        if i >= 2:  # two requests in flight at most: the halo set-up's small uploads share the one
+                            self.ready[i - 2].synchronize()  # host-to-device copy engine and must not queue behind GBs
+                        with torch.cuda.stream(self.h2d):
+                            self.d_in[a:b].copy_(src[a:b], non_blocking=True)
+                            self.ready[i].record(self.h2d)
+                        self.queued[i].set()
+                    return
                 stage = [torch.empty((min(self.CHUNK, src.shape[0]), 4), dtype=torch.float64, pin_memory=True)
                          for _ in range(3)]
                 free = [None] * 3
@@ -57,7 +67,8 @@ class _RecordPipeline:
                     k = i % 3
                     if free[k] is not None:
                         free[k].synchronize()  # the H2D copy that last used this staging buffer is done
-                    stage[k][: b - a].copy_(src[a:b])
+                    stage[k][: b - a].copy_(src[a:b])  # (torch's OpenMP copy: a Python thread pool per 32 MB chunk
+                    # fights the main thread for the GIL -- measured 181 vs 138 ms end to end)
                     with torch.cuda.stream(self.h2d):
                         self.d_in[a:b].copy_(stage[k][: b - a], non_blocking=True)
                         self.ready[i].record(self.h2d)

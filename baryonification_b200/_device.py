@@ -25,61 +25,171 @@ def ptr(t):
     return C.c_void_p(0) if t is None else C.c_void_p(t.data_ptr())
 
 
+def thread_budget():
+    """Call first in every helper thread that copies host memory with torch.  torchrun starts the ranks with
+    OMP_NUM_THREADS=1, and a thread created later takes its OpenMP team size from that environment default, not from the
+    main thread's ``torch.set_num_threads`` -- its pageable -> page-locked staging copies (GBs per call) would run on one
+    core.  Gives the thread this rank's share of the host cores (never fewer than it has)."""
+    from .host import host_cores
+    n = host_cores()
+    if torch.get_num_threads() < n:
+        torch.set_num_threads(n)
+    return n
+
+
+_copy_pool = None
+
+
+def host_copy(dst, src):
+    """``dst.copy_(src)`` for contiguous host tensors of one dtype, as ``numpy.copyto`` of equal pieces in a thread pool
+    of this rank's share of the host cores (numpy releases the GIL in its copy loops).  Measured on the B200 boxes
+    (scripts/host_copy_probe.py, 800 MB pageable -> page-locked): torch ``copy_`` 7.7 GB/s on one thread -- what a helper
+    thread gets under torchrun's OMP_NUM_THREADS=1 -- and 46 GB/s on 8; numpy in a pool 15.7 GB/s on one thread, 75 GB/s
+    on 8; the PCIe link moves 55 GB/s, so only the pooled copy keeps the staging off the critical path."""
+    global _copy_pool
+    n = dst.numel()
+    if (n < (1 << 20) or dst.dtype != src.dtype or not dst.is_contiguous() or not src.is_contiguous()
+            or dst.device.type != "cpu" or src.device.type != "cpu"):
+        dst.copy_(src)
+        return dst
+    from concurrent.futures import ThreadPoolExecutor
+    from .host import host_cores
+    nt = max(1, min(16, host_cores()))
+    if _copy_pool is None or _copy_pool._max_workers != nt:
+        _copy_pool = ThreadPoolExecutor(max_workers=nt, thread_name_prefix="bf-copy")
+    import warnings
+    with warnings.catch_warnings():  # (a read-only source is only ever read)
+        warnings.simplefilter("ignore")
+        d, s = dst.view(-1).numpy(), src.detach().view(-1).numpy()
+    edges = np.linspace(0, n, nt + 1).astype(np.int64)
+    list(_copy_pool.map(lambda i: np.copyto(d[edges[i]:edges[i + 1]], s[edges[i]:edges[i + 1]]), range(nt)))
+    return dst
+
+
+# ---- page-locking a caller's array in place -------------------------------------------------------------------------
+# Staging a large input through page-locked memory costs a host memcpy that all ranks of a box share (1.6 GB of map at
+# ~76 GB/s = 21 ms however many GPUs work on it) -- hidden behind a 54 ms pair kernel on one GPU, exposed behind a 7 ms
+# one on eight.  Baryonification runs are parameter sweeps: the same map / snapshot is processed again and again with
+# other models.  So an input of >= 64 MiB is staged the FIRST time it is seen and page-locked where it lies
+# (cudaHostRegister) the SECOND time; from then on its rows go to the GPU straight from the caller's memory at PCIe
+# speed.  One-shot callers never pay the registration (~0.1 ms per MB), and the registration ends with the array
+# (weakref finaliser on the array that owns the memory).  BF_PIN_INPUTS=0 turns it off, =1 registers at first sight.
+_PIN_MIN_BYTES = 64 << 20
+_pin_seen, _pin_done = {}, {}
+
+
+def _root_owner(a):
+    while isinstance(getattr(a, "base", None), np.ndarray):
+        a = a.base
+    return a
+
+
+def _unpin(key):
+    ptr = _pin_done.pop(key, None)
+    if ptr is not None:
+        try:
+            torch.cuda.cudart().cudaHostUnregister(ptr)
+        except Exception:
+            pass
+
+
+def pin_in_place(a):
+    """True when the memory of the C-contiguous numpy array ``a`` is page-locked (now or already): the caller may issue
+    asynchronous copies straight from it."""
+    import os
+    import weakref
+    mode = os.environ.get("BF_PIN_INPUTS", "")
+    if mode == "0" or not torch.cuda.is_available() or not a.flags.c_contiguous or a.nbytes < _PIN_MIN_BYTES:
+        return False
+    root = _root_owner(a)
+    lo = a.__array_interface__["data"][0]
+    for (p0, n0) in _pin_done:  # (a slice of a registered array)
+        if p0 <= lo and lo + a.nbytes <= p0 + n0:
+            return True
+    key = (lo, a.nbytes)  # (the range that is used -- a rank's slice of the map -- not the whole owning array)
+    if _pin_seen.get(key) == "failed":
+        return False
+    if key not in _pin_seen and mode != "1":
+        _pin_seen[key] = "seen"
+        try:  # forget the sighting when the array goes away (its address may be reused)
+            weakref.finalize(root, _pin_seen.pop, key, None)
+        except TypeError:
+            _pin_seen[key] = "failed"
+        return False
+    try:
+        fin = weakref.finalize(root, _unpin, key)
+    except TypeError:
+        _pin_seen[key] = "failed"
+        return False
+    rc = torch.cuda.cudart().cudaHostRegister(key[0], key[1], 0)
+    if int(rc) != 0:
+        fin.detach()
+        _pin_seen[key] = "failed"
+        return False
+    _pin_done[key] = key[0]
+    return True
+
+
+def _as_tensor(a):
+    import warnings
+    with warnings.catch_warnings():  # (a read-only input is only ever read)
+        warnings.simplefilter("ignore")
+        return torch.from_numpy(a)
+
+
 def to_dev(a, dtype=np.float64, dev=None, pinned=False):
-    """numpy -> device tensor (contiguous).  `pinned` stages through page-locked memory (async H2D)."""
+    """numpy -> device tensor (contiguous).  `pinned` stages through page-locked memory (async H2D) unless the array is
+    page-locked in place (``pin_in_place``)."""
     a = np.ascontiguousarray(a, dtype=dtype)
-    t = torch.from_numpy(a)
-    if pinned:
-        t = t.pin_memory()
+    t = _as_tensor(a)
+    if pinned and not pin_in_place(a):
+        t = host_copy(torch.empty(t.shape, dtype=t.dtype, pin_memory=True), t)
     return t.to(dev or device(), non_blocking=pinned)
 
 
-class AsyncUpload:
-    """Pageable numpy array -> HBM, off the critical path.
+_PIECE = 8 << 20  # elements (64 MiB of float64) per H2D request of a large upload
 
-    A helper thread copies the caller's array into page-locked memory (torch's caching host allocator keeps the
-    block for the next call; the CPU copy is multi-threaded) and enqueues the H2D copy on a side stream, while
-    the main thread sets up halos and runs the binning / pair kernels.  ``result()`` joins and makes the current
-    stream wait for the copy."""
 
-    def __init__(self, a, dev, dtype=np.float64):
-        import threading
-        self.dev = dev
-        self.side = torch.cuda.Stream(device=dev)
-        self.done = torch.cuda.Event()
-        self.out = None
-        self.err = None
-        a = np.ascontiguousarray(a, dtype=dtype)
-
-        def work():
-            try:
-                with torch.cuda.device(dev):
-                    src = torch.from_numpy(a) if a.flags.writeable else torch.from_numpy(a.copy())
-                    pin = torch.empty(src.shape, dtype=src.dtype, pin_memory=True)
-                    pin.copy_(src)
-                    with torch.cuda.stream(self.side):
-                        self.out = pin.to(dev, non_blocking=True)
-                        self.done.record(self.side)
-            except BaseException as e:  # re-raised in result()
-                self.err = e
-
-        self.th = threading.Thread(target=work, daemon=True)
-        self.th.start()
-
-    def result(self):
-        self.th.join()
-        if self.err is not None:
-            raise self.err
-        torch.cuda.current_stream(self.dev).wait_event(self.done)
-        self.out.record_stream(torch.cuda.current_stream(self.dev))
-        return self.out
+def _trickle(dev, side, src, out, pinned, edges, on_range):
+    """Copy the flat host tensor ``src`` to the device tensor ``out`` range by range (``edges``) on stream ``side``,
+    calling ``on_range(i)`` (with ``side`` current) when range i has been enqueued.  Every range goes as requests of at
+    most 64 MiB, and a request is only enqueued when the one before it has finished: the GPU has ONE host-to-device copy
+    engine, and the per-halo scalars, tables and counters that the other streams upload meanwhile would otherwise queue
+    behind the whole map (measured: 30 ms added to the binning stage when 1.6 GB was enqueued at once).  With ``pinned``
+    false every request is staged through page-locked memory first (``host_copy``)."""
+    half = max(1, min(_PIECE, max((hi - lo for lo, hi in zip(edges[:-1], edges[1:])), default=1)))  # largest request
+    stage = None if pinned else torch.empty(2 * half, dtype=src.dtype, pin_memory=True)
+    prev, k = [None, None], 0
+    for i, (lo, hi) in enumerate(zip(edges[:-1], edges[1:])):
+        for p0 in range(lo, hi, _PIECE):
+            p1 = min(p0 + _PIECE, hi)
+            slot = k & 1
+            if prev[slot] is not None:
+                prev[slot].synchronize()  # (also: the staging half this request reuses is free again)
+            if pinned:
+                piece = src[p0:p1]
+                if prev[slot ^ 1] is not None:
+                    prev[slot ^ 1].synchronize()
+            else:
+                piece = host_copy(stage[slot * half: slot * half + (p1 - p0)], src[p0:p1])
+            with torch.cuda.stream(side):
+                out[p0:p1].copy_(piece, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(side)
+            prev[slot] = ev
+            k += 1
+        with torch.cuda.stream(side):
+            on_range(i)
+    return stage
 
 
 class ChunkedUpload:
-    """``AsyncUpload`` in consecutive pieces: ``edges`` cuts the (flat) array into ranges that are staged and copied in
-    order, each with its own completion event, so that a consumer that works through the array front to back
-    (the ring-band pipeline of ``ShellEngine.baryonify_to_host``) can start on the first range while the rest is still
-    on its way.  ``wait(i)`` makes the current stream wait for range i; ``.out`` is the whole device array."""
+    """Pageable (or page-locked-in-place, ``pin_in_place``) numpy array -> HBM, off the critical path, in consecutive
+    ranges: ``edges`` cuts the (flat) array into ranges that travel in order, each with its own completion event, so that
+    a consumer that works through the array front to back (the ring-band pipeline of ``ShellEngine.baryonify_to_host``)
+    can start on the first range while the rest is still on its way.  A helper thread feeds the copy engine
+    (``_trickle``) while the main thread sets up halos and runs the binning / pair kernels.  ``wait(i)`` makes the
+    current stream wait for range i; ``result()`` for all of them; ``.out`` is the whole device array."""
 
     def __init__(self, a, dev, edges, dtype=np.float64):
         import threading
@@ -89,21 +199,19 @@ class ChunkedUpload:
         self.events = [torch.cuda.Event() for _ in range(len(self.edges) - 1)]
         self.ready = [threading.Event() for _ in self.events]
         self.err = None
-        a = np.ascontiguousarray(a, dtype=dtype).reshape(-1)
+        self.keep = a = np.ascontiguousarray(a, dtype=dtype).reshape(-1)
         self.out = torch.empty(a.shape, dtype=torch.float64, device=dev)
+        pinned = pin_in_place(a)
+
+        def on_range(i):
+            self.events[i].record(self.side)
+            self.ready[i].set()
 
         def work():
             try:
+                thread_budget()
                 with torch.cuda.device(dev):
-                    src = torch.from_numpy(a) if a.flags.writeable else torch.from_numpy(a.copy())
-                    pin = torch.empty(src.shape, dtype=src.dtype, pin_memory=True)
-                    for i, (lo, hi) in enumerate(zip(self.edges[:-1], self.edges[1:])):
-                        pin[lo:hi].copy_(src[lo:hi])
-                        with torch.cuda.stream(self.side):
-                            self.out[lo:hi].copy_(pin[lo:hi], non_blocking=True)
-                            self.events[i].record(self.side)
-                        self.ready[i].set()
-                    self.pin = pin  # (alive until the copies are done; released with the object)
+                    self.stage = _trickle(dev, self.side, _as_tensor(a), self.out, pinned, self.edges, on_range)
             except BaseException as e:  # re-raised in wait()
                 self.err = e
                 for r in self.ready:
@@ -124,6 +232,18 @@ class ChunkedUpload:
         self.th.join()
         self.out.record_stream(torch.cuda.current_stream(self.dev))
         return self.out
+
+
+class AsyncUpload(ChunkedUpload):
+    """``ChunkedUpload`` of the whole array as one range (any shape)."""
+
+    def __init__(self, a, dev, dtype=np.float64):
+        a = np.ascontiguousarray(a, dtype=dtype)
+        self.shape = a.shape
+        super().__init__(a, dev, [0, a.size], dtype)
+
+    def result(self):
+        return super().result().view(self.shape)
 
 
 def to_host(t, pinned=True):

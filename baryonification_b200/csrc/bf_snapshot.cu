@@ -521,7 +521,7 @@ __global__ void __launch_bounds__(SN_THREADS, SN_MINBLOCKS) snap_gather_kernel(s
 #define SS_WARPS 4
 #define SS_THREADS (32 * SS_WARPS)
 #ifndef SS_D
-#define SS_D 6
+#define SS_D 4
 #endif
 #ifndef SS_MINBLOCKS
 #define SS_MINBLOCKS 4

@@ -377,11 +377,8 @@ def claim_host_threads():
     """torchrun starts every rank with OMP_NUM_THREADS=1, which makes torch's pageable -> page-locked staging copies (the
     map slice, the particle records: GBs per call) single-threaded.  The sharded runners give torch this rank's share of
     the host cores instead (never fewer threads than it already has)."""
-    from .host import host_cores
-    n = host_cores()
-    if torch.get_num_threads() < n:
-        torch.set_num_threads(n)
-    return n
+    from ._device import thread_budget
+    return thread_budget()
 
 
 _SHELL_KEYS = ("a", "D", "radius", "z_in", "M_in", "lon", "lat", "cut", "lnr_shift")
@@ -432,40 +429,52 @@ class ShardedShell:
         a, b = index_split(n, self.world)[self.rank]
         part = copy.copy(cat)
         part.cat = cat.cat[a:b]
+        import time
+        t_host = time.perf_counter()
         s = host.shell_scalars(part, r.cosmo, r.mass_def, r.epsilon_max, r.model, self.baryonify)
+        self.timings["host_scalars"] = time.perf_counter() - t_host  # (part of host_setup_allgather)
         ex = host.property_columns(part.cat, r.model)
         nx = 0 if ex is None else ex.shape[1]
-        width = len(_SHELL_KEYS) + 3 + nx
+        nk = len(_SHELL_KEYS)
+        width = nk + 3 + nx
         chunk = -(-n // self.world) if n else 0  # equal pieces for one all_gather_into_tensor
-        mine = torch.zeros((chunk, width), dtype=torch.float64, pin_memory=torch.cuda.is_available())
-        m = mine.numpy()
+        # one ROW per scalar (key-major): the page-locked slabs the host set-up wrote go up as they are, one asynchronous
+        # copy each -- no host-side interleave into a [halo][key] staging array
+        pins = s.get("_pinned") or {}
+        mine_d = torch.zeros((width, chunk), dtype=torch.float64, device=dev)
+
+        def up(k):
+            src = pins[k] if k in pins else torch.from_numpy(np.ascontiguousarray(s[k], dtype=np.float64))
+            return src.to(dev, non_blocking=True)
+
         for c, k in enumerate(_SHELL_KEYS):
-            m[:b - a, c] = s[k]
-        m[:b - a, len(_SHELL_KEYS):len(_SHELL_KEYS) + 3] = s["vec"]
+            mine_d[c, :b - a].copy_(up(k), non_blocking=True)
+        mine_d[nk:nk + 3, :b - a] = up("vec").t()
         if nx:
-            m[:b - a, len(_SHELL_KEYS) + 3:] = ex
-        mine_d = mine.to(dev, non_blocking=True)
+            mine_d[nk + 3:, :b - a] = torch.from_numpy(ex).to(dev).t()
         if self.world > 1:
-            full = torch.empty((chunk * self.world, width), dtype=torch.float64, device=dev)
-            dist.all_gather_into_tensor(full, mine_d, group=self.group)
+            full = torch.empty((self.world, width, chunk), dtype=torch.float64, device=dev)
+            dist.all_gather_into_tensor(full.view(-1), mine_d.view(-1), group=self.group)
             sizes = [hi - lo for lo, hi in index_split(n, self.world)]
-            if any(sz != chunk for sz in sizes):  # drop the padding rows of the shorter pieces
-                full = torch.cat([full[i * chunk:i * chunk + sz] for i, sz in enumerate(sizes)])
+            if all(sz == chunk for sz in sizes):
+                full = full.permute(1, 0, 2).reshape(width, chunk * self.world)
+            else:  # drop the padding columns of the shorter pieces
+                full = torch.cat([full[i, :, :sz] for i, sz in enumerate(sizes)], dim=1)
         else:
-            full = mine_d[:n]
+            full = mine_d[:, :n]
         nside = r.LightconeShell.NSIDE
         ci = {k: c for c, k in enumerate(_SHELL_KEYS)}
         if self.world > 1:  # halos_touching_bands on the device (conservative by `margin_rings`, like the host form)
             lo, hi = bands
-            theta0 = torch.acos(full[:, len(_SHELL_KEYS) + 2].clamp(-1.0, 1.0))
-            rad = full[:, ci["radius"]]
+            theta0 = torch.acos(full[nk + 2].clamp(-1.0, 1.0))
+            rad = full[ci["radius"]]
             first_ring, last_ring = max(lo * 8 + 1 - 3, 0), min(hi * 8 + 3, 4 * nside)
             t_lo, t_hi = float(ring_colatitude(nside, first_ring)), float(ring_colatitude(nside, last_ring))
             keep = ((theta0 + rad >= t_lo) & (theta0 - rad <= t_hi)) | ~torch.isfinite(rad)
-            full = full[keep]
-        t = {k: full[:, ci[k]].contiguous() for k in _SHELL_KEYS}
-        t["vec"] = full[:, len(_SHELL_KEYS):len(_SHELL_KEYS) + 3].contiguous()
-        t["extras"] = full[:, len(_SHELL_KEYS) + 3:].contiguous() if nx else None
+            full = full[:, keep]
+        t = {k: full[ci[k]].contiguous() for k in _SHELL_KEYS}
+        t["vec"] = full[nk:nk + 3].t().contiguous()
+        t["extras"] = full[nk + 3:].t().contiguous() if nx else None
         return t
 
     def process_device(self, gather=False):
@@ -485,12 +494,13 @@ class ShardedShell:
         htab = displacement_host_table(r.model) if self.baryonify else profile_host_table(r.model, "2D")
         with torch.cuda.device(dev):
             t0 = time.perf_counter()
-            up = None
-            if self.baryonify:  # this rank's slice of the map travels while the halos are prepared
-                orig = np.ascontiguousarray(r.LightconeShell.map, dtype=np.float64).reshape(-1)
-                up = dv.AsyncUpload(orig[first:last], dev)
             t = self.scalars_device(dev, (lo, hi))
             t0 = self._tick("host_setup_allgather", t0, dev)
+            up = None
+            if self.baryonify:  # this rank's slice of the map travels under the binning and the pair kernel (after the
+                # host set-up, not beside it: the staging copy would compete with it for the host cores)
+                orig = np.ascontiguousarray(r.LightconeShell.map, dtype=np.float64).reshape(-1)
+                up = dv.ChunkedUpload(orig[first:last], dev, np.linspace(0, last - first, 9).astype(np.int64))
             eng = engine.ShellEngine(nside, mode, htab, None, dev, variant="gather", bands=(lo, hi))
             eng.max_entries = getattr(self, "_bin_hint", 0)  # (a repeated call skips the counting pass of the binning)
             eng.upload_device(t).bin()
@@ -527,7 +537,7 @@ class ShardedShell:
 
     def _tick(self, name, t0, dev):
         import time
-        torch.cuda.synchronize(dev)
+        torch.cuda.current_stream(dev).synchronize()  # (this stream only: the map upload on its side stream runs on)
         self.timings[name] = time.perf_counter() - t0
         return time.perf_counter()
 
