@@ -88,7 +88,7 @@ def _unpin(key):
     ptr = _pin_done.pop(key, None)
     if ptr is not None:
         try:
-            torch.cuda.cudart().cudaHostUnregister(ptr)
+            _lib.load().bf_host_unpin(C.c_void_p(ptr))
         except Exception:
             pass
 
@@ -103,13 +103,16 @@ def pin_in_place(a):
         return False
     root = _root_owner(a)
     lo = a.__array_interface__["data"][0]
-    for (p0, n0) in _pin_done:  # (a slice of a registered array)
+    for (p0, n0) in list(_pin_done):  # (a slice of a registered range)
         if p0 <= lo and lo + a.nbytes <= p0 + n0:
             return True
     key = (lo, a.nbytes)  # (the range that is used -- a rank's slice of the map -- not the whole owning array)
-    if _pin_seen.get(key) == "failed":
+    state = _pin_seen.get(key)
+    if state == "failed":
         return False
-    if key not in _pin_seen and mode != "1":
+    if state == "pinned":  # page-locked by its owner (a Runner's own result array fed back in)
+        return True
+    if state is None and mode != "1":
         _pin_seen[key] = "seen"
         try:  # forget the sighting when the array goes away (its address may be reused)
             weakref.finalize(root, _pin_seen.pop, key, None)
@@ -121,12 +124,12 @@ def pin_in_place(a):
     except TypeError:
         _pin_seen[key] = "failed"
         return False
-    rc = torch.cuda.cudart().cudaHostRegister(key[0], key[1], 0)
-    if int(rc) != 0:
+    rc = int(_lib.load(require_cuda=True).bf_host_pin(C.c_void_p(lo), a.nbytes))
+    if rc != 0:
         fin.detach()
-        _pin_seen[key] = "failed"
-        return False
-    _pin_done[key] = key[0]
+        _pin_seen[key] = "pinned" if rc == 1 else "failed"
+        return rc == 1
+    _pin_done[key] = lo
     return True
 
 

@@ -58,6 +58,8 @@ _SIGS = {
     "bf_launch_count": (C.c_ulonglong, []),
     "bf_probe_fp64": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_ulonglong), C.c_void_p]),
     "bf_device_sm_count": (C.c_int, [_P(C.c_int)]),
+    "bf_host_pin": (C.c_int, [C.c_void_p, C.c_size_t]),
+    "bf_host_unpin": (C.c_int, [C.c_void_p]),
     "bf_table_collapse_zM": (C.c_int, [_P(Table), _i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p]),
     "bf_table_collapse_nd": (C.c_int, [_P(TableND), _i64, _dbl_p, _dbl_p, C.c_void_p]),
     "bf_table_readout": (C.c_int, [_P(Table), _dbl_p, _i64, _dbl_p, C.c_double, C.c_double, C.c_int, _dbl_p,
@@ -129,6 +131,9 @@ _SIGS = {
                                     C.c_void_p]),
     "bf_snap_displace_records": (C.c_int, [C.c_int, _i64, C.c_void_p, C.c_double, C.c_double, _P(SnapHalos), _P(Table),
                                            _i64, C.c_void_p, C.c_void_p, _dbl_p, C.c_void_p]),
+    "bf_make_map_ws_bytes": (C.c_size_t, [_i64]),
+    "bf_make_map": (C.c_int, [C.c_int, _i64, _dbl_p, _dbl_p, _dbl_p, _dbl_p, C.c_void_p, _dbl_p, _i64, _dbl_p, C.c_void_p,
+                              C.c_size_t, C.c_void_p]),
     "bf_pk_ngp_deposit": (C.c_int, [_i64, _dbl_p, _dbl_p, _dbl_p, C.c_void_p, C.c_double, _i64, _dbl_p, C.c_void_p]),
     "bf_pk_bin_ws_bytes": (C.c_size_t, [_i64, _i64]),
     "bf_pk_bin": (C.c_int, [_i64, C.c_void_p, _P(_i64), C.c_double, C.c_double, C.c_double, _i64, _dbl_p, C.c_void_p,

@@ -55,3 +55,38 @@ extern "C" int bf_device_sm_count(int *sm_count_host) {
     *sm_count_host = n;
     return BF_OK;
 }
+
+// Page-locking a caller's host array where it lies (the Python side registers large inputs that are processed
+// repeatedly, _device.pin_in_place).  The CUDA runtime keeps a failed call's error code until somebody asks for it, and
+// the next unrelated check (torch's, ours) would then report it -- so these two wrappers always leave the error state
+// clean.  bf_host_pin: 0 = registered now, 1 = already page-locked (cudaHostAlloc / registered before: nothing to do),
+// BF_E_INVALID = could not be registered.  bf_host_unpin undoes a 0.
+extern "C" int bf_host_pin(void *ptr, size_t bytes) {
+    BF_REQUIRE(ptr != nullptr && bytes > 0, "ptr / bytes");
+    cudaPointerAttributes at;
+    cudaError_t e = cudaPointerGetAttributes(&at, ptr);
+    if (e == cudaSuccess && at.type == cudaMemoryTypeHost) {
+        cudaPointerAttributes last;
+        e = cudaPointerGetAttributes(&last, (const char *)ptr + (bytes - 1));
+        if (e == cudaSuccess && last.type == cudaMemoryTypeHost) return 1;
+    }
+    (void)cudaGetLastError();
+    e = cudaHostRegister(ptr, bytes, cudaHostRegisterDefault);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        bf_set_error("bf_host_pin: cudaHostRegister(%p, %zu) -> %s", ptr, bytes, cudaGetErrorString(e));
+        return BF_E_INVALID;
+    }
+    return BF_OK;
+}
+
+extern "C" int bf_host_unpin(void *ptr) {
+    BF_REQUIRE(ptr != nullptr, "ptr");
+    cudaError_t e = cudaHostUnregister(ptr);
+    (void)cudaGetLastError();
+    if (e != cudaSuccess) {
+        bf_set_error("bf_host_unpin: cudaHostUnregister(%p) -> %s", ptr, cudaGetErrorString(e));
+        return BF_E_INVALID;
+    }
+    return BF_OK;
+}

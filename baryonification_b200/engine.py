@@ -457,27 +457,38 @@ class ShellEngine:
         main.synchronize()
         return out.numpy(), new_sum, old_sum
 
-    def accumulate_to_host(self, chunks=8):
+    def accumulate_to_host(self, chunks=8, out_h=None):
         """Pair stage + read-back of the accumulator (PaintProfilesShell) -> host array.  Pixel owners finish ring band
-        by ring band, so the gather kernel is launched over ``chunks`` groups of bands (equal pixel counts) and every
-        finished group is copied to page-locked host memory on a side stream while the next one is evaluated."""
-        whole = self.pix_first == 0 and self.pix_last == self.npix
-        if self.variant != "gather" or not whole or chunks < 2 or self.nh == 0:
+        by ring band, so the gather kernel is launched over ``chunks`` groups of the engine's bands and every finished
+        group is copied to page-locked host memory on a side stream while the next one is evaluated.  ``out_h``: a
+        page-locked host tensor for the engine's pixel range (a ring-band shard writes its piece of the shared result
+        array); default: a fresh one from torch's caching host allocator."""
+        nloc = self.pix_last - self.pix_first
+        shape = (nloc,) if self.mode == PAINT else (nloc, 3)
+        if self.variant != "gather" or chunks < 2 or self.nh == 0 or self.bands[1] - self.bands[0] < 2:
             out = self.accumulate()
             self.pair_count()
-            return dv.to_host(out, True)
-        from .sharding import band_pixel_range, band_split
-        nb = self.lib.bf_shell_num_bands(self.nside)
-        groups = [g for g in band_split(self.nside, min(chunks, nb)) if g[1] > g[0]]
-        shape = (self.npix,) if self.mode == PAINT else (self.npix, 3)
+            if out_h is None:
+                return dv.to_host(out, True)
+            out_h.copy_(out.view(out_h.shape), non_blocking=True)
+            torch.cuda.current_stream(self.dev).synchronize()
+            return out_h.numpy()
+        from .sharding import band_pixel_range
+        lo0, hi0 = self.bands
+        k = min(chunks, hi0 - lo0)
+        ends = [band_pixel_range(self.nside, lo0, b)[1] for b in range(lo0, hi0 + 1)]  # last pixel + 1 of bands lo0 .. b - 1
+        cuts = [lo0] + [lo0 + int(np.searchsorted(ends, self.pix_first + nloc * i // k)) for i in range(1, k)] + [hi0]
+        groups = [(a, b) for a, b in zip(cuts[:-1], cuts[1:]) if b > a]  # near-equal pixel counts
         out_d = dv.empty(shape, dev=self.dev)
-        out_h = torch.empty(shape, dtype=torch.float64, pin_memory=True)
+        if out_h is None:
+            out_h = torch.empty(shape, dtype=torch.float64, pin_memory=True)
         main, side = torch.cuda.current_stream(self.dev), torch.cuda.Stream(device=self.dev)
         self.cnt.zero_()
         for lo, hi in groups:
             _lib.call("bf_shell_gather", self.nside, self.mode, C.byref(self.desc), C.byref(self.table.desc), lo, hi,
-                      dv.ptr(self.ws), dv.ptr(out_d), 0, 0, dv.ptr(self.cnt), dv.stream_ptr())
+                      dv.ptr(self.ws), dv.ptr(out_d), self.pix_first, 0, dv.ptr(self.cnt), dv.stream_ptr())
             a, b = band_pixel_range(self.nside, lo, hi)
+            a, b = a - self.pix_first, b - self.pix_first
             done = torch.cuda.Event()
             done.record(main)
             side.wait_event(done)

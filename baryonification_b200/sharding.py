@@ -350,9 +350,11 @@ class SharedHostArena:
         if rank == 0:
             os.unlink(name[0])
         if torch.cuda.is_available():
+            import ctypes as C
             t = torch.from_numpy(self.array)
-            rc = torch.cuda.cudart().cudaHostRegister(t.data_ptr(), t.numel() * t.element_size(), 0)
-            self.registered = int(rc) == 0
+            rc = int(_lib.load(require_cuda=True).bf_host_pin(C.c_void_p(t.data_ptr()), t.numel() * t.element_size())) \
+                if t.numel() else -1
+            self.registered = rc == 0
             self._tensor = t
 
     @property
@@ -363,7 +365,8 @@ class SharedHostArena:
 
     def close(self):
         if self.registered:
-            torch.cuda.cudart().cudaHostUnregister(self._tensor.data_ptr())
+            import ctypes as C
+            _lib.load().bf_host_unpin(C.c_void_p(self._tensor.data_ptr()))
             self.registered = False
 
     def __del__(self):
@@ -477,7 +480,7 @@ class ShardedShell:
         t["extras"] = full[nk + 3:].t().contiguous() if nx else None
         return t
 
-    def process_device(self, gather=False):
+    def process_device(self, gather=False, out_h=None):
         """Device part: returns (own slice [first, last) on the device -- or the whole map with ``gather=True`` --,
         (sum new, sum old) or None, ranges)."""
         import time
@@ -507,6 +510,14 @@ class ShardedShell:
             if eng.nentries is not None:
                 self._bin_hint = eng.nentries + eng.nentries // 16 + 1024
             t0 = self._tick("collapse_bin", t0, dev)
+            if out_h is not None and not self.baryonify:  # paint: finished band groups travel under the next group's kernel
+                eng.accumulate_to_host(out_h=out_h)
+                pairs = eng.cnt.clone()
+                if self.world > 1:
+                    dist.all_reduce(pairs, group=self.group)
+                self.npairs = int(pairs.item())
+                self._tick("pairs_d2h", t0, dev)
+                return None, None, ranges
             acc = eng.accumulate()
             pairs = eng.cnt.clone()
             if self.world > 1:
@@ -550,6 +561,18 @@ class ShardedShell:
 
     def process(self):
         import time
+        if not self.baryonify and torch.cuda.is_available():  # paint: read-back pipelined with the pair stage
+            _, ranges = self.plan()
+            arena = self._arena(ranges[-1][1])
+            a, b = ranges[self.rank]
+            if arena.registered:
+                self.process_device(gather=False, out_h=arena.tensor[a:b])
+                t0 = time.perf_counter()
+                if self.world > 1:
+                    dist.barrier(group=self.group)
+                self.timings["barrier"] = time.perf_counter() - t0
+                return arena.array
+            self._turn ^= 1  # (not page-locked: the plain path below takes the same arena)
         out, sums, ranges = self.process_device(gather=False)
         t0 = time.perf_counter()
         if sums is not None:
@@ -557,11 +580,14 @@ class ShardedShell:
                 "ERROR in pixel regridding, sum(new_map) [%0.14e] != sum(oldmap) [%0.14e]" % sums
         arena = self._arena(ranges[-1][1])
         a, b = ranges[self.rank]
+        t1 = time.perf_counter()
         arena.tensor[a:b].copy_(out, non_blocking=arena.registered)  # every rank: its band, its own PCIe link
         if out.is_cuda:
             torch.cuda.current_stream(out.device).synchronize()
+        t2 = time.perf_counter()
         if self.world > 1:
             dist.barrier(group=self.group)
+        self.timings["arena"], self.timings["d2h"], self.timings["barrier"] = t1 - t0, t2 - t1, time.perf_counter() - t2
         self.timings["d2h_barrier"] = time.perf_counter() - t0
         return arena.array
 

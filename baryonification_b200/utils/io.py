@@ -208,10 +208,35 @@ class ParticleSnapshot:
     def cosmology(self):
         return self.cosmo
 
-    def make_map(self, N_grid):
-        """Mass histogram on an ``N_grid``-per-side mesh (host numpy; not on the hot path)."""
+    def make_map(self, N_grid, device=None):
+        """Mass map on an ``N_grid``-per-side mesh: ``np.histogramdd(coords, bins=(linspace(0, L, N_grid + 1),) * D,
+        weights=M)[0]`` (utils/io.py:657-670) evaluated on the GPU by ``bf_make_map`` -- the same bins (the numpy edges
+        are uploaded and searched exactly) and the same per-cell summation order (particle order), hence the same bits.
+        ``device="host"`` runs numpy itself (no GPU needed: what the reference does)."""
         assert np.isnan(self.cat["M"]).sum() == 0, "If you want to make a map, provide a value for the particle mass"
         edges = np.linspace(0, self.L, N_grid + 1)
         names = ("x", "y") if self.is2D else ("x", "y", "z")
-        coords = np.stack([self.cat[k] for k in names], axis=1)
-        return np.histogramdd(coords, bins=(edges,) * len(names), weights=self.cat["M"])[0]
+        if device == "host":
+            coords = np.stack([self.cat[k] for k in names], axis=1)
+            return np.histogramdd(coords, bins=(edges,) * len(names), weights=self.cat["M"])[0]
+        import ctypes as C
+        import torch
+        from .. import _device as dv, _lib
+        from ..Runners.snapshot import BaryonifySnapshot
+        lib = _lib.load(require_cuda=True)
+        dev = dv.device(device)
+        dim, n = len(names), len(self.cat)
+        with torch.cuda.device(dev):
+            grid = dv.empty((int(N_grid),) * dim, dev=dev)
+            ws = torch.empty(max(lib.bf_make_map_ws_bytes(n), 256), dtype=torch.uint8, device=dev)
+            e_d = dv.to_dev(edges, dev=dev)
+            if BaryonifySnapshot._is_reference_layout(self.cat):
+                rec = dv.AsyncUpload(self.cat.view(np.float64).reshape(-1, 4), dev).result()
+                args = (None, None, None, None, dv.ptr(rec))
+            else:
+                cols = [dv.to_dev(self.cat[k], dev=dev, pinned=True) for k in names]
+                cols += [None] * (3 - dim) + [dv.to_dev(self.cat["M"], dev=dev, pinned=True)]
+                args = tuple(dv.ptr(c) for c in cols) + (None,)
+            _lib.call("bf_make_map", dim, n, *args, dv.ptr(e_d), int(N_grid), dv.ptr(grid), dv.ptr(ws), ws.numel(),
+                      dv.stream_ptr())
+            return dv.to_host(grid, True)

@@ -42,6 +42,12 @@ int bf_version(void);
 int bf_device_sm_count(int *sm_count_host);
 /* Kernel launches of this library since it was loaded (CUB's internal kernels not included). */
 unsigned long long bf_launch_count(void);
+/* Page-lock a caller's host array where it lies / undo it (cudaHostRegister / cudaHostUnregister with the runtime's error
+ * state left clean on failure).  bf_host_pin: 0 = registered now, 1 = the range is already page-locked (nothing to undo),
+ * BF_E_INVALID = not possible.  No counterpart in the reference (numpy arrays are pageable): plumbing of the runners'
+ * upload path, which registers inputs >= 64 MiB that are processed a second time (parameter sweeps). */
+int bf_host_pin(void *ptr, size_t bytes);
+int bf_host_unpin(void *ptr);
 /* Throughput probe: `blocks` CTAs of 256 threads, each thread runs 8 independent chains of `iters` fused multiply-adds
  * in fp64; out is [blocks * 256] doubles (scratch), *dfma_per_thread_host = 8 * iters.  Time it with events. */
 int bf_probe_fp64(int blocks, int iters, double *out, unsigned long long *dfma_per_thread_host, void *stream);
@@ -304,6 +310,18 @@ int bf_snap_pair_list(int dim, int64_t np, const double *x, const double *y, con
 int bf_snap_displace_records(int dim, int64_t np, const void *cat, double L, double a, const bf_snap_halos *h_host,
                              const bf_table *tab_host, int64_t ng, const void *ws, void *cat_out,
                              unsigned long long *npairs, void *stream);
+
+/* ---- ParticleSnapshot.make_map on the device (utils/io.py:622-670) ---- */
+/* np.histogramdd(coords, bins = (edges,) * dim, weights = M)[0] with edges = np.linspace(0, L, ngrid + 1) UPLOADED by the
+ * caller (device, [ngrid + 1]): bin = searchsorted(edges, x, 'right') - 1, samples on the last edge go to the last bin,
+ * samples outside [edges[0], edges[ngrid]] are dropped, and a cell's masses are added in particle order (np.bincount) --
+ * stable radix sort by cell + in-order run sums, no atomics: bit-identical to numpy and bit-reproducible.
+ * Give x, y, (z,) m or `records` ((M, x, y, z) float64, 16-byte aligned).  grid is [ngrid]^dim float64 (overwritten).
+ * Synchronises `stream` once (reads the ends of `edges`).  ngrid^dim < 2^32, np < 2^31. */
+size_t bf_make_map_ws_bytes(int64_t np);
+int bf_make_map(int dim, int64_t np, const double *x, const double *y, const double *z, const double *m,
+                const void *records, const double *edges, int64_t ngrid, double *grid, void *ws, size_t ws_bytes,
+                void *stream);
 
 /* ---- Delta P(k) summary (examples/10_Reproduce_Schneider_deltaPk.ipynb, cells 1, 12, 15) ---- */
 /* NGP mass assignment of (folded) positions: grid[ix][iy][iz] += 1 with ix = int((x % Lfold) / (Lfold / ngrid))

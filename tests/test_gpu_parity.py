@@ -244,6 +244,49 @@ def test_snapshot_dense_block_uses_several_queue_rounds(gpu):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("dim,n,ngrid", [(3, 300_000, 64), (2, 200_000, 256), (3, 5_000, 7)])
+def test_make_map_equals_numpy_histogramdd_bit_for_bit(gpu, dim, n, ngrid):
+    """ParticleSnapshot.make_map (utils/io.py:657-670) on the device: the bins of np.histogramdd (particles on cell
+    edges, on the box edges x = 0 and x = L, outside the box) and np.bincount's summation order -> the same bits, for
+    unequal masses too; bit-reproducible."""
+    from baryonification_b200 import synthetic as syn
+    rng = np.random.default_rng(100 + dim + ngrid)
+    L = 250.0
+    xyz = [rng.uniform(0.0, L, n) for _ in range(dim)]
+    edges = np.linspace(0, L, ngrid + 1)
+    for c in xyz:  # exact hits on interior edges, on both ends of the box, and strays outside it
+        c[:200] = rng.choice(edges, 200)
+        c[200:210] = L
+        c[210:220] = 0.0
+        c[220:230] = np.array([-1e-9, L + 1e-9, -5.0, 2 * L, np.nextafter(L, 0), np.nextafter(0, 1), np.nextafter(L, 2 * L),
+                               -0.0, L / 3, 2 * L / 3])
+        rng.shuffle(c)
+    M = rng.lognormal(0.0, 2.0, n)  # unequal masses: the summation order matters
+    snap = syn.ParticleSnapshot(x=xyz[0], y=xyz[1], z=xyz[2] if dim == 3 else None, M=M, L=L, redshift=0.0, cosmo=syn.COSMO)
+    want = np.histogramdd(np.stack(xyz, axis=1), bins=(edges,) * dim, weights=M)[0]
+    got = snap.make_map(ngrid)
+    assert got.shape == want.shape and got.dtype == want.dtype
+    assert np.array_equal(got, want)
+    assert np.array_equal(got, snap.make_map(ngrid, device="host"))
+    assert np.array_equal(got, snap.make_map(ngrid))
+    wide = np.zeros(n, dtype=snap.cat.dtype.descr + [("id", "i8")])  # not the 32-byte record: the column path
+    for k in snap.cat.dtype.names:
+        wide[k] = snap.cat[k]
+    snap.cat = wide
+    assert np.array_equal(snap.make_map(ngrid), want)
+
+
+@pytest.mark.gpu
+def test_make_map_empty_and_nan_mass(gpu):
+    from baryonification_b200 import synthetic as syn
+    snap = syn.ParticleSnapshot(x=np.zeros(0), y=np.zeros(0), z=np.zeros(0), M=np.zeros(0), L=10.0, redshift=0.0, cosmo=syn.COSMO)
+    assert np.array_equal(snap.make_map(8), np.zeros((8, 8, 8)))
+    bad = syn.ParticleSnapshot(x=np.ones(3), y=np.ones(3), z=np.ones(3), M=np.nan, L=10.0, redshift=0.0, cosmo=syn.COSMO)
+    with pytest.raises(AssertionError, match="provide a value for the particle mass"):
+        bad.make_map(8)
+
+
+@pytest.mark.gpu
 def test_repeated_large_input_is_page_locked_in_place(gpu):
     """A >= 64 MiB map is staged through page-locked memory the first time it is processed and page-locked where it lies
     from the second time on (parameter sweeps process the same map again and again): same bits either way, and the

@@ -73,3 +73,17 @@ def test_reference_healpix_regrid_kernel(bfg):
     got = np.zeros(npix)
     orc._lib().bfo_regrid_shell(nside, orig, np.ascontiguousarray(off), got)
     assert np.allclose(got, want, rtol=1e-13, atol=0)
+
+
+def test_make_map_host_form_equals_the_reference(bfg):
+    """utils/io.py:657-670 -- the repo's ParticleSnapshot.make_map(device="host") is the reference's numpy call."""
+    from baryonification_b200 import synthetic as syn
+    rng = np.random.default_rng(5)
+    for dim in (2, 3):
+        xyz = [rng.uniform(0, 100.0, 20_000) for _ in range(dim)]
+        xyz[0][:5] = [0.0, 100.0, 50.0, 25.0, 100.0]
+        M = rng.lognormal(0, 1, 20_000)
+        kw = dict(x=xyz[0], y=xyz[1], z=xyz[2] if dim == 3 else None, M=M, L=100.0, redshift=0.3, cosmo=syn.COSMO)
+        want = bfg.utils.io.ParticleSnapshot(**kw).make_map(16)
+        got = syn.ParticleSnapshot(**kw).make_map(16, device="host")
+        assert np.array_equal(got, want)
