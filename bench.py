@@ -45,7 +45,8 @@ B_GRID_PAIR = 48.0 # BaryonifyGrid 3-D: 16 * D bytes per pair
 B_GRID_CELL = 168.0
 # fp64 instructions per pair in the whole-strip loop of gather_kernel (counted in `cuobjdump -sass`: DADD/DMUL/DFMA/DSETP)
 FP64_PER_PAIR = {"shell": 39, "paint": 40}
-CPU_SAMPLE = 10_000  # halos of the seed-42 shuffle in the bounded CPU sample -- the SAME for cpu_baseline and the reference arm
+CPU_SAMPLE = 40_000  # halos of the seed-42 shuffle in the bounded CPU sample (~5 s on 16 threads) -- the SAME for
+                     # cpu_baseline and the reference arm (whose --steps 20 --warmup 5 run then takes ~2.5 minutes)
 
 
 def parse():
@@ -222,7 +223,7 @@ def cpu_shell_sample(cfg, args, nthreads, nsample):
     t0 = time.perf_counter()
     off = r.offsets()
     t_loop = time.perf_counter() - t0
-    p1 = min(npix, 4_000_000)
+    p1 = min(npix, 8_000_000)
     new_map = np.zeros(npix)
     t0 = time.perf_counter()
     orc._lib().bfo_regrid_shell_range(cfg["field"].NSIDE, 0, p1, np.ascontiguousarray(cfg["field"].map), off, new_map)
@@ -650,7 +651,7 @@ def run_grid3d(args, rank, local_rank, world):
     ms_step, ms_pairs, ms_rg, ms_pk = (float(v) for v in ms)
     npairs = int(pairs[0])
     S = state["S"]
-    e2e = None
+    e2e, n1 = None, {}
     if not args.no_e2e:
         del res, state
         torch.cuda.empty_cache()
@@ -663,6 +664,17 @@ def run_grid3d(args, rank, local_rank, world):
             if i >= 3:
                 ts.append(time.perf_counter() - t0)
         t_e2e = float(np.mean(ts))
+        if world > 1 and not args.no_n1_check:  # outside every timed region: this rank-0 slab vs ONE GPU, on rank 0
+            if rank == 0:
+                try:
+                    single = bf.BaryonifyGrid(cfg["catalog"], G, 20.0, cfg["model"], verbose=False, device=local_rank).process()
+                    a0, a1 = sh.index_split(n, world)[0]
+                    n1 = {"n1_equal": bool(np.array_equal(single[a0:a1].reshape(out.shape), out)),
+                          "n1_criterion": "bitwise, rank 0's row slab (cell owners + destination-gather re-binning)"}
+                    del single
+                except Exception as e:  # (a diagnostic outside the measurement: never lose the line over it)
+                    n1 = {"n1_equal": None, "n1_error": repr(e)[:200]}
+            barrier()
         e2e = {"value": npairs / t_e2e, "unit": "pairs/s", "ms": t_e2e * 1e3,
                "h2d_bytes_per_step": int(G.map.nbytes // world), "d2h_bytes_per_step": int(out.nbytes),
                "bytes_are": "per rank (row slab)" if world > 1 else "whole job",
@@ -676,7 +688,7 @@ def run_grid3d(args, rank, local_rank, world):
         out_j = {"metric": "halo-cell updates/sec", "value": npairs / (ms_step * 1e-3), "unit": "pairs/s",
                  "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
                  "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                 "config": {"workload": workload_name(args), "parallelism": f"row-slab x{world}", "pairs": npairs,
+                 "config": {**n1, "workload": workload_name(args), "parallelism": f"row-slab x{world}", "pairs": npairs,
                             "timed_region_repeats": reps,
                             "stages_ms_max_over_ranks": {"pair_stage": ms_pairs, "regrid": ms_rg, "delta_pk": ms_pk},
                             "mass_conservation_relerr": abs(float(sums[0]) / float(sums[1]) - 1.0),

@@ -598,6 +598,38 @@ def test_shell_regrid_gather_partial_sums_of_ring_band_shards_add_up(gpu, nside,
     assert np.mean(total == want) > 0.9
 
 
+@pytest.mark.parametrize("mode_name", ["paint", "baryonify"])
+def test_band_shard_pair_stage_with_pipelined_read_back(gpu, mode_name):
+    """The N-GPU paint path on one GPU: every ring-band shard evaluates its bands group by group and copies each finished
+    group into ITS piece of one page-locked host array (``accumulate_to_host(out_h=...)``); the pieces assemble the
+    whole-sphere accumulator bit for bit (pixel owners: no collective)."""
+    import torch
+    from baryonification_b200 import engine, host, sharding as sh, synthetic as syn
+    from baryonification_b200._ccl import default_mass_def
+    from baryonification_b200.tables import displacement_host_table, profile_host_table
+    nside = 128
+    cfg = syn.config_shell(nside=nside, nhalo=1500, zero_map=(mode_name == "paint"))
+    bary = mode_name == "baryonify"
+    model = cfg["model"] if bary else cfg["paint_model"]
+    mode = engine.BARYONIFY if bary else engine.PAINT
+    htab = displacement_host_table(model) if bary else profile_host_table(model, "2D")
+    s = host.shell_scalars(cfg["catalog"], cfg["catalog"].cosmo, default_mass_def(), cfg["epsilon_max"], model, bary)
+    whole = engine.ShellEngine(nside, mode, htab, s, gpu).upload().bin()
+    want = whole.accumulate().cpu().numpy()
+    npairs = whole.pair_count()
+    shape = want.shape
+    out_h = torch.empty(shape, dtype=torch.float64, pin_memory=True)
+    out_h.fill_(float("nan"))
+    total = 0
+    for lo, hi in sh.band_split(nside, 3):
+        eng = engine.ShellEngine(nside, mode, htab, s, gpu, bands=(lo, hi)).upload().bin()
+        a, b = eng.pix_first, eng.pix_last
+        eng.accumulate_to_host(chunks=4, out_h=out_h[a:b])
+        total += eng.npairs
+    assert total == npairs
+    assert np.array_equal(out_h.numpy(), want)
+
+
 def test_shell_regrid_gather_window_fallback_and_runner_default(gpu):
     import baryonification_b200 as bf
     from baryonification_b200 import synthetic as syn
