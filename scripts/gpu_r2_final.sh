@@ -5,7 +5,7 @@ mkdir -p gpurun_out
 O=gpurun_out
 nvidia-smi --query-gpu=name,memory.total --format=csv > $O/r2f_smi.txt; nproc >> $O/r2f_smi.txt
 timeout 1500 python -m pytest tests -m gpu -x -q --durations=10 > $O/r2f_pytest.log 2>&1; echo "pytest rc=$?"; tail -16 $O/r2f_pytest.log
-timeout 600 python bench.py --steps 10 --warmup 3 > $O/r2f_bench_shell_n1.json 2> $O/r2f_bench_shell_n1.err; echo "bench shell rc=$?"
+timeout 600 python bench.py --steps 20 --warmup 5 > $O/r2f_bench_shell_n1.json 2> $O/r2f_bench_shell_n1.err; echo "bench shell rc=$?"
 timeout 400 python bench.py --impl reference --steps 3 --warmup 1 > $O/r2f_bench_reference_arm.json 2> $O/r2f_bench_reference_arm.err; echo "ref arm rc=$?"
 for w in paint snapshot; do
   timeout 600 python bench.py --workload $w --steps 10 --warmup 3 > $O/r2f_bench_${w}_n1.json 2> $O/r2f_bench_${w}_n1.err; echo "bench $w rc=$?"
