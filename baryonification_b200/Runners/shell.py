@@ -199,7 +199,10 @@ class BaryonifyShell(DefaultRunner):
         nside = self.LightconeShell.NSIDE
         _, edges = engine.band_groups(nside, self.PIPELINE_GROUPS)
         box = {}
-        self._after_host = lambda: box.setdefault("up", dv.ChunkedUpload(orig, dev, edges))
+        # a pageable map starts its way (host memcpy into page-locked memory) as soon as the host set-up has released the
+        # cores; a map that is page-locked in place has nothing to prepare and starts after the binning stage, whose small
+        # uploads would otherwise stand behind it on the GPU's one host-to-device copy engine
+        self._after_host = lambda: None if dv.pinned_already(orig) else box.setdefault("up", dv.ChunkedUpload(orig, dev, edges))
         try:
             eng = self._engine(dev, engine.BARYONIFY)
         finally:
@@ -230,7 +233,7 @@ class BaryonifyShell(DefaultRunner):
             # the 8 B/pixel map travels (pageable -> pinned -> HBM) while halos are binned and evaluated on the GPU; it
             # starts after the host set-up, which wants all host cores for itself
             box = {}
-            self._after_host = lambda: box.setdefault("up", dv.AsyncUpload(orig, dev))
+            self._after_host = lambda: None if dv.pinned_already(orig) else box.setdefault("up", dv.AsyncUpload(orig, dev))
             try:
                 off = self.offsets_device(dev)
             finally:

@@ -133,6 +133,17 @@ def pin_in_place(a):
     return True
 
 
+def pinned_already(a):
+    """True when ``a`` lies in memory that ``pin_in_place`` has page-locked before (no registration is attempted): an
+    upload of it needs no host-side preparation, so it need not start early."""
+    if not isinstance(a, np.ndarray) or not a.flags.c_contiguous:
+        return False
+    lo = a.__array_interface__["data"][0]
+    if _pin_seen.get((lo, a.nbytes)) == "pinned":
+        return True
+    return any(p0 <= lo and lo + a.nbytes <= p0 + n0 for (p0, n0) in list(_pin_done))
+
+
 def _as_tensor(a):
     import warnings
     with warnings.catch_warnings():  # (a read-only input is only ever read)

@@ -500,13 +500,20 @@ class ShardedShell:
             t = self.scalars_device(dev, (lo, hi))
             t0 = self._tick("host_setup_allgather", t0, dev)
             up = None
-            if self.baryonify:  # this rank's slice of the map travels under the binning and the pair kernel (after the
-                # host set-up, not beside it: the staging copy would compete with it for the host cores)
+
+            def start_upload():  # this rank's slice of the map travels under the pair kernel
                 orig = np.ascontiguousarray(r.LightconeShell.map, dtype=np.float64).reshape(-1)
-                up = dv.ChunkedUpload(orig[first:last], dev, np.linspace(0, last - first, 9).astype(np.int64))
+                return dv.ChunkedUpload(orig[first:last], dev, np.linspace(0, last - first, 9).astype(np.int64))
+
+            early = self.baryonify and not dv.pinned_already(
+                np.ascontiguousarray(r.LightconeShell.map, dtype=np.float64).reshape(-1)[first:last])
+            if early:  # pageable: the staging memcpy starts now (after the host set-up, which wanted the cores); a slice
+                up = start_upload()  # that is page-locked in place starts after the binning stage's small uploads
             eng = engine.ShellEngine(nside, mode, htab, None, dev, variant="gather", bands=(lo, hi))
             eng.max_entries = getattr(self, "_bin_hint", 0)  # (a repeated call skips the counting pass of the binning)
             eng.upload_device(t).bin()
+            if self.baryonify and up is None:
+                up = start_upload()
             if eng.nentries is not None:
                 self._bin_hint = eng.nentries + eng.nentries // 16 + 1024
             t0 = self._tick("collapse_bin", t0, dev)
