@@ -567,7 +567,7 @@ def cpu_snapshot_record(cfg, args):
     from baryonification_b200 import synthetic as syn
     cat = cfg["field"].cat
     cores = os.cpu_count() or 1
-    m = min(2_000_000, cat.size)  # bounded sample: the first 2e6 particles against the full halo catalogue
+    m = min(20_000_000, cat.size)  # bounded sample (~13 s): the first 2e7 particles against the full halo catalogue
     sub = syn.ParticleSnapshot(x=cat["x"][:m], y=cat["y"][:m], z=cat["z"][:m], M=1.0, L=cfg["field"].L,
                                redshift=cfg["field"].redshift, cosmo=cfg["field"].cosmo)
     r = orc.BaryonifySnapshot(cfg["catalog"], sub, cfg["epsilon_max"], cfg["model"], nthreads=cores)
