@@ -473,10 +473,10 @@ class ShellEngine:
             out_h.copy_(out.view(out_h.shape), non_blocking=True)
             torch.cuda.current_stream(self.dev).synchronize()
             return out_h.numpy()
-        from .sharding import band_pixel_range
+        from .sharding import band_ends, band_pixel_range
         lo0, hi0 = self.bands
         k = min(chunks, hi0 - lo0)
-        ends = [band_pixel_range(self.nside, lo0, b)[1] for b in range(lo0, hi0 + 1)]  # last pixel + 1 of bands lo0 .. b - 1
+        ends = band_ends(self.nside)[lo0:hi0 + 1]  # first pixel after bands .. b - 1, for b = lo0 .. hi0
         cuts = [lo0] + [lo0 + int(np.searchsorted(ends, self.pix_first + nloc * i // k)) for i in range(1, k)] + [hi0]
         groups = [(a, b) for a, b in zip(cuts[:-1], cuts[1:]) if b > a]  # near-equal pixel counts
         out_d = dv.empty(shape, dev=self.dev)

@@ -38,6 +38,22 @@ def band_pixel_range(nside, band_lo, band_hi):
     return f.value, l.value
 
 
+_band_ends_cache = {}
+
+
+def band_ends(nside):
+    """ends[b] = first pixel after ring bands 0 .. b - 1 (int64 array of bf_shell_num_bands + 1 entries; cached per NSIDE:
+    a few thousand library calls, milliseconds that every ``process()`` would otherwise pay again)."""
+    nside = int(nside)
+    ends = _band_ends_cache.get(nside)
+    if ends is None:
+        nb = int(_lib.load().bf_shell_num_bands(nside))
+        ends = np.array([band_pixel_range(nside, 0, b)[1] for b in range(nb + 1)], dtype=np.int64)
+        ends.flags.writeable = False
+        _band_ends_cache[nside] = ends
+    return ends
+
+
 def band_split(nside, world):
     """``world`` contiguous ring-band ranges [lo, hi) with (nearly) equal pixel counts, covering the sphere."""
     lib = _lib.load()
@@ -45,7 +61,7 @@ def band_split(nside, world):
     if world > nb:
         raise ValueError(f"cannot split {nb} ring bands of NSIDE {nside} over {world} ranks")
     npix = 12 * nside * nside
-    ends = np.array([band_pixel_range(nside, 0, b)[1] for b in range(nb + 1)], dtype=np.int64)
+    ends = band_ends(nside)
     cuts = [0]
     for r in range(1, world):
         c = int(np.searchsorted(ends, npix * r / world))
