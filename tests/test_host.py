@@ -174,3 +174,71 @@ def test_runners_are_picklable_like_the_reference_ones():
         r2 = pickle.loads(pickle.dumps(r))
         assert type(r2) is type(r) and r2.epsilon_max == r.epsilon_max
         assert np.array_equal(r2.model.raw_input_r_range, r.model.raw_input_r_range)
+
+
+def test_pin_in_place_state_machine(monkeypatch):
+    """_device.pin_in_place without a GPU (the library calls are stubbed): first sight stages, second sight registers the
+    range that is used, slices of a registered range need nothing, a failed or already page-locked range is remembered,
+    and the registration / the sighting end with the array."""
+    import gc
+    import torch
+    from baryonification_b200 import _device as dv
+
+    class FakeLib:
+        def __init__(self):
+            self.pinned, self.rc = {}, 0
+
+        def bf_host_pin(self, ptr, nbytes):
+            if self.rc == 0:
+                self.pinned[ptr.value] = nbytes
+            return self.rc
+
+        def bf_host_unpin(self, ptr):
+            self.pinned.pop(ptr.value)
+            return 0
+
+    fake = FakeLib()
+    monkeypatch.setattr(torch.cuda, "is_available", lambda: True)
+    monkeypatch.setattr(dv._lib, "load", lambda require_cuda=False: fake)
+    monkeypatch.setattr(dv, "_PIN_MIN_BYTES", 1 << 10)
+    monkeypatch.delenv("BF_PIN_INPUTS", raising=False)
+    n0, s0 = len(dv._pin_done), len(dv._pin_seen)
+
+    a = np.zeros(4096)
+    assert not dv.pin_in_place(a[:10])                      # too small
+    assert not dv.pin_in_place(a[::2])                      # not contiguous
+    assert not dv.pin_in_place(a) and not fake.pinned       # first sight: staged
+    assert not dv.pinned_already(a)
+    assert dv.pin_in_place(a.reshape(64, 64))               # second sight (another view of the same range): registered
+    assert fake.pinned == {a.ctypes.data: a.nbytes} and dv.pinned_already(a)
+    assert dv.pin_in_place(a[1000:3000]) and len(fake.pinned) == 1   # a slice of a registered range
+    del a
+    gc.collect()
+    assert not fake.pinned and len(dv._pin_done) == n0 and len(dv._pin_seen) == s0   # ended with the array
+
+    b = np.zeros(4096)
+    sl = b[512:2048]                                        # a rank's slice of a map: only that range is registered
+    assert not dv.pin_in_place(sl) and dv.pin_in_place(b[512:2048])
+    assert fake.pinned == {b.ctypes.data + 512 * 8: 1536 * 8}
+    del b, sl
+    gc.collect()
+    assert not fake.pinned and len(dv._pin_seen) == s0
+
+    c = np.zeros(4096)
+    fake.rc = 1                                             # already page-locked by its owner: usable, nothing to undo
+    assert not dv.pin_in_place(c) and dv.pin_in_place(c) and dv.pin_in_place(c) and dv.pinned_already(c)
+    assert not fake.pinned
+    d = np.zeros(4096)
+    fake.rc = -1                                            # cannot be registered: remembered, staged from then on
+    assert not dv.pin_in_place(d) and not dv.pin_in_place(d) and not dv.pin_in_place(d)
+    fake.rc = 0
+    assert not dv.pin_in_place(d) and not fake.pinned
+    monkeypatch.setenv("BF_PIN_INPUTS", "1")                # register at first sight
+    e = np.zeros(4096)
+    assert dv.pin_in_place(e) and len(fake.pinned) == 1
+    monkeypatch.setenv("BF_PIN_INPUTS", "0")                # off
+    f = np.zeros(4096)
+    assert not dv.pin_in_place(f) and not dv.pin_in_place(f)
+    del c, d, e, f
+    gc.collect()
+    assert not fake.pinned and len(dv._pin_done) == n0 and len(dv._pin_seen) == s0

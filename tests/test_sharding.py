@@ -334,3 +334,41 @@ def test_fixed_margins_need_bands_longer_than_the_margin():
     assert sh.fixed_margins_ok(ranges, sh.margin_pixels(4096))       # the benchmark partition takes the fast path
     small = [sh.band_pixel_range(16, *b) for b in sh.band_split(16, 2)]
     assert not sh.fixed_margins_ok(small, sh.margin_pixels(16))      # small spheres: the general exchange
+
+
+# ------------------------------------------------------------------ split host set-up of the shell runners
+def _w_split_setup(rank, world, nside, nhalo, baryonify):
+    import baryonification_b200 as bf
+    from baryonification_b200 import host
+    from baryonification_b200._ccl import default_mass_def
+    cfg = syn.config_shell(nside=nside, nhalo=nhalo, zero_map=not baryonify)
+    model = cfg["model"] if baryonify else cfg["paint_model"]
+    cls = bf.BaryonifyShell if baryonify else bf.PaintProfilesShell
+    runner = cls(cfg["catalog"], cfg["field"], cfg["epsilon_max"], model, verbose=False)
+    shard = sh.ShardedShell(runner)
+    bands, _ = shard.plan()
+    got = shard.scalars_device(torch.device("cpu"), bands[rank])  # 1/N of the host work + one all-gather + band mask
+    s = host.shell_scalars(cfg["catalog"], cfg["catalog"].cosmo, default_mass_def(), cfg["epsilon_max"], model, baryonify)
+    keep = sh.halos_touching_bands(s["vec"][:, 2], s["radius"], nside, *bands[rank])
+    # the device-side mask may keep a few more halos than the host form, never fewer, and always in catalogue order
+    full_idx = np.flatnonzero(np.isin(s["lon"], got["lon"].numpy()) & np.isin(s["lat"], got["lat"].numpy()))
+    assert got["a"].numel() >= int(keep.sum())
+    for k in ("a", "D", "radius", "z_in", "M_in", "lon", "lat", "cut", "lnr_shift"):
+        g = got[k].numpy()
+        assert g.ndim == 1 and got[k].is_contiguous()
+        sel = s[k][keep]
+        pos = np.searchsorted(full_idx, np.flatnonzero(keep))  # the kept halos inside the (super)set this rank holds
+        assert np.array_equal(g[pos], sel), k  # bit-identical to the one-process set-up
+    assert got["vec"].shape == (got["a"].numel(), 3) and got["vec"].is_contiguous()
+    pos = np.searchsorted(full_idx, np.flatnonzero(keep))
+    assert np.array_equal(got["vec"].numpy()[pos], s["vec"][keep])
+    assert np.all(np.diff(full_idx) > 0)
+    assert got["extras"] is None
+
+
+@pytest.mark.parametrize("world,nside,nhalo,baryonify", [(2, 32, 301, True), (3, 16, 200, False), (3, 8, 2, True)])
+def test_split_host_setup_all_gathers_the_catalogue_in_order(world, nside, nhalo, baryonify):
+    """ShardedShell.scalars_device: every rank prepares 1/N of the halos (uneven pieces, pieces of zero halos), one
+    all-gather, band mask -- each rank ends up with the one-process per-halo scalars of (at least) the halos that can
+    touch its bands, bit for bit and in catalogue order."""
+    _run(_w_split_setup, world, nside, nhalo, baryonify)
