@@ -83,12 +83,16 @@ class _RecordPipeline:
             for q in self.queued:
                 q.set()
 
-    def run(self, kernel):
-        """kernel(rec_chunk, out_chunk, stream) per chunk on the current stream; returns the host result array."""
+    def run(self, kernel, out=None):
+        """kernel(rec_chunk, out_chunk, stream) per chunk on the current stream; returns the host result array.
+        ``out``: a page-locked [n, 4] float64 host tensor to receive it (a rank's piece of a result array the ranks of a
+        box share); default: a fresh one from torch's caching host allocator."""
         n = self.rec.shape[0]
         cur = torch.cuda.current_stream(self.dev)
         d_out = torch.empty((n, 4), dtype=torch.float64, device=self.dev)
-        out = torch.empty((n, 4), dtype=torch.float64, pin_memory=True)
+        if out is None:
+            out = torch.empty((n, 4), dtype=torch.float64, pin_memory=True)
+        assert tuple(out.shape) == (n, 4) and out.dtype == torch.float64 and out.is_contiguous()
         done = torch.cuda.Event()
         self.consuming.set()
         for i, (a, b) in enumerate(self.bounds):
@@ -220,7 +224,9 @@ class BaryonifySnapshot(DefaultRunnerSnapshot):
             self.npairs = n
             return np.sort(pairs[:n].cpu().numpy().view(np.uint64))
 
-    def process(self):
+    def process(self, _out=None):
+        """``_out`` (internal, ``sharding.ShardedSnapshot``): page-locked [n, 4] float64 host tensor that receives the
+        displaced (M, x, y, z) records instead of a fresh array; only honoured for the reference's record layout."""
         dev = dv.device(self.device)
         S = self.ParticleSnapshot
         with torch.cuda.device(dev):
@@ -240,7 +246,7 @@ class BaryonifySnapshot(DefaultRunnerSnapshot):
                     _lib.call("bf_snap_displace_records", dim, rec.shape[0], dv.ptr(rec), st["L"], float(s["a"]),
                               C.byref(st["desc"]), C.byref(st["table"].desc), st["ng"], dv.ptr(st["ws"]),
                               dv.ptr(rec_out), dv.ptr(cnt), C.c_void_p(stream.cuda_stream))
-                new_cat = pipe.run(displace).reshape(-1).view(cat.dtype).reshape(cat.shape)
+                new_cat = pipe.run(displace, out=_out).reshape(-1).view(cat.dtype).reshape(cat.shape)
             else:  # any other record layout: field by field
                 names = ("x", "y", "z")[:dim]
                 xin = [dv.to_dev(cat[k], dev=dev, pinned=True) for k in names]

@@ -372,6 +372,12 @@ class SharedHostArena:
                 if t.numel() else -1
             self.registered = rc == 0
             self._tensor = t
+        self.all_registered = self.registered  # page-locked on EVERY rank: what collective decisions must be based on
+        if world > 1:
+            flag = torch.tensor([1 if self.registered else 0], dtype=torch.int32,
+                                device="cuda" if dist.get_backend(group) == "nccl" else "cpu")
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+            self.all_registered = bool(flag.item())
 
     @property
     def tensor(self):
@@ -588,7 +594,7 @@ class ShardedShell:
             _, ranges = self.plan()
             arena = self._arena(ranges[-1][1])
             a, b = ranges[self.rank]
-            if arena.registered:
+            if arena.all_registered:
                 self.process_device(gather=False, out_h=arena.tensor[a:b])
                 t0 = time.perf_counter()
                 if self.world > 1:
@@ -617,16 +623,28 @@ class ShardedShell:
 
 class ShardedSnapshot:
     """Index-sharded BaryonifySnapshot: every rank displaces a contiguous slice of the particle array against the
-    full (replicated) halo grid; rank slices are gathered in input order.  No collective on the data path."""
+    full (replicated) halo grid.  No collective on the data path.  ``process()`` returns the whole displaced array on
+    every rank: for the reference's (M, x, y, z) record layout as a view of a host array all ranks of the box share
+    (``SharedHostArena``; every rank's GPU writes ITS slice over its own PCIe link, two arenas alternate so a result
+    stays valid until the second-next call), for any other layout by an object all-gather."""
 
     def __init__(self, runner, group=None, device=None):
         self.runner, self.group, self.device = runner, group, device
         self.rank, self.world = _world(group)
         self.npairs = None
+        self._arenas, self._turn = [None, None], 0
         claim_host_threads()
+
+    def _arena(self, n):
+        self._turn ^= 1
+        ar = self._arenas[self._turn]
+        if ar is None or ar.n != n:
+            ar = self._arenas[self._turn] = SharedHostArena(n, self.group)
+        return ar
 
     def process(self, gather=True):
         import copy
+        from .Runners.snapshot import BaryonifySnapshot
         r = self.runner
         cat = r.ParticleSnapshot.cat
         ranges = index_split(len(cat), self.world)
@@ -635,11 +653,23 @@ class ShardedSnapshot:
         part.cat = cat[a:b]
         local = type(r)(r.HaloNDCatalog, part, r.epsilon_max, r.model, r.mass_def, verbose=False,
                         device=self.device)
-        out = local.process()
+        shared = None
+        if gather and torch.cuda.is_available() and BaryonifySnapshot._is_reference_layout(cat) and len(cat) > 0:
+            arena = self._arena(4 * len(cat))
+            if arena.all_registered:
+                shared = arena
+            else:
+                self._turn ^= 1
+        if shared is not None:
+            local.process(_out=shared.tensor.view(-1, 4)[a:b])
+        else:
+            out = local.process()
         pairs = torch.tensor([local.npairs], dtype=torch.int64,
                              device="cuda" if dist.get_backend(self.group) == "nccl" else "cpu")
-        dist.all_reduce(pairs, group=self.group)
+        dist.all_reduce(pairs, group=self.group)  # (also: every rank's slice has arrived in the shared array)
         self.npairs = int(pairs.item())
+        if shared is not None:
+            return np.asarray(shared.array).view(cat.dtype).reshape(cat.shape)
         if not gather:
             return out
         parts = [None] * self.world
