@@ -24,12 +24,15 @@ class PowerSpectrumGrid:
         self.npairs = None
 
     def _setup(self, factor):
-        """kbins / fftfreq constants exactly as notebook cell 12 writes them (host numpy)."""
-        L = self.Lbox / factor
+        """(fold length, fftfreq scale, kbins[0], kbins[1] - kbins[0]).  The k bins are those of notebook cell 12, which
+        computes them ONCE for the whole box (``Lbox = Snap.L``); the ``for factor`` loop of cells 15-21 only folds the
+        positions into ``Snap.L / factor`` and reports ``k_cen * factor`` -- so the binning constants do not depend on
+        ``factor`` (pinned against the notebook's own code: tests/golden/make_golden_pk.py)."""
+        L = self.Lbox
         kbins = np.linspace(2 * np.pi / L, 2 * np.pi / L * self.Ngrd / 2, self.Nk + 1)
         d = 1 / (2 * np.pi / L) / self.Ngrd
         val = 1.0 / (self.Ngrd * d)  # np.fft.fftfreq(n, d): results * val
-        return L, float(val), float(kbins[0]), float(kbins[1] - kbins[0])
+        return self.Lbox / factor, float(val), float(kbins[0]), float(kbins[1] - kbins[0])
 
     def upload(self, particles, dev=None):
         """Host particles -> a device form ``density`` accepts, so that several folding factors read one upload:

@@ -1,7 +1,9 @@
 """oracle/pk.py -- TEST INFRASTRUCTURE ONLY.  CPU restatement of the Delta P(k) recipe of the reference's notebook
-examples/10_Reproduce_Schneider_deltaPk.ipynb (cell 1: numba_histogram3d; cell 12: k bins; cells 15-21: folding,
-fftn, bincount), statement by statement in numpy.  The notebook is the only place the reference has this code, and
-it ships no expected numbers, so this restatement is PARITY UNPINNED beyond being a line-by-line copy of the recipe.
+examples/10_Reproduce_Schneider_deltaPk.ipynb (cell 1: numba_histogram3d; cell 12: k bins, computed once for the whole
+box; cells 15-21: folding, fftn, bincount, k_cen * factor), statement by statement in numpy.  The notebook is the only
+place the reference has this code.  PINNED: tests/golden/make_golden_pk.py executes the notebook's own cells verbatim
+on seeded particle sets (tests/golden/pk_notebook.npz); tests/test_oracle_pk.py holds this restatement to those outputs
+bit for bit (histograms, mode counts, P(k), k centres) and re-runs the notebook code live when /root/reference is there.
 """
 import numpy as np
 
@@ -28,8 +30,8 @@ def k_setup(Ngrd, Nk, Lbox):  # cell 12
 
 
 def power(points, Ngrd, Nk, Lsnap, factor=1):  # cells 15-21, one particle set
+    kinds, kmsk, k_c, k_cen = k_setup(Ngrd, Nk, Lsnap)  # cell 12: the bins of the WHOLE box, whatever the folding factor
     Lbox = Lsnap / factor
-    kinds, kmsk, k_c, k_cen = k_setup(Ngrd, Nk, Lbox)
     Map = histogram3d(points % Lbox, bins=Ngrd, min_vals=0.0, max_vals=Lbox)
     FFT = np.fft.fftn(Map)
     FFT = (np.conjugate(FFT) * FFT).real.flatten()

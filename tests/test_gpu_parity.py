@@ -918,6 +918,31 @@ def test_delta_pk_matches_notebook_recipe(gpu, ngrd, nk, factor):
     assert np.array_equal(P, P2) and np.array_equal(k, k2)  # deterministic reduction: bit-reproducible
 
 
+def test_delta_pk_matches_the_notebooks_own_code(gpu):
+    """Against tests/golden/pk_notebook.npz -- outputs of the code cells of
+    examples/10_Reproduce_Schneider_deltaPk.ipynb executed verbatim (tests/golden/make_golden_pk.py): NGP counts and mode
+    counts bit-exact, the reported k centres (k_cen * factor, bins of the whole box) to 1e-13, P(k) to 1e-11."""
+    import importlib.util
+    import os
+    from baryonification_b200.pk import PowerSpectrumGrid
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    spec = importlib.util.spec_from_file_location("make_golden_pk", os.path.join(here, "make_golden_pk.py"))
+    mg = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mg)
+    g = np.load(os.path.join(here, "pk_notebook.npz"))
+    for name, seed, n, Ngrd, Nk, L, f in mg.CASES:
+        pts = mg.particles(seed, n, L)
+        ps = PowerSpectrumGrid(Ngrd, L, Nk)
+        grid = ps.density(pts, f)
+        k, P, nm = ps.power(grid, f)
+        assert np.array_equal(grid.cpu().numpy(), g[name + ".Map"].astype(np.float64)), name
+        kc = g[name + ".k_c"]
+        assert np.array_equal(nm, kc.astype(np.float64)), name
+        ok = kc > 0
+        assert np.allclose(k[ok], (g[name + ".k_cen"] * f)[ok], rtol=1e-13, atol=0), name
+        assert np.allclose(P[ok], g[name + ".Pk"][ok], rtol=1e-11, atol=0), name
+
+
 @pytest.mark.parametrize("ngrd,nk,parts", [(32, 12, 2), (27, 9, 4), (20, 7, 8)])
 def test_delta_pk_piecewise_binning_adds_up(gpu, ngrd, nk, parts):
     """bf_pk_bin_part over y-ranges of the spectrum (the pieces the slab-decomposed transform leaves on the ranks):
