@@ -23,8 +23,7 @@ res = {}
 def timed(fn, n=3):
     """(result, fastest wall time).  When `fn` is a bound Runner method, the Runner's `timings` are left as those of the
     FASTEST call: `gpu_process_ms` and `stages_ms` of one line then describe the same call (round 1 printed the minimum
-    next to the stage times of whichever call came last -- 504 vs 3757 ms at 1024^3, where the last call had to grow the
-    page-locked result buffers again)."""
+    next to the stage times of whichever call came last -- 504 vs 3757 ms at 1024^3)."""
     fn()
     ts, best = [], None
     runner = getattr(fn, "__self__", None)
