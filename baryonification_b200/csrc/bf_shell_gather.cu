@@ -134,22 +134,23 @@ __device__ __forceinline__ void gather_pairs(const gather_smem &sm, const int c[
         dx[u] = v[0] - q0.x; dy[u] = v[1] - q0.y; dz[u] = v[2] - q1.x;
         d2[u] = fma(dz[u], dz[u], fma(dy[u], dy[u], dx[u] * dx[u]));
         x[u] = fma(0.5, gather_log(logtab, d2[u]), q1.y);
-        // Table cell: uniform-grid guess, accepted when 0 <= tt < 1 - 2^-50, which PROVES g[k] <= x < g[k+1] (tt >= 0 iff
+        // Table cell: uniform-grid guess, accepted when 0 <= tt < 1 - 2^-21, which PROVES g[k] <= x < g[k+1] (tt >= 0 iff
         // x >= g[k]; x >= g[k+1] would give tt >= 1 - 4 ulp) and with it that x lies inside the table.  For tt >= 0 the
         // order of doubles is the order of their bit patterns; negative tt and NaN have larger patterns, so one
-        // unsigned compare decides.  Everything else -- rounding at a node, a non-uniform axis, x == glast, x outside
-        // the table (fill_value NaN) -- takes the exact route.
+        // unsigned compare of the HIGH WORDS decides (the 5e-7 of the pairs with 1 - 2^-21 <= tt < 1 take the exact
+        // route needlessly and get the same cell).  Everything else -- rounding at a node, a non-uniform axis,
+        // x == glast, x outside the table (fill_value NaN) -- takes the exact route.
         k[u] = (int)((x[u] - ax.g0) * ax.inv_dx);
         k[u] = max(0, min(k[u], ax.nr - 2));
         const double2 gi = gi_s[k[u]];
         tt[u] = (x[u] - gi.x) * gi.y;
         inr[u] = true;
-        fast = fast && (u64)__double_as_longlong(tt[u]) < 0x3feffffffffffff8ull;  // (bits of 1 - 2^-50)
+        fast = fast && (unsigned)__double2hiint(tt[u]) < 0x3fefffffu;  // (high word of 1 - 2^-21: one 32-bit compare)
     }
     if (!fast) {
 #pragma unroll
         for (int u = 0; u < NP; ++u)
-            if ((u64)__double_as_longlong(tt[u]) >= 0x3feffffffffffff8ull) {
+            if ((unsigned)__double2hiint(tt[u]) >= 0x3fefffffu) {
                 inr[u] = x[u] >= ax.g0 && x[u] <= ax.glast;
                 if (inr[u]) {
                     k[u] = bf_find_cell(ax, x[u]);
