@@ -80,15 +80,20 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def measured_traffic(kernel, source):
+def measured_traffic(kernel, source, info=None):
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of `kernel`, from profiles/traffic.json (written by
     scripts/ncu_traffic.py from an `ncu --set full` capture) -- only while the kernel's source file still has the
-    content it was profiled at; None (null) when the capture is stale or absent."""
+    content it was profiled at; None (null) when the capture is stale or absent.  `info` (a dict) receives what the last
+    capture said and which source it belongs to, so that a stale value is still visible -- as a stale value."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     try:
         rec = json.load(open(p))[kernel]
         sha = hashlib.sha256(open(os.path.join(ROOT, "baryonification_b200", "csrc", source), "rb").read()).hexdigest()[:16]
-        return float(rec["bytes"]) if rec.get("src_sha16") == sha else None
+        fresh = rec.get("src_sha16") == sha
+        if info is not None:
+            info.update(bytes=float(rec["bytes"]), captured_at_src_sha16=rec.get("src_sha16"), current_src_sha16=sha,
+                        matches_current_source=fresh)
+        return float(rec["bytes"]) if fresh else None
     except Exception:
         return None
 
@@ -405,7 +410,8 @@ def run_shell(args, rank, local_rank, world):
         kname = "gather_kernel<%d>" % (1 if baryonify else 0) if args.variant == "gather" else "shell_atomic_kernel"
         alg_bytes = npairs / world * B_PAIR[args.workload]  # per launch (per rank)
         ach = alg_bytes / (ms_acc * 1e-3) / 1e9
-        traffic = measured_traffic(kname, "bf_shell_gather.cu") if (world == 1 and nside == 4096 and args.nhalo == 1_000_000) else None
+        tinfo = {}
+        traffic = measured_traffic(kname, "bf_shell_gather.cu", tinfo) if (world == 1 and nside == 4096 and args.nhalo == 1_000_000) else None
         fp64_ach = npairs / world * FP64_PER_PAIR[args.workload] / (ms_acc * 1e-3) / 1e9
         res = {
             "metric": "halo-pixel updates/sec", "value": npairs / (ms_step * 1e-3), "unit": "pairs/s",
@@ -428,6 +434,7 @@ def run_shell(args, rank, local_rank, world):
                          "traffic": traffic,
                          "traffic_unit": "bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum; null = no capture "
                                          "of the current kernel source, see profiles/traffic.json)",
+                         "traffic_last_capture": tinfo or None,
                          "dram": None if traffic is None else {"gbs": traffic / (ms_acc * 1e-3) / 1e9,
                                                                 "frac": traffic / (ms_acc * 1e-3) / 1e9 / peak},
                          "fp64": {"instr_per_pair": FP64_PER_PAIR[args.workload], "achieved_ginstr_s": fp64_ach,
@@ -538,7 +545,8 @@ def run_snapshot(args, rank, local_rank, world):
         alg = (cat.size * B_PARTICLE + npairs * B_SNAP_PAIR) / world
         kname = "snap_gather_kernel<3,1>" if os.environ.get("BF_SNAP_CHUNKED") else "snap_stream_kernel<3>"
         ach = alg / (ms_k * 1e-3) / 1e9
-        traffic = measured_traffic(kname, "bf_snapshot.cu") if (world == 1 and args.npart_side == 512) else None
+        tinfo = {}
+        traffic = measured_traffic(kname, "bf_snapshot.cu", tinfo) if (world == 1 and args.npart_side == 512) else None
         out_j = {"metric": "particle updates/sec", "value": cat.size / (ms_step * 1e-3), "unit": "particles/s",
                  "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
                  "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -547,7 +555,7 @@ def run_snapshot(args, rank, local_rank, world):
                                  "l2": "particle records (64 B/particle in+out) far exceed the 126 MB L2"}, **n1),
                  "roofline": {"bound": "hbm", "kernel": kname, "achieved": ach, "peak": peak,
                               "unit": "GB/s", "frac": ach / peak, "peak_source": peak_src, "kernel_ms": ms_k,
-                              "traffic": traffic,
+                              "traffic": traffic, "traffic_last_capture": tinfo or None,
                               "dram": None if traffic is None else {"gbs": traffic / (ms_k * 1e-3) / 1e9,
                                                                      "frac": traffic / (ms_k * 1e-3) / 1e9 / peak},
                               "compulsory_bytes": cat.size / world * 64.0,
