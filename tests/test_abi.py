@@ -71,3 +71,16 @@ def test_product_never_imports_the_oracle():
     for py in glob.glob(os.path.join(ROOT, "baryonification_b200", "**", "*.py"), recursive=True):
         src = open(py).read()
         assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), py
+
+
+def test_every_exported_entry_point_is_documented_in_integration_md():
+    """INTEGRATION.md maps each C entry point to the reference lines it replaces (or says that it has no counterpart)."""
+    import os
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "baryonification_b200.h")).read()
+    doc = open(os.path.join(root, "INTEGRATION.md")).read()
+    names = sorted(set(re.findall(r"\b(bf_[a-z0-9_]+)\s*\(", hdr)))
+    assert len(names) > 50
+    missing = [n for n in names if n not in doc]
+    assert not missing, missing
