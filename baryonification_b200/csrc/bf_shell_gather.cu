@@ -10,7 +10,8 @@
 //   3. every lane walks the candidate list with its own cursor, skipping (integer compares) to the next
 //      halo whose range holds its pixel, and evaluates that pair; lanes of a warp work on DIFFERENT halos at
 //      the same time, so the fp64 pipe stays full even when discs are narrower than the strip.
-// Each pixel's contributions are summed in registers in catalogue order and written once: no atomics, no
+// Each pixel's contributions are summed in registers in a fixed order (per candidate chunk: the whole-strip candidates
+// in catalogue order, then the partly covering ones in catalogue order) and written once: no atomics, no
 // read-modify-write traffic, bit-reproducible.
 //
 // Pair arithmetic (fp64).  With delta = v - c (unit vectors), |delta|^2 = d2:
